@@ -1,0 +1,111 @@
+// Shared definitions of the featurizer kernels (sm_100a) and of their host-side emulation build.
+//
+// Every kernel is written as a sequence of PHASES separated by block barriers.  A phase is a plain
+// function of (params, shared-memory base, thread id, CTA id) that uses no warp intrinsics, so the
+// identical source also compiles with g++ (tests/emu/): there the phases run thread after thread over
+// an ordinary array.  That build exists to check index maps, codelets and tables on the GPU-less
+// authoring box; it is test infrastructure and is never linked into libb200feat.so.
+#pragma once
+#include <stdint.h>
+#include <math.h>
+
+#if defined(__CUDACC__)
+#define FE_HD __device__
+#define FE_INLINE __forceinline__
+#define FE_CONSTANT __constant__ const
+#define FE_LOG2(x) __log2f(x)
+#define FE_SQRT(x) sqrtf(x)
+#else
+#define FE_HD
+#define FE_INLINE inline __attribute__((always_inline))
+#define FE_CONSTANT static const
+#define FE_LOG2(x) log2f(x)
+#define FE_SQRT(x) sqrtf(x)
+struct float2 { float x, y; };
+struct float4 { float x, y, z, w; };
+static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b; return r; }
+#endif
+
+#define FE_WARP 32
+
+// order-preserving float <-> int key (signed compare of keys == float compare)
+FE_HD FE_INLINE int fe_float_key(float f) {
+    union { float f; int i; } u;
+    u.f = f;
+    return u.i >= 0 ? u.i : (u.i ^ 0x7fffffff);
+}
+FE_HD FE_INLINE float fe_key_float(int k) {
+    union { float f; int i; } u;
+    u.i = k >= 0 ? k : (k ^ 0x7fffffff);
+    return u.f;
+}
+// key lower than the key of every finite value the kernels produce (memset byte 0x80)
+#define FE_KEY_INIT_BYTE 0x80
+#define FE_KEY_INIT ((int)0x80808080)
+
+// reflect-pad fetch: index g into a signal of `lp` samples (the first `len` real, the rest zeros),
+// reflected without repeating the edge sample (torch pad_mode="reflect").
+FE_HD FE_INLINE float fe_fetch_reflect(const float* __restrict__ x, int64_t g, int64_t len, int64_t lp) {
+    if (g < 0) g = -g;
+    if (g >= lp) g = 2 * (lp - 1) - g;
+    if (g < 0) g = 0;               // degenerate clips shorter than the pad: stay in bounds
+    if (g >= lp) g = lp - 1;
+    return (g < len) ? x[g] : 0.0f;
+}
+
+enum { FE_NORM_PER_CLIP = 0, FE_NORM_PER_CALL = 1 };
+
+struct FeWhisperParams {
+    const float* wave;         // (B, wave_stride) fp32
+    const int64_t* lengths;    // nullable, device: valid samples per clip
+    int64_t wave_stride;
+    int64_t L;                 // samples per clip when lengths == nullptr (also the clamp for lengths)
+    int32_t B;
+    int32_t padding;           // zeros appended to every clip before framing
+    int32_t n_mels;            // 80 | 128
+    int32_t norm_mode;         // FE_NORM_*
+    float* out;                // (B, n_mels, T_out)
+    int64_t out_batch_stride;  // floats between clips in `out`
+    int64_t T_out;             // frames per output row (row stride)
+    int32_t tiles_per_clip;    // ceil(T_out / 32)
+    int32_t vec_ok;            // wave base 16B-aligned and wave_stride % 4 == 0
+    int32_t* max_keys;         // (B) or (1): order-preserving keys of the running max
+    int32_t clip0;             // first clip of this launch (clips are processed in waves)
+    int32_t nclips;            // clips in this launch
+};
+
+struct FeCosyParams {
+    const float* wave;         // (B, wave_stride) fp32 @ 24 kHz
+    const int64_t* lengths;
+    int64_t wave_stride;
+    int64_t L;
+    int32_t B;
+    float* out;                // (B, 80, T_out)
+    int64_t out_batch_stride;
+    int64_t T_out;
+    int32_t tiles_per_clip;    // ceil(T_out / 16)
+    int32_t vec_ok;
+};
+
+struct FeKaldiParams {
+    const float* wave;         // (B, wave_stride) fp32 @ 16 kHz
+    const int64_t* lengths;
+    int64_t wave_stride;
+    int64_t L;
+    int32_t B;
+    int32_t subtract_mean;
+    float* out;                // (B, T_out, 80) frame-major
+    int64_t out_batch_stride;
+    int64_t T_out;
+    int32_t tiles_per_clip;    // ceil(T_out / 32)
+    int32_t vec_ok;
+    float* colsum;             // workspace (B, tiles_per_clip, 80): per-tile column sums for CMN
+};
+
+FE_HD FE_INLINE int64_t fe_clip_len(const int64_t* lengths, int b, int64_t L) {
+    if (lengths == nullptr) return L;
+    int64_t v = lengths[b];
+    if (v < 0) v = 0;
+    if (v > L) v = L;
+    return v;
+}

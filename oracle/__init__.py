@@ -1,0 +1,32 @@
+"""CPU oracle for the waveform -> log-mel / mel / fbank hot path.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``oracle/`` is part of the product: only
+``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import it, and only as the checker / the timed CPU
+baseline.  The product (``expressive_speech_translation_b200``) never imports it
+and has no CPU fallback.
+
+Parity status: the reference (RobMills28/Expressive-Speech-Translation) holds NO
+golden vectors or numeric tests for this path, and the
+arithmetic lives in third-party packages (openai-whisper [unpinned], Matcha-TTS
+inside the missing CosyVoice submodule fca1df3e, torchaudio.compliance.kaldi).
+The oracle is pinned instead against the implementations that ARE importable in
+the authoring container (see ``oracle/make_golden.py``):
+  * Whisper log-mel  : transformers.WhisperFeatureExtractor torch + numpy paths
+                       (independent restatements of whisper/audio.py)
+  * kaldi fbank      : torchaudio.compliance.kaldi.fbank itself (the real code
+                       the reference's CosyVoice frontend calls)
+  * CosyVoice mel    : restated from matcha/utils/audio.py::mel_spectrogram with
+                       the parameters bound at /root/reference/greek_sft.yaml:55-63;
+                       single-source ("parity unpinned" for this one), cross-checked
+                       only against an independent numpy/fp64 restatement.
+"""
+from .filters import slaney_mel_filters, kaldi_mel_banks  # noqa: F401
+from .featurizers import (  # noqa: F401
+    whisper_log_mel,
+    cosyvoice_mel,
+    kaldi_fbank,
+    whisper_num_frames,
+    cosyvoice_num_frames,
+    kaldi_num_frames,
+)

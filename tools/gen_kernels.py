@@ -1,0 +1,277 @@
+#!/usr/bin/env python
+"""Generates the straight-line parts of the featurizer kernels.
+
+  expressive_speech_translation_b200/csrc/generated/fe_codelets.h   DFT codelets (tools/fftgen.py)
+  expressive_speech_translation_b200/csrc/generated/fe_tables.h     windows, inter-stage twiddles,
+                                                                    unrolled sparse mel projections
+
+Run from the repo root:  python tools/gen_kernels.py
+The output is committed; the build does not run this script.
+
+Filter tables baked here:
+  * Slaney mel (Whisper 80/128 @16k/400, CosyVoice 80 @24k/1920): librosa.filters.mel formula
+    (SURVEY.md appendix A.1), float64 -> float32, identical to whisper's mel_filters.npz /
+    transformers.audio_utils.mel_filter_bank(norm="slaney", mel_scale="slaney").
+  * kaldi banks: torchaudio.compliance.kaldi.get_mel_banks(80, 512, 16000, 20, 0, 100, -500, 1.0)
+    itself (site-packages/torchaudio/compliance/kaldi.py:436-511), float32.
+"""
+import math
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import fftgen as g  # noqa: E402
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "expressive_speech_translation_b200", "csrc", "generated")
+
+
+# ------------------------------------------------------------------ filters
+def hz_to_mel(f):
+    f = np.asarray(f, dtype=np.float64)
+    f_sp = 200.0 / 3
+    min_log_hz = 1000.0
+    min_log_mel = min_log_hz / f_sp
+    logstep = math.log(6.4) / 27.0
+    return np.where(f >= min_log_hz, min_log_mel + np.log(np.maximum(f, 1e-300) / min_log_hz) / logstep, f / f_sp)
+
+
+def mel_to_hz(m):
+    m = np.asarray(m, dtype=np.float64)
+    f_sp = 200.0 / 3
+    min_log_hz = 1000.0
+    min_log_mel = min_log_hz / f_sp
+    logstep = math.log(6.4) / 27.0
+    return np.where(m >= min_log_mel, min_log_hz * np.exp(logstep * (m - min_log_mel)), f_sp * m)
+
+
+def slaney(sr, n_fft, n_mels, fmin, fmax):
+    nb = n_fft // 2 + 1
+    ff = np.arange(nb, dtype=np.float64) * (float(sr) / n_fft)
+    mel_f = mel_to_hz(np.linspace(hz_to_mel(fmin), hz_to_mel(fmax), n_mels + 2))
+    fd = np.diff(mel_f)
+    ramps = mel_f[:, None] - ff[None, :]
+    w = np.zeros((n_mels, nb))
+    for i in range(n_mels):
+        w[i] = np.maximum(0.0, np.minimum(-ramps[i] / fd[i], ramps[i + 2] / fd[i + 1]))
+    w *= (2.0 / (mel_f[2:n_mels + 2] - mel_f[:n_mels]))[:, None]
+    return w.astype(np.float32)
+
+
+def kaldi_banks():
+    import torchaudio
+    b, _ = torchaudio.compliance.kaldi.get_mel_banks(80, 512, 16000.0, 20.0, 0.0, 100.0, -500.0, 1.0)
+    out = np.zeros((80, 257), dtype=np.float32)
+    out[:, :256] = b.numpy()
+    return out
+
+
+# ------------------------------------------------------------------ helpers
+def flit(v):
+    v = float(np.float32(v))
+    s = repr(v)
+    if "e" not in s and "." not in s and "inf" not in s and "nan" not in s:
+        s += ".0"
+    return s + "f"
+
+
+def emit_array(name, arr, per_line=8, ctype="float"):
+    flat = [flit(v) for v in np.asarray(arr).reshape(-1)]
+    lines = [f"FE_CONSTANT {ctype} {name}[{len(flat)}] = {{"]
+    for i in range(0, len(flat), per_line):
+        lines.append("    " + ", ".join(flat[i:i + per_line]) + ",")
+    lines.append("};")
+    return "\n".join(lines)
+
+
+def gen_codelet(name, n, real_in=False, nz=None, outs=None, real_out=()):
+    """void name(const float* xr, [const float* xi,] float* yr, float* yi)
+    inputs x[0..nz) (rest zero); outputs listed in `outs` written at yr[j], yi[j] (j = position
+    in `outs`); outputs whose index is in `real_out` have no imaginary part emitted."""
+    d = g.Dag()
+    nz = n if nz is None else nz
+    xs = []
+    for i in range(n):
+        if i < nz:
+            xs.append(g.C(d.inp(("r", i)), None if real_in else d.inp(("i", i))))
+        else:
+            xs.append(g.C(None, None))
+    ys = g.dft(d, xs)
+    outs = list(range(n)) if outs is None else list(outs)
+    vals, slots = [], []
+    for j, k in enumerate(outs):
+        vals.append(ys[k].re)
+        slots.append(("r", j))
+        if k not in real_out:
+            vals.append(ys[k].im)
+            slots.append(("i", j))
+    ops = g.count_ops(d, vals)
+
+    def in_expr(nm):
+        return f"x{nm[0]}[{nm[1]}]"
+
+    def out_stmt(idx, e):
+        s = slots[idx]
+        return f"y{s[0]}[{s[1]}] = {e};"
+
+    body = g.emit_body(d, vals, in_expr, out_stmt)
+    args = "const float* __restrict__ xr, " + ("" if real_in else "const float* __restrict__ xi, ")
+    args += "float* __restrict__ yr, float* __restrict__ yi"
+    hdr = (f"// DFT-{n} {'real' if real_in else 'complex'} input ({nz} non-zero), outputs k={outs[0]}..{outs[-1]}"
+           f"  [{ops['add'] + ops['sub']} add/sub, {ops['mul']} mul before FMA contraction]\n")
+    return hdr + f"FE_HD FE_INLINE void {name}({args}) {{\n{body}\n}}\n"
+
+
+# ------------------------------------------------------------------ mel projection
+def partition(costs, nch):
+    """contiguous partition of `costs` into nch chunks minimising the max chunk cost."""
+    n = len(costs)
+    lo, hi = max(costs), sum(costs)
+
+    def fits(cap):
+        cnt, cur = 1, 0
+        for c in costs:
+            if cur + c > cap:
+                cnt += 1
+                cur = c
+            else:
+                cur += c
+        return cnt <= nch
+
+    while lo < hi:
+        mid = (lo + hi) // 2
+        if fits(mid):
+            hi = mid
+        else:
+            lo = mid + 1
+    cap = lo
+    bounds, cur, start = [], 0, 0
+    for i, c in enumerate(costs):
+        if cur + c > cap:
+            bounds.append((start, i))
+            start, cur = i, c
+        else:
+            cur += c
+    bounds.append((start, n))
+    while len(bounds) < nch:  # split the largest multi-filter chunk until we have nch
+        j = max(range(len(bounds)), key=lambda q: (bounds[q][1] - bounds[q][0] > 1) * sum(costs[bounds[q][0]:bounds[q][1]]))
+        a, b = bounds[j]
+        if b - a <= 1:
+            break
+        mid = (a + b) // 2
+        bounds[j:j + 1] = [(a, mid), (mid, b)]
+    return bounds
+
+
+def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
+    """template<int PS, class Emit> void name(int chunk, const float* P, Emit&& emit)
+    P points at this lane's column: bin k lives at P[k*PS].  emit(m, value) is called once per
+    filter of the chunk."""
+    n_mels = filt.shape[0]
+    assert not np.any(filt[:, max_bin + 1:]), "filter weight beyond max_bin"
+    costs = []
+    for m in range(n_mels):
+        nnz = int(np.count_nonzero(filt[m]))
+        costs.append(2 * nnz + epi_cost)
+    bounds = partition(costs, nch)
+    out = [f"// sparse mel projection, {n_mels} filters, {int(np.count_nonzero(filt))} non-zeros, {len(bounds)} chunks",
+           f"#define {name.upper()}_NCHUNK {len(bounds)}",
+           "template <int PS, class Emit>",
+           f"FE_HD FE_INLINE void {name}(int chunk, const float* __restrict__ P, Emit&& emit) {{",
+           "    switch (chunk) {"]
+    for c, (a, b) in enumerate(bounds):
+        out.append(f"    case {c}: {{  // filters {a}..{b - 1}")
+        bins = sorted(set(int(k) for m in range(a, b) for k in np.nonzero(filt[m])[0]))
+        body = []
+        decl = set()
+        for k in bins:
+            body.append(f"        {{ const float p = P[{k} * PS];")
+            for m in range(a, b):
+                w = filt[m, k]
+                if w != 0:
+                    if m in decl:
+                        body.append(f"          a{m} = fmaf(p, {flit(w)}, a{m});")
+                    else:
+                        body.append(f"          a{m} = p * {flit(w)};")
+                        decl.add(m)
+            body.append("        }")
+        out.append("        float " + ", ".join(f"a{m} = 0.0f" for m in range(a, b)) + ";")
+        out.extend(body)
+        for m in range(a, b):
+            out.append(f"        emit({m}, a{m});")
+        out.append("    } break;")
+    out.append("    default: break;")
+    out.append("    }")
+    out.append("}")
+    return "\n".join(out) + "\n"
+
+
+def twiddle_table(N, rows, cols):
+    """float2 table T[row][col] = exp(-2*pi*i*row*col/N), rows x cols."""
+    t = np.zeros((rows, cols, 2), dtype=np.float64)
+    for r in range(rows):
+        for c in range(cols):
+            wr, wi = g.twiddle(r * c, N)
+            t[r, c] = (wr, wi)
+    return t
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    # ---------------- codelets
+    cl = ["// GENERATED by tools/gen_kernels.py -- do not edit.", "#pragma once", ""]
+    # Whisper: N = 400 = 20 x 20
+    cl.append(gen_codelet("fe_rdft20_h11", 20, real_in=True, outs=range(11), real_out=(0, 10)))
+    cl.append(gen_codelet("fe_cdft20", 20))
+    cl.append(gen_codelet("fe_rdft20_h10", 20, real_in=True, outs=range(10), real_out=(0,)))
+    cl.append(gen_codelet("fe_cdft20_h10", 20, outs=range(10)))
+    # kaldi: N = 512 = 32 x 16, 400 samples -> n1 < 25 non-zero
+    cl.append(gen_codelet("fe_rdft32z25_h17", 32, real_in=True, nz=25, outs=range(17), real_out=(0, 16)))
+    cl.append(gen_codelet("fe_cdft16", 16))
+    cl.append(gen_codelet("fe_rdft16_h8", 16, real_in=True, outs=range(8), real_out=(0,)))
+    cl.append(gen_codelet("fe_cdft16_h8", 16, outs=range(8)))
+    # CosyVoice: N = 1920 = 16 x 12 x 10
+    cl.append(gen_codelet("fe_rdft16_h9", 16, real_in=True, outs=range(9), real_out=(0, 8)))
+    cl.append(gen_codelet("fe_cdft12", 12))
+    cl.append(gen_codelet("fe_cdft10", 10))
+    with open(os.path.join(OUT, "fe_codelets.h"), "w") as f:
+        f.write("\n".join(cl))
+
+    # ---------------- tables
+    tb = ["// GENERATED by tools/gen_kernels.py -- do not edit.", "#pragma once", ""]
+    n = np.arange(400, dtype=np.float64)
+    tb.append("// periodic Hann, N = 400 (torch.hann_window default)")
+    tb.append(emit_array("fe_win_whisper", 0.5 - 0.5 * np.cos(2 * np.pi * n / 400.0)))
+    tb.append("// povey = symmetric Hann ^ 0.85, N = 400 (torchaudio kaldi.py:100)")
+    tb.append(emit_array("fe_win_kaldi", (0.5 - 0.5 * np.cos(2 * np.pi * n / 399.0)) ** 0.85))
+    n = np.arange(1920, dtype=np.float64)
+    tb.append("// periodic Hann, N = 1920")
+    tb.append(emit_array("fe_win_cosy", 0.5 - 0.5 * np.cos(2 * np.pi * n / 1920.0)))
+    tb.append("// Whisper stage-A twiddles W_400^(n2*k1), [n2 = 0..19][k1 = 0..10] (re, im)")
+    tb.append(emit_array("fe_tw_whisper", twiddle_table(400, 20, 11)))
+    tb.append("// kaldi stage-A twiddles W_512^(n2*k1), [n2 = 0..15][k1 = 0..16]")
+    tb.append(emit_array("fe_tw_kaldi", twiddle_table(512, 16, 17)))
+    tb.append("// CosyVoice stage-A twiddles W_1920^(m*k1), [m = 0..119][k1 = 0..8]")
+    tb.append(emit_array("fe_tw_cosy_a", twiddle_table(1920, 120, 9)))
+    tb.append("// CosyVoice stage-B twiddles W_120^(n3*k2), [n3 = 0..9][k2 = 0..11]")
+    tb.append(emit_array("fe_tw_cosy_b", twiddle_table(120, 10, 12)))
+    w80 = slaney(16000, 400, 80, 0.0, 8000.0)
+    w128 = slaney(16000, 400, 128, 0.0, 8000.0)
+    cz = slaney(24000, 1920, 80, 0.0, 8000.0)
+    kb = kaldi_banks()
+    tb.append(gen_melproj("fe_melproj_w80", w80, 10, 199))
+    tb.append(gen_melproj("fe_melproj_w128", w128, 10, 199))
+    tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
+    tb.append(gen_melproj("fe_melproj_cosy", cz, 16, 639))
+    with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
+        f.write("\n".join(tb))
+    # the float32 tables the kernels bake, for the parity tests (tests/ compares them to the oracle's)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "baked_filters.npz"),
+                        whisper80=w80, whisper128=w128, cosy80=cz, kaldi80=kb)
+    print("wrote", OUT)
+
+
+if __name__ == "__main__":
+    main()
