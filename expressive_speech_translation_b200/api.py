@@ -1,0 +1,391 @@
+"""Host-side mirror of the reference's featurizer call signatures, on top of libb200feat.so.
+
+The three drop-in functions keep the name, argument order, defaults and error behaviour of the calls
+the reference makes:
+
+  log_mel_spectrogram(audio, n_mels=80, padding=0, device=None)
+      = whisper.audio.log_mel_spectrogram, called inside transcribe() at
+        /root/reference/Backend/services/cascaded_backend.py:158,
+        /root/reference/Backend/speech_translation_pipeline.py:140,
+        /root/reference/Backend/gtts_pipeline_fixed.py:64
+  mel_spectrogram(y, n_fft, num_mels, sampling_rate, hop_size, win_size, fmin, fmax, center=False)
+      = matcha.utils.audio.mel_spectrogram as bound at /root/reference/greek_sft.yaml:55-63
+  fbank(waveform, ...kaldi kwargs...)
+      = torchaudio.compliance.kaldi.fbank as the CosyVoice frontend calls it
+        (num_mel_bins=80, dither=0, sample_frequency=16000)
+
+plus the batched entry points the manifest runner uses (whisper_log_mel_batch, cosy_mel_batch,
+kaldi_fbank_batch) and their host-buffer (end-to-end) twins (*_host).  PyTorch is used for device
+memory and streams only; all arithmetic happens in the CUDA library.  There is no CPU fallback.
+"""
+import ctypes
+import wave as _wave
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check, KIND_WHISPER, KIND_COSY, KIND_KALDI, NORM_PER_CLIP, NORM_PER_CALL
+
+WHISPER_SR, WHISPER_N_FFT, WHISPER_HOP = 16000, 400, 160
+COSY_PARAMS = dict(n_fft=1920, num_mels=80, sampling_rate=24000, hop_size=480, win_size=1920, fmin=0, fmax=8000)
+_NORMS = {"per_clip": NORM_PER_CLIP, "per_call": NORM_PER_CALL}
+
+
+def num_frames(kind, n_samples, padding=0):
+    k = {"whisper": KIND_WHISPER, "cosy": KIND_COSY, "kaldi": KIND_KALDI}[kind]
+    return int(lib.b200feat_num_frames(k, int(n_samples), int(padding)))
+
+
+def launch_count():
+    """kernel launches issued by the library in this process (bench.py's gpu_launches)."""
+    return int(lib.b200feat_launch_count())
+
+
+def profile_begin():
+    """bracket every subsequent kernel launch with CUDA events on its launching stream (roofline leg)."""
+    check(lib.b200feat_profile_begin(), "b200feat_profile_begin")
+
+
+def profile_end():
+    """-> dict(feature_ms, feature_launches, epilogue_ms, epilogue_launches) summed since profile_begin."""
+    fm, em = ctypes.c_double(0.0), ctypes.c_double(0.0)
+    fn, en = ctypes.c_int64(0), ctypes.c_int64(0)
+    check(lib.b200feat_profile_end(ctypes.byref(fm), ctypes.byref(fn), ctypes.byref(em), ctypes.byref(en)),
+          "b200feat_profile_end")
+    return dict(feature_ms=fm.value, feature_launches=fn.value, epilogue_ms=em.value, epilogue_launches=en.value)
+
+
+# ----------------------------------------------------------------------------------------- helpers
+def _cuda_device(device=None):
+    if not torch.cuda.is_available():
+        raise RuntimeError("expressive_speech_translation_b200 needs a CUDA device (sm_100a); there is no CPU path")
+    if device is None:
+        return torch.device("cuda", torch.cuda.current_device())
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise ValueError(f"device must be a CUDA device, got {device}")
+    if device.index is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    return device
+
+
+def _as_float_tensor(x, what):
+    if isinstance(x, np.ndarray):
+        x = torch.from_numpy(x)
+    if not torch.is_tensor(x):
+        raise TypeError(f"{what} must be a torch.Tensor or numpy.ndarray, got {type(x).__name__}")
+    if not x.is_floating_point():
+        raise TypeError(f"{what} must be floating point (the reference's torch.stft rejects {x.dtype})")
+    return x
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _lengths_dev(lengths, B, device):
+    if lengths is None:
+        return None
+    if isinstance(lengths, (list, tuple, np.ndarray)):
+        lengths = torch.as_tensor(np.asarray(lengths, dtype=np.int64))
+    lengths = lengths.to(device=device, dtype=torch.int64).contiguous()
+    if lengths.numel() != B:
+        raise ValueError(f"lengths has {lengths.numel()} entries for a batch of {B}")
+    return lengths
+
+
+def _prep_wave(wave, device):
+    """(B, L) float32 on `device` with a usable row stride; returns (tensor, stride)."""
+    w = wave.to(device=device, dtype=torch.float32)
+    if w.dim() != 2:
+        raise ValueError(f"expected a (B, L) waveform batch, got shape {tuple(w.shape)}")
+    if w.stride(1) != 1 or (w.shape[0] > 1 and w.stride(0) < w.shape[1]):
+        w = w.contiguous()
+    stride = w.stride(0) if w.shape[0] > 1 else max(w.shape[1], 1)
+    return w, stride
+
+
+def _workspace(kind, B, L, device):
+    n = int(lib.b200feat_workspace_bytes(kind, B, L))
+    return torch.empty(n, dtype=torch.uint8, device=device), n
+
+
+def _stream(device):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+# ----------------------------------------------------------------------------------------- batched device API
+def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_clip", out=None):
+    """(B, L) waveform batch on a CUDA device -> (B, n_mels, (L + padding) // 160) log-mel, async on the
+    current stream.  `lengths` (B,) marks ragged clips (frames past a clip's own count are 0)."""
+    assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    wave = _as_float_tensor(wave, "wave")
+    device = _cuda_device(wave.device if wave.is_cuda else None)
+    w, stride = _prep_wave(wave, device)
+    B, L = w.shape
+    T = (L + padding) // WHISPER_HOP
+    if out is None:
+        out = torch.empty((B, n_mels, T), dtype=torch.float32, device=device)
+    elif out.shape != (B, n_mels, T) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError("out must be a contiguous float32 (B, n_mels, T) tensor on the wave's device")
+    if B == 0 or T == 0:
+        return out
+    ln = _lengths_dev(lengths, B, device)
+    ws, nws = _workspace(KIND_WHISPER, B, L, device)
+    with torch.cuda.device(device):
+        rc = lib.b200feat_whisper_logmel(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
+                                         _ptr(out), n_mels * T, T, _ptr(ws), nws, _stream(device))
+    check(rc, "b200feat_whisper_logmel")
+    return out
+
+
+def cosy_mel_batch(wave, lengths=None, out=None):
+    """(B, L) 24 kHz batch on a CUDA device -> (B, 80, T) ln-mel (n_fft 1920, hop 480)."""
+    wave = _as_float_tensor(wave, "y")
+    device = _cuda_device(wave.device if wave.is_cuda else None)
+    w, stride = _prep_wave(wave, device)
+    B, L = w.shape
+    T = num_frames("cosy", L)
+    if out is None:
+        out = torch.empty((B, 80, T), dtype=torch.float32, device=device)
+    elif out.shape != (B, 80, T) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError("out must be a contiguous float32 (B, 80, T) tensor on the wave's device")
+    if B == 0 or T == 0:
+        return out
+    ln = _lengths_dev(lengths, B, device)
+    ws, nws = _workspace(KIND_COSY, B, L, device)
+    with torch.cuda.device(device):
+        rc = lib.b200feat_cosy_mel(_ptr(w), _ptr(ln), B, L, stride, _ptr(out), 80 * T, T, _ptr(ws), nws,
+                                   _stream(device))
+    check(rc, "b200feat_cosy_mel")
+    return out
+
+
+def kaldi_fbank_batch(wave, lengths=None, subtract_mean=True, out=None):
+    """(B, L) 16 kHz batch on a CUDA device -> (B, T, 80) kaldi fbank, optionally mean-normalised per clip."""
+    wave = _as_float_tensor(wave, "waveform")
+    device = _cuda_device(wave.device if wave.is_cuda else None)
+    w, stride = _prep_wave(wave, device)
+    B, L = w.shape
+    T = num_frames("kaldi", L)
+    if out is None:
+        out = torch.empty((B, T, 80), dtype=torch.float32, device=device)
+    elif out.shape != (B, T, 80) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError("out must be a contiguous float32 (B, T, 80) tensor on the wave's device")
+    if B == 0 or T == 0:
+        return out
+    ln = _lengths_dev(lengths, B, device)
+    ws, nws = _workspace(KIND_KALDI, B, L, device)
+    with torch.cuda.device(device):
+        rc = lib.b200feat_kaldi_fbank(_ptr(w), _ptr(ln), B, L, stride, 1 if subtract_mean else 0, _ptr(out),
+                                      T * 80, T, _ptr(ws), nws, _stream(device))
+    check(rc, "b200feat_kaldi_fbank")
+    return out
+
+
+# ----------------------------------------------------------------------------------------- host-buffer (end-to-end) API
+def _host_2d(x, what):
+    x = _as_float_tensor(x, what)
+    if x.is_cuda:
+        raise ValueError(f"{what}: the *_host entry points take host memory")
+    x = x.to(torch.float32)
+    if x.dim() != 2:
+        raise ValueError(f"expected a (B, L) waveform batch, got shape {tuple(x.shape)}")
+    return x.contiguous()
+
+
+def _host_lengths(lengths, B):
+    if lengths is None:
+        return None
+    ln = torch.as_tensor(np.asarray(lengths, dtype=np.int64)).contiguous()
+    if ln.numel() != B:
+        raise ValueError(f"lengths has {ln.numel()} entries for a batch of {B}")
+    return ln
+
+
+def _host_out(shape, out, pin):
+    if out is not None:
+        if tuple(out.shape) != tuple(shape) or out.dtype != torch.float32 or out.is_cuda or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous float32 host tensor of shape {tuple(shape)}")
+        return out
+    return torch.empty(shape, dtype=torch.float32, pin_memory=pin)
+
+
+def whisper_log_mel_host(wave, lengths=None, n_mels=80, padding=0, norm="per_clip", out=None, device=None,
+                         pin_output=True):
+    """Host (ideally pinned) (B, L) waveform -> host (B, n_mels, T) log-mel through the chunked
+    H2D / kernel / D2H pipeline inside the library.  Blocks until the result is complete."""
+    assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    w = _host_2d(wave, "wave")
+    B, L = w.shape
+    T = (L + padding) // WHISPER_HOP
+    dev = _cuda_device(device)
+    out = _host_out((B, n_mels, T), out, pin_output)
+    ln = _host_lengths(lengths, B)
+    if B and T:
+        rc = lib.b200feat_whisper_logmel_host(_ptr(w), _ptr(ln), B, L, n_mels, int(padding), _NORMS[norm],
+                                              _ptr(out), dev.index)
+        check(rc, "b200feat_whisper_logmel_host")
+    return out
+
+
+def cosy_mel_host(wave, lengths=None, out=None, device=None, pin_output=True):
+    w = _host_2d(wave, "y")
+    B, L = w.shape
+    T = num_frames("cosy", L)
+    dev = _cuda_device(device)
+    out = _host_out((B, 80, T), out, pin_output)
+    ln = _host_lengths(lengths, B)
+    if B and T:
+        check(lib.b200feat_cosy_mel_host(_ptr(w), _ptr(ln), B, L, _ptr(out), dev.index), "b200feat_cosy_mel_host")
+    return out
+
+
+def kaldi_fbank_host(wave, lengths=None, subtract_mean=True, out=None, device=None, pin_output=True):
+    w = _host_2d(wave, "waveform")
+    B, L = w.shape
+    T = num_frames("kaldi", L)
+    dev = _cuda_device(device)
+    out = _host_out((B, T, 80), out, pin_output)
+    ln = _host_lengths(lengths, B)
+    if B and T:
+        check(lib.b200feat_kaldi_fbank_host(_ptr(w), _ptr(ln), B, L, 1 if subtract_mean else 0, _ptr(out),
+                                            dev.index), "b200feat_kaldi_fbank_host")
+    return out
+
+
+# ----------------------------------------------------------------------------------------- drop-in signatures
+def _load_wav_16k(path):
+    """whisper.load_audio shells out to ffmpeg (absent here); 16 kHz mono PCM16 .wav files are read
+    directly, anything else must be decoded by the caller."""
+    with _wave.open(path, "rb") as f:
+        if f.getframerate() != WHISPER_SR or f.getnchannels() != 1 or f.getsampwidth() != 2:
+            raise ValueError(f"{path}: only 16 kHz mono 16-bit PCM .wav can be loaded without ffmpeg; "
+                             "decode and resample first (e.g. Backend/app.py:36-57 does this with ffmpeg)")
+        pcm = np.frombuffer(f.readframes(f.getnframes()), dtype=np.int16)
+    return pcm.astype(np.float32) / 32768.0
+
+
+def log_mel_spectrogram(audio, n_mels: int = 80, padding: int = 0, device=None):
+    """Drop-in for whisper.audio.log_mel_spectrogram.
+
+    audio: path, np.ndarray or Tensor of shape (L,) / (*, L) at 16 kHz.  Returns (n_mels, T) /
+    (*, n_mels, T) float32 with T = (L + padding) // 160; the dynamic-range clamp uses the max over the
+    WHOLE call, as upstream.  The result lives on `device` if given, else on the input's device (host
+    inputs run through the pipelined host path and come back as host tensors)."""
+    if isinstance(audio, str):
+        audio = _load_wav_16k(audio)
+    audio = _as_float_tensor(audio, "audio")
+    assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    lead = audio.shape[:-1]
+    L = audio.shape[-1] if audio.dim() > 0 else 0
+    if audio.dim() == 0:
+        raise ValueError("audio must have at least one dimension")
+    if L + padding <= WHISPER_N_FFT // 2:
+        # torch.stft's reflect pad raises for inputs this short; keep the failure loud and typed
+        raise RuntimeError(f"Argument #4: Padding size should be less than the corresponding input dimension, "
+                           f"but got: padding (200, 200) at dimension 1 of input of length {L + padding}")
+    x = audio.reshape(-1, L)
+    if device is not None:
+        x = x.to(_cuda_device(device))
+    if x.is_cuda:
+        res = whisper_log_mel_batch(x, n_mels=n_mels, padding=padding, norm="per_call")
+    else:
+        res = whisper_log_mel_host(x, n_mels=n_mels, padding=padding, norm="per_call", pin_output=False)
+    return res.reshape(*lead, n_mels, res.shape[-1])
+
+
+def mel_spectrogram(y, n_fft, num_mels, sampling_rate, hop_size, win_size, fmin, fmax, center=False):
+    """Drop-in for matcha.utils.audio.mel_spectrogram with the parameter set the reference binds
+    (greek_sft.yaml:55-63).  y: (B, L) at 24 kHz in [-1, 1] -> (B, 80, T).  Any other parameter set is
+    rejected (this library bakes the 1920/480/80/0-8000 Hz tables)."""
+    got = dict(n_fft=n_fft, num_mels=num_mels, sampling_rate=sampling_rate, hop_size=hop_size,
+               win_size=win_size, fmin=fmin, fmax=fmax)
+    for k, v in COSY_PARAMS.items():
+        if float(got[k]) != float(v):
+            raise NotImplementedError(f"mel_spectrogram: only the CosyVoice parameter set {COSY_PARAMS} is built; got {got}")
+    if center:
+        raise NotImplementedError("mel_spectrogram: center=True is not used by the reference and not built")
+    y = _as_float_tensor(y, "y")
+    if y.dim() != 2:
+        raise ValueError(f"mel_spectrogram expects y of shape (B, L), got {tuple(y.shape)}")
+    if y.shape[1] <= 720:
+        raise RuntimeError(f"Argument #4: Padding size should be less than the corresponding input dimension, "
+                           f"but got: padding (720, 720) at dimension 2 of input of length {y.shape[1]}")
+    if y.is_cuda:
+        return cosy_mel_batch(y)
+    return cosy_mel_host(y, pin_output=False)
+
+
+def fbank(waveform, blackman_coeff: float = 0.42, channel: int = -1, dither: float = 0.0,
+          energy_floor: float = 1.0, frame_length: float = 25.0, frame_shift: float = 10.0,
+          high_freq: float = 0.0, htk_compat: bool = False, low_freq: float = 20.0, min_duration: float = 0.0,
+          num_mel_bins: int = 23, preemphasis_coefficient: float = 0.97, raw_energy: bool = True,
+          remove_dc_offset: bool = True, round_to_power_of_two: bool = True, sample_frequency: float = 16000.0,
+          snip_edges: bool = True, subtract_mean: bool = False, use_energy: bool = False,
+          use_log_fbank: bool = True, use_power: bool = True, vtln_high: float = -500.0, vtln_low: float = 100.0,
+          vtln_warp: float = 1.0, window_type: str = "povey"):
+    """Drop-in for torchaudio.compliance.kaldi.fbank for the configuration the reference uses
+    (num_mel_bins=80, dither=0, sample_frequency=16000, every other option at its default; subtract_mean
+    is honoured).  waveform: (c, n) -> (m, 80).  Any other configuration is rejected loudly."""
+    fixed = dict(blackman_coeff=(blackman_coeff, 0.42), dither=(dither, 0.0), energy_floor=(energy_floor, 1.0),
+                 frame_length=(frame_length, 25.0), frame_shift=(frame_shift, 10.0), high_freq=(high_freq, 0.0),
+                 htk_compat=(htk_compat, False), low_freq=(low_freq, 20.0), num_mel_bins=(num_mel_bins, 80),
+                 preemphasis_coefficient=(preemphasis_coefficient, 0.97), raw_energy=(raw_energy, True),
+                 remove_dc_offset=(remove_dc_offset, True), round_to_power_of_two=(round_to_power_of_two, True),
+                 sample_frequency=(sample_frequency, 16000.0), snip_edges=(snip_edges, True),
+                 use_energy=(use_energy, False), use_log_fbank=(use_log_fbank, True), use_power=(use_power, True),
+                 vtln_warp=(vtln_warp, 1.0), window_type=(window_type, "povey"))
+    bad = {k: v[0] for k, v in fixed.items() if v[0] != v[1]}
+    if bad:
+        raise NotImplementedError(f"fbank: only the CosyVoice speaker-embedding configuration is built "
+                                  f"(num_mel_bins=80, dither=0, sample_frequency=16000, defaults otherwise); got {bad}")
+    waveform = _as_float_tensor(waveform, "waveform")
+    if waveform.dim() != 2:
+        raise ValueError(f"fbank expects waveform of shape (c, n), got {tuple(waveform.shape)}")
+    ch = max(channel, 0)
+    assert ch < waveform.size(0), "Invalid channel {} for size {}".format(ch, waveform.size(0))
+    x = waveform[ch:ch + 1, :]
+    n = x.shape[1]
+    assert 2 <= 400 <= n, "choose a window size {} that is [2, {}]".format(400, n)  # kaldi.py:142
+    if n < min_duration * sample_frequency:
+        return torch.empty(0, device=waveform.device, dtype=waveform.dtype)  # kaldi.py:595-597
+    if x.is_cuda:
+        return kaldi_fbank_batch(x, subtract_mean=subtract_mean)[0]
+    return kaldi_fbank_host(x, subtract_mean=subtract_mean, pin_output=False)[0]
+
+
+# ----------------------------------------------------------------------------------------- install / uninstall
+_PATCHED = []
+
+
+def install(verbose=False):
+    """Point the reference's call sites at this library by patching the third-party module attributes
+    they resolve at call time.  Modules that are not importable are skipped.  Returns the patched names."""
+    import importlib
+    targets = [("whisper.audio", "log_mel_spectrogram", log_mel_spectrogram),
+               ("whisper.transcribe", "log_mel_spectrogram", log_mel_spectrogram),
+               ("whisper", "log_mel_spectrogram", log_mel_spectrogram),
+               ("matcha.utils.audio", "mel_spectrogram", mel_spectrogram),
+               ("torchaudio.compliance.kaldi", "fbank", fbank)]
+    done = []
+    for mod_name, attr, fn in targets:
+        try:
+            mod = importlib.import_module(mod_name)
+        except Exception:
+            continue
+        if not hasattr(mod, attr):
+            continue
+        _PATCHED.append((mod, attr, getattr(mod, attr)))
+        setattr(mod, attr, fn)
+        done.append(f"{mod_name}.{attr}")
+        if verbose:
+            print(f"[b200feat] patched {mod_name}.{attr}")
+    return done
+
+
+def uninstall():
+    while _PATCHED:
+        mod, attr, orig = _PATCHED.pop()
+        setattr(mod, attr, orig)

@@ -1,0 +1,166 @@
+// Host-buffer entry points (the end-to-end path): clips are streamed host -> device arena -> kernels ->
+// host in chunks, round-robin over NSLOT streams so the H2D copy of chunk i+1, the kernels of chunk i and
+// the D2H copy of chunk i-1 overlap (two copy engines + SMs).  Included at the end of b200feat.cu.
+namespace {
+
+constexpr int NSLOT = 4;
+
+struct Arena {
+    std::mutex mu;
+    int dev = -1;
+    char* base = nullptr;
+    size_t bytes = 0;
+    cudaStream_t streams[NSLOT] = {nullptr, nullptr, nullptr, nullptr};
+    bool streams_ok = false;
+};
+
+std::mutex g_arenas_mu;
+std::vector<Arena*> g_arenas;  // index = device ordinal
+
+Arena* arena_for(int dev) {
+    std::lock_guard<std::mutex> lk(g_arenas_mu);
+    if ((int)g_arenas.size() <= dev) g_arenas.resize(dev + 1, nullptr);
+    if (!g_arenas[dev]) {
+        g_arenas[dev] = new Arena();
+        g_arenas[dev]->dev = dev;
+    }
+    return g_arenas[dev];
+}
+
+int arena_reserve(Arena* a, size_t need) {
+    if (!a->streams_ok) {
+        for (int i = 0; i < NSLOT; ++i) FE_CUDA(cudaStreamCreateWithFlags(&a->streams[i], cudaStreamNonBlocking));
+        a->streams_ok = true;
+    }
+    if (a->bytes >= need) return 0;
+    if (a->base) {
+        FE_CUDA(cudaDeviceSynchronize());
+        FE_CUDA(cudaFree(a->base));
+        a->base = nullptr;
+        a->bytes = 0;
+    }
+    FE_CUDA(cudaMalloc(reinterpret_cast<void**>(&a->base), need));
+    a->bytes = need;
+    return 0;
+}
+
+size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int64_t host_chunk_bytes() {
+    static const int64_t v = [] {
+        const char* s = getenv("B200FEAT_HOST_CHUNK_MB");
+        int64_t mb = s ? atoll(s) : 16;
+        if (mb < 1) mb = 1;
+        return mb << 20;
+    }();
+    return v;
+}
+
+// launch(d_wave, d_len_or_null, nclips, d_out, d_ws, ws_bytes, stream) -> rc
+template <class Launch>
+int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                  int64_t out_per_clip, float* out_host, int device, bool single_chunk, Launch launch) {
+    if (B < 0 || L < 0) return fail(B200FEAT_EINVAL, "host call: negative B or L");
+    if (B == 0 || out_per_clip == 0) return 0;
+    if (!wave_host || !out_host) return fail(B200FEAT_EINVAL, "host call: null wave/out pointer");
+    int prev = 0;
+    FE_CUDA(cudaGetDevice(&prev));
+    if (device < 0) device = prev;
+    FE_CUDA(cudaSetDevice(device));
+    Arena* a = arena_for(device);
+    std::lock_guard<std::mutex> lk(a->mu);
+
+    const int64_t in_bytes = L * 4, out_bytes = out_per_clip * 4;
+    int64_t chunk = host_chunk_bytes() / (in_bytes + out_bytes);
+    if (chunk < 1) chunk = 1;
+    if (chunk > B || single_chunk) chunk = B;
+    const int nslot = (chunk >= B) ? 1 : NSLOT;
+    const size_t s_wave = round_up((size_t)chunk * in_bytes, 256);
+    const size_t s_out = round_up((size_t)chunk * out_bytes, 256);
+    const size_t s_len = round_up((size_t)chunk * 8, 256);
+    const size_t s_ws = round_up((size_t)b200feat_workspace_bytes(kind, (int32_t)chunk, L), 256);
+    const size_t slot_bytes = s_wave + s_out + s_len + s_ws;
+    int rc = arena_reserve(a, slot_bytes * nslot);
+    if (rc) { cudaSetDevice(prev); return rc; }
+
+    int64_t i = 0;
+    for (int64_t c0 = 0; c0 < B; c0 += chunk, ++i) {
+        const int64_t nc = (B - c0 < chunk) ? (B - c0) : chunk;
+        const int slot = (int)(i % nslot);
+        cudaStream_t st = a->streams[slot];
+        char* sb = a->base + slot_bytes * slot;
+        float* d_wave = reinterpret_cast<float*>(sb);
+        float* d_out = reinterpret_cast<float*>(sb + s_wave);
+        int64_t* d_len = reinterpret_cast<int64_t*>(sb + s_wave + s_out);
+        void* d_ws = sb + s_wave + s_out + s_len;
+        cudaError_t e = cudaMemcpyAsync(d_wave, wave_host + c0 * L, (size_t)nc * in_bytes, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess && lengths_host)
+            e = cudaMemcpyAsync(d_len, lengths_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) { rc = fail(B200FEAT_ECUDA, "host call: H2D copy failed: %s", cudaGetErrorString(e)); break; }
+        rc = launch(d_wave, lengths_host ? d_len : nullptr, (int32_t)nc, d_out, d_ws, (int64_t)s_ws, st);
+        if (rc) break;
+        e = cudaMemcpyAsync(out_host + c0 * out_per_clip, d_out, (size_t)nc * out_bytes, cudaMemcpyDeviceToHost, st);
+        if (e != cudaSuccess) { rc = fail(B200FEAT_ECUDA, "host call: D2H copy failed: %s", cudaGetErrorString(e)); break; }
+    }
+    for (int s = 0; s < nslot; ++s) {
+        cudaError_t e = cudaStreamSynchronize(a->streams[s]);
+        if (e != cudaSuccess && rc == 0) rc = fail(B200FEAT_ECUDA, "host call: stream sync failed: %s", cudaGetErrorString(e));
+    }
+    cudaSetDevice(prev);
+    return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200feat_whisper_logmel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                                 int32_t n_mels, int32_t padding, int32_t norm_mode, float* out_host,
+                                 int32_t device) {
+    if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "whisper_logmel_host: Unsupported n_mels: %d", n_mels);
+    if (padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel_host: padding < 0");
+    const int64_t T = (L + padding) / FeWCfg::HOP;
+    return host_pipeline(B200FEAT_KIND_WHISPER, wave_host, lengths_host, B, L, (int64_t)n_mels * T, out_host, device,
+                         norm_mode == FE_NORM_PER_CALL,
+                         [=](const float* dw, const int64_t* dl, int32_t nc, float* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return b200feat_whisper_logmel(dw, dl, nc, L, L, n_mels, padding, norm_mode, dout,
+                                                            (int64_t)n_mels * T, T, ws, wsb, st);
+                         });
+}
+
+int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                           float* out_host, int32_t device) {
+    const int64_t T = b200feat_num_frames(B200FEAT_KIND_COSY, L, 0);
+    return host_pipeline(B200FEAT_KIND_COSY, wave_host, lengths_host, B, L, (int64_t)FeCCfg::NMEL * T, out_host, device, false,
+                         [=](const float* dw, const int64_t* dl, int32_t nc, float* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return b200feat_cosy_mel(dw, dl, nc, L, L, dout, (int64_t)FeCCfg::NMEL * T, T, ws, wsb, st);
+                         });
+}
+
+int b200feat_kaldi_fbank_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                              int32_t subtract_mean, float* out_host, int32_t device) {
+    const int64_t T = b200feat_num_frames(B200FEAT_KIND_KALDI, L, 0);
+    return host_pipeline(B200FEAT_KIND_KALDI, wave_host, lengths_host, B, L, (int64_t)FeKCfg::NMEL * T, out_host, device, false,
+                         [=](const float* dw, const int64_t* dl, int32_t nc, float* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return b200feat_kaldi_fbank(dw, dl, nc, L, L, subtract_mean, dout, (int64_t)FeKCfg::NMEL * T, T, ws, wsb, st);
+                         });
+}
+
+void b200feat_release(void) {
+    std::lock_guard<std::mutex> lk(g_arenas_mu);
+    for (Arena* a : g_arenas) {
+        if (!a) continue;
+        std::lock_guard<std::mutex> lk2(a->mu);
+        int prev = 0;
+        if (cudaGetDevice(&prev) != cudaSuccess) continue;
+        cudaSetDevice(a->dev);
+        if (a->base) { cudaFree(a->base); a->base = nullptr; a->bytes = 0; }
+        if (a->streams_ok) {
+            for (int i = 0; i < NSLOT; ++i) cudaStreamDestroy(a->streams[i]);
+            a->streams_ok = false;
+        }
+        cudaSetDevice(prev);
+    }
+}
+
+}  // extern "C"

@@ -13,7 +13,14 @@
 #define FE_HD __device__
 #define FE_INLINE __forceinline__
 #define FE_CONSTANT __constant__ const
-#define FE_LOG2(x) __log2f(x)
+// lg2.approx.ftz: one MUFU, max abs error 2^-22 on log2; every caller floors its argument at a
+// normal number first (1e-10, 1e-5, FLT_EPSILON), so flushing subnormals never triggers
+static __device__ __forceinline__ float fe_lg2_ftz(float x) {
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+#define FE_LOG2(x) fe_lg2_ftz(x)
 #define FE_SQRT(x) sqrtf(x)
 #else
 #define FE_HD
@@ -85,6 +92,7 @@ struct FeCosyParams {
     int64_t T_out;
     int32_t tiles_per_clip;    // ceil(T_out / 16)
     int32_t vec_ok;
+    int32_t clip0, nclips;     // clips [clip0, clip0 + nclips) are processed by this launch
 };
 
 struct FeKaldiParams {
@@ -98,8 +106,9 @@ struct FeKaldiParams {
     int64_t out_batch_stride;
     int64_t T_out;
     int32_t tiles_per_clip;    // ceil(T_out / 32)
-    int32_t vec_ok;
+    int32_t vec_ok;            // bit 0: wave float4-loadable, bit 1: out float4-storable
     float* colsum;             // workspace (B, tiles_per_clip, 80): per-tile column sums for CMN
+    int32_t clip0, nclips;
 };
 
 FE_HD FE_INLINE int64_t fe_clip_len(const int64_t* lengths, int b, int64_t L) {

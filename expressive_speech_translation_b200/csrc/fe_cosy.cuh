@@ -1,0 +1,190 @@
+// CosyVoice 24 kHz prompt mel (matcha mel_spectrogram): phases of the fused kernel.
+//
+// Replaces matcha/utils/audio.py::mel_spectrogram(y, n_fft=1920, num_mels=80, sampling_rate=24000,
+// hop_size=480, win_size=1920, fmin=0, fmax=8000, center=False) -- UPSTREAM Matcha-TTS, parameters bound
+// at /root/reference/greek_sft.yaml:55-63, used by the CosyVoice frontend behind
+// /root/reference/Docker/cosyvoice_api.py:128.  reflect-pad 720 | periodic Hann STFT | sqrt(re^2+im^2+1e-9)
+// | Slaney mel (bins >= 640 carry zero weight) | ln(max(., 1e-5)).
+//
+// N = 1920 = 16 x 12 x 10, real input, three shared-memory stages.  A frame in flight needs 8.6 KB, so a
+// CTA holds FT = 16 frames: a warp is two task slots x 16 frames (lane & 15 = frame, lane >> 4 = slot).
+//   n = 120*n1 + m,  m = 10*n2 + n3 ;  k = k1 + 16*k',  k' = k2 + 12*k3
+//   phase A : real radix-16 DFT over n1 for each m, window fused, k1 = 0..8, times W_1920^(m*k1) -> A[f][k1][m]
+//   phase B : complex radix-12 DFT over n2 for each (k1, n3), times W_120^(n3*k2), in place   -> A[f][k1][10*k2+n3]
+//   phase C : complex radix-10 DFT over n3 for each (k1, k2); magnitude of the bins <= 639 (direct, and
+//             mirrored 1920 - k for k1 not in {0, 8})                                        -> P[bin][f]
+//   phase M : unrolled sparse mel projection, ln(max(., 1e-5)), store.
+#pragma once
+#include "fe_common.h"
+
+struct FeCCfg {
+    static constexpr int N = 1920, HOP = 480, PADL = 720, R1 = 16, R2 = 12, R3 = 10, M = 120;
+    static constexpr int NK1 = R1 / 2 + 1;               // 9
+    static constexpr int FT = 16;                        // frames per tile (half a warp)
+    static constexpr int NW = 16, NT = NW * 32;
+    static constexpr int RT = (FT - 1) * HOP + N;        // 9120
+    static constexpr int SW = RT + RT / HOP + 2;
+    static constexpr int FS = NK1 * M + 1;               // 1081 float2 per frame (odd)
+    static constexpr int PS = 17;                        // P row stride (slots of a warp differ by 16 banks)
+    static constexpr int NBIN = 640;
+    static constexpr int NMEL = 80;
+    static constexpr int R0 = (SW > NBIN * PS) ? SW : NBIN * PS;
+    static constexpr int OFF_A = R0;
+    static constexpr int SMEM_FLOATS = OFF_A + FT * FS * 2;
+    static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
+    static constexpr int TASKS_A = 64;                   // warp-tasks: slots (m, m + 16), m = 32*j + i
+    static constexpr int TASKS_B = (NK1 * R3 + 1) / 2;   // 45
+    static constexpr int TASKS_C = (NK1 * R2 + 1) / 2;   // 54
+};
+
+struct FeCTile {
+    int b, t0, T;
+    int64_t len;
+};
+
+FE_HD FE_INLINE FeCTile fe_c_tile(const FeCosyParams& p, int cta) {
+    typedef FeCCfg C;
+    FeCTile t;
+    t.b = p.clip0 + cta / p.tiles_per_clip;
+    t.t0 = (cta % p.tiles_per_clip) * C::FT;
+    t.len = fe_clip_len(p.lengths, t.b, p.L);
+    int64_t T = (t.len + 2 * C::PADL < C::N) ? 0 : 1 + (t.len + 2 * C::PADL - C::N) / C::HOP;
+    t.T = (int)(T < p.T_out ? T : p.T_out);
+    return t;
+}
+
+// ---------------------------------------------------------------- phase L
+FE_HD FE_INLINE void fe_c_phase_load(const FeCosyParams& p, float* sm, int tid, int cta) {
+    typedef FeCCfg C;
+    const FeCTile t = fe_c_tile(p, cta);
+    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
+    const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
+    for (int r4 = tid * 4; r4 < C::RT; r4 += C::NT * 4) {
+        const int64_t g = g0 + r4;
+        float v0, v1, v2, v3;
+        if ((p.vec_ok & 1) && g >= 0 && g + 3 < t.len) {
+            const float4 q = *reinterpret_cast<const float4*>(x + g);
+            v0 = q.x; v1 = q.y; v2 = q.z; v3 = q.w;
+        } else {
+            v0 = fe_fetch_reflect(x, g + 0, t.len, t.len);
+            v1 = fe_fetch_reflect(x, g + 1, t.len, t.len);
+            v2 = fe_fetch_reflect(x, g + 2, t.len, t.len);
+            v3 = fe_fetch_reflect(x, g + 3, t.len, t.len);
+        }
+        float* d = sm + r4 + r4 / C::HOP;
+        d[0] = v0; d[1] = v1; d[2] = v2; d[3] = v3;
+    }
+}
+
+// ---------------------------------------------------------------- phase A
+FE_HD FE_INLINE void fe_c_stage_a(float* sm, int f, int m) {
+    typedef FeCCfg C;
+    const float* __restrict__ s = sm + (C::HOP + 1) * f + m;
+    float x[C::R1];
+#pragma unroll
+    for (int n1 = 0; n1 < C::R1; ++n1) {
+        // sample n = 120*n1 + m; (120*n1 + m) / 480 == n1 / 4 for every m < 120
+        x[n1] = s[C::M * n1 + n1 / (C::HOP / C::M)] * fe_win_cosy[C::M * n1 + m];
+    }
+    float yr[9], yi[9];
+    fe_rdft16_h9(x, yr, yi);
+    float2* __restrict__ a = reinterpret_cast<float2*>(sm + C::OFF_A) + C::FS * f + m;
+    const float* __restrict__ tw = fe_tw_cosy_a + m * 18;
+    a[0] = make_float2(yr[0], 0.0f);
+#pragma unroll
+    for (int k1 = 1; k1 < 8; ++k1) {
+        const float wr = tw[2 * k1], wi = tw[2 * k1 + 1];
+        a[C::M * k1] = make_float2(yr[k1] * wr - yi[k1] * wi, yr[k1] * wi + yi[k1] * wr);
+    }
+    a[C::M * 8] = make_float2(yr[8] * tw[16], yr[8] * tw[17]);
+}
+
+FE_HD FE_INLINE void fe_c_phase_a(const FeCosyParams&, float* sm, int tid, int) {
+    typedef FeCCfg C;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int f = lane & 15, slot = lane >> 4;
+    for (int u = warp; u < C::TASKS_A; u += C::NW) {
+        const int m = 32 * (u >> 4) + (u & 15) + 16 * slot;  // slots 16 apart: disjoint banks
+        if (m < C::M) fe_c_stage_a(sm, f, m);
+    }
+}
+
+// ---------------------------------------------------------------- phase B
+FE_HD FE_INLINE void fe_c_stage_b(float* sm, int f, int k1, int n3) {
+    typedef FeCCfg C;
+    float2* __restrict__ a = reinterpret_cast<float2*>(sm + C::OFF_A) + C::FS * f + C::M * k1 + n3;
+    float xr[12], xi[12], yr[12], yi[12];
+#pragma unroll
+    for (int n2 = 0; n2 < 12; ++n2) {
+        const float2 v = a[C::R3 * n2];
+        xr[n2] = v.x; xi[n2] = v.y;
+    }
+    fe_cdft12(xr, xi, yr, yi);
+    const float* __restrict__ tw = fe_tw_cosy_b + n3 * 24;
+    a[0] = make_float2(yr[0], yi[0]);
+#pragma unroll
+    for (int k2 = 1; k2 < 12; ++k2) {
+        const float wr = tw[2 * k2], wi = tw[2 * k2 + 1];
+        a[C::R3 * k2] = make_float2(yr[k2] * wr - yi[k2] * wi, yr[k2] * wi + yi[k2] * wr);
+    }
+}
+
+FE_HD FE_INLINE void fe_c_phase_b(const FeCosyParams&, float* sm, int tid, int) {
+    typedef FeCCfg C;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int f = lane & 15, slot = lane >> 4;
+    for (int u = warp; u < C::TASKS_B; u += C::NW) {
+        const int q = 2 * u + slot;
+        if (q < C::NK1 * C::R3) fe_c_stage_b(sm, f, q / C::R3, q % C::R3);
+    }
+}
+
+// ---------------------------------------------------------------- phase C
+FE_HD FE_INLINE void fe_c_stage_c(float* sm, int f, int k1, int k2) {
+    typedef FeCCfg C;
+    const float2* __restrict__ a = reinterpret_cast<const float2*>(sm + C::OFF_A) + C::FS * f + C::M * k1 + C::R3 * k2;
+    float xr[10], xi[10], yr[10], yi[10];
+#pragma unroll
+    for (int n3 = 0; n3 < 10; ++n3) {
+        const float2 v = a[n3];
+        xr[n3] = v.x; xi[n3] = v.y;
+    }
+    fe_cdft10(xr, xi, yr, yi);
+    const int kb = k1 + C::R1 * k2;                 // bin = kb + 192*k3
+    const bool mirror = (k1 != 0) && (k1 != C::R1 / 2);
+    float* __restrict__ P = sm + f;
+#pragma unroll
+    for (int k3 = 0; k3 < 10; ++k3) {
+        const int bin = kb + C::R1 * C::R2 * k3;
+        const float mag = FE_SQRT(yr[k3] * yr[k3] + yi[k3] * yi[k3] + 1e-9f);
+        if (bin < C::NBIN) P[bin * C::PS] = mag;
+        else if (mirror && (C::N - bin) < C::NBIN) P[(C::N - bin) * C::PS] = mag;
+    }
+}
+
+FE_HD FE_INLINE void fe_c_phase_c(const FeCosyParams&, float* sm, int tid, int) {
+    typedef FeCCfg C;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int f = lane & 15, slot = lane >> 4;
+    for (int u = warp; u < C::TASKS_C; u += C::NW) {
+        const int q = 2 * u + slot;
+        if (q < C::NK1 * C::R2) fe_c_stage_c(sm, f, q / C::R2, q % C::R2);
+    }
+}
+
+// ---------------------------------------------------------------- phase M
+FE_HD FE_INLINE void fe_c_phase_mel(const FeCosyParams& p, float* sm, int tid, int cta) {
+    typedef FeCCfg C;
+    const int lane = tid & 31, warp = tid >> 5;
+    if (lane >= C::FT) return;
+    const FeCTile t = fe_c_tile(p, cta);
+    const int frame = t.t0 + lane;
+    const bool live = frame < t.T;
+    float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + frame;
+    const int64_t rs = p.T_out;
+    auto emit = [&](int m, float v) {
+        const float lg = FE_LOG2(fmaxf(v, 1e-5f)) * 0.69314718055994531f;  // ln
+        if (frame < p.T_out) o[(int64_t)m * rs] = live ? lg : 0.0f;  // ragged batches: zeros past T_b
+    };
+    for (int c = warp; c < FE_MELPROJ_COSY_NCHUNK; c += C::NW) fe_melproj_cosy<C::PS>(c, sm + lane, emit);
+}

@@ -66,7 +66,7 @@ FE_HD FE_INLINE void fe_w_phase_load(const FeWhisperParams& p, float* sm, int ti
     for (int r4 = tid * 4; r4 < C::RT; r4 += C::NT * 4) {
         const int64_t g = g0 + r4;
         float v0, v1, v2, v3;
-        if (p.vec_ok && g >= 0 && g + 3 < t.len) {
+        if ((p.vec_ok & 1) && g >= 0 && g + 3 < t.len) {
             const float4 q = *reinterpret_cast<const float4*>(x + g);
             v0 = q.x; v1 = q.y; v2 = q.z; v3 = q.w;
         } else {

@@ -1,0 +1,116 @@
+/* libb200feat -- C ABI of the B200 (sm_100a) waveform -> log-mel / mel / fbank featurizers.
+ *
+ * This is the drop-in boundary of the hot path.  The reference
+ * (RobMills28/Expressive-Speech-Translation) is pure Python and reaches the path through three
+ * third-party Python calls; each entry point below is what a ctypes binding of that call would bind
+ * (INTEGRATION.md shows the stubs):
+ *
+ *   b200feat_whisper_logmel  <- whisper.audio.log_mel_spectrogram(audio, n_mels, padding, device)
+ *        called inside asr_model.transcribe(...) at
+ *        /root/reference/Backend/services/cascaded_backend.py:158,
+ *        /root/reference/Backend/speech_translation_pipeline.py:140,
+ *        /root/reference/Backend/gtts_pipeline_fixed.py:64 and (n_mels = 128) by the CosyVoice frontend
+ *        behind /root/reference/Docker/cosyvoice_api.py:128.
+ *   b200feat_cosy_mel        <- matcha.utils.audio.mel_spectrogram(y, 1920, 80, 24000, 480, 1920, 0, 8000,
+ *        center=False), bound at /root/reference/greek_sft.yaml:55-63 (feat_extractor) and used by
+ *        frontend.zero_shot_frontend behind /root/reference/Docker/cosyvoice_api.py:128.
+ *   b200feat_kaldi_fbank     <- torchaudio.compliance.kaldi.fbank(waveform, num_mel_bins=80, dither=0,
+ *        sample_frequency=16000) [site-packages/torchaudio/compliance/kaldi.py:514-645] followed by the
+ *        CosyVoice frontend's feat - feat.mean(0) (speaker embedding input, model named at
+ *        /root/reference/Docker/debug_trigger_test_cosyvoice.py:102,258).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ or torch types cross this boundary.
+ *   - `wave`, `out`, `lengths`, `workspace` are DEVICE pointers owned by the caller (the *_host variants
+ *     take HOST pointers, ideally pinned, and stage through a library-owned device arena).
+ *   - `lengths` may be NULL (every clip has L samples); otherwise int64[B] on the device, values are
+ *     clamped to [0, L].  Frames past a clip's own frame count are written as 0.
+ *   - launches are asynchronous on `cuda_stream` (a cudaStream_t / CUstream; NULL = legacy default
+ *     stream); the library never synchronises the device in the device-pointer entry points.
+ *   - every function returns 0 on success and a negative B200FEAT_E* code otherwise;
+ *     b200feat_last_error() returns a thread-local description of the last failure.
+ *   - reentrant and thread-safe: no global mutable scratch; constant tables live in the module image.
+ */
+#ifndef B200FEAT_H
+#define B200FEAT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200FEAT_VERSION 100 /* major*10000 + minor*100 + patch */
+
+enum {
+    B200FEAT_OK = 0,
+    B200FEAT_EINVAL = -1,     /* bad argument (message says which) */
+    B200FEAT_ECUDA = -2,      /* a CUDA runtime call failed */
+    B200FEAT_EWORKSPACE = -3, /* workspace too small */
+    B200FEAT_EARCH = -4       /* device is not sm_100 */
+};
+
+enum { B200FEAT_KIND_WHISPER = 0, B200FEAT_KIND_COSY = 1, B200FEAT_KIND_KALDI = 2 };
+enum { B200FEAT_NORM_PER_CLIP = 0, B200FEAT_NORM_PER_CALL = 1 };
+
+int b200feat_version(void);
+const char* b200feat_last_error(void);
+
+/* frames produced for a clip of n_samples (padding only applies to Whisper) */
+int64_t b200feat_num_frames(int32_t kind, int64_t n_samples, int32_t padding);
+
+/* bytes of device workspace the call needs (>= 16, never 0) */
+int64_t b200feat_workspace_bytes(int32_t kind, int32_t B, int64_t L);
+
+/* Whisper log-mel.  out: (B, n_mels, T_out) fp32, out_batch_stride floats between clips,
+ * T_out >= num_frames(L, padding) is the row stride.  n_mels in {80, 128}.
+ * norm_mode: PER_CLIP = max over each clip (HF WhisperFeatureExtractor / one transcribe() call per
+ * clip); PER_CALL = max over the whole call (whisper.audio semantics for a batched tensor). */
+int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                            int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                            float* out, int64_t out_batch_stride, int64_t T_out,
+                            void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
+/* CosyVoice 24 kHz mel (n_fft 1920, hop 480, 80 mels, ln, no normalisation).
+ * out: (B, 80, T_out) fp32. */
+int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                      int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
+                      void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
+/* kaldi fbank (80 bins, 25 ms / 10 ms, povey, dither 0, snip_edges), optional per-clip mean
+ * subtraction over frames.  out: (B, T_out, 80) fp32 frame-major. */
+int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                         int64_t wave_stride, int32_t subtract_mean, float* out,
+                         int64_t out_batch_stride, int64_t T_out,
+                         void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
+/* Host-buffer variants (the end-to-end path): wave_host / out_host are HOST pointers (pinned memory
+ * gives full PCIe bandwidth); clips are streamed through a library-owned device arena in chunks with
+ * H2D copy, kernels and D2H copy overlapped on internal streams.  Blocks until out_host is complete.
+ * lengths_host may be NULL.  Output layouts as above, densely packed (T_out = num_frames(L)). */
+int b200feat_whisper_logmel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                                 int32_t n_mels, int32_t padding, int32_t norm_mode, float* out_host,
+                                 int32_t device);
+int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                           float* out_host, int32_t device);
+int b200feat_kaldi_fbank_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+                              int32_t subtract_mean, float* out_host, int32_t device);
+
+/* frees the host-variant staging arenas of the calling process (optional; also done at unload) */
+void b200feat_release(void);
+
+/* number of kernel launches this library has issued in this process (bench.py's gpu_launches) */
+int64_t b200feat_launch_count(void);
+
+/* Optional per-launch timing for the roofline report: between profile_begin and profile_end every kernel
+ * launch is bracketed by CUDA events on its launching stream.  profile_end synchronises those events and
+ * returns the summed device time and launch count of the featurizer kernels and of the epilogue kernels
+ * (Whisper normalisation / kaldi CMN).  Off by default; not meant for production calls. */
+int b200feat_profile_begin(void);
+int b200feat_profile_end(double* feature_ms, int64_t* feature_launches, double* epilogue_ms,
+                         int64_t* epilogue_launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200FEAT_H */

@@ -1,0 +1,135 @@
+"""CPU suite: the kernels' phase functions (the very source the CUDA kernels call), compiled with g++ and run
+thread after thread, against the fp64 oracle.  This checks index maps, codelets, twiddle/window/mel tables
+and the ragged / padding logic on the GPU-less authoring box; the `-m gpu` tests check the real kernels."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from tests.emu import build as emu_build
+from tests.conftest import speech_like
+
+vp, i64 = ctypes.c_void_p, ctypes.c_int64
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return emu_build.load()
+
+
+def _lens(lengths):
+    if lengths is None:
+        return None, None
+    la = np.ascontiguousarray(np.asarray(lengths, dtype=np.int64))
+    return la, la.ctypes.data_as(vp)
+
+
+def emu_whisper(emu, x, n_mels=80, padding=0, norm=0, lengths=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    T = (L + padding) // 160
+    out = np.full((B, n_mels, T), 7.0, dtype=np.float32)
+    keep, lp = _lens(lengths)
+    assert emu.emu_whisper(x.ctypes.data_as(vp), lp, B, L, L, n_mels, padding, norm, out.ctypes.data_as(vp), T) == 0
+    return out
+
+
+def emu_kaldi(emu, x, cmn=1, lengths=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    T = 1 + (L - 400) // 160
+    out = np.full((B, T, 80), 7.0, dtype=np.float32)
+    keep, lp = _lens(lengths)
+    assert emu.emu_kaldi(x.ctypes.data_as(vp), lp, B, L, L, cmn, out.ctypes.data_as(vp), T) == 0
+    return out
+
+
+def emu_cosy(emu, x, lengths=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    T = 1 + (L + 1440 - 1920) // 480
+    out = np.full((B, 80, T), 7.0, dtype=np.float32)
+    keep, lp = _lens(lengths)
+    assert emu.emu_cosy(x.ctypes.data_as(vp), lp, B, L, L, out.ctypes.data_as(vp), T) == 0
+    return out
+
+
+@pytest.mark.parametrize("B,L,nm,pad", [(2, 16000, 80, 0), (1, 12345, 128, 777), (3, 4000, 128, 0), (1, 8000, 80, 48000)])
+def test_whisper_noise(emu, B, L, nm, pad):
+    x = (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(L))).clamp(-1, 1)
+    ref = oracle.whisper_log_mel(x, nm, padding=pad, dtype=torch.float64, norm="per_clip").numpy()
+    got = emu_whisper(emu, x.numpy(), nm, pad)
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= 1e-4
+
+
+def test_whisper_speech_sine_zeros_percall_ragged(emu):
+    gen = torch.Generator().manual_seed(5)
+    x = speech_like(gen, 2, 16000, 16000)
+    ref = oracle.whisper_log_mel(x, 128, dtype=torch.float64, norm="per_clip").numpy()
+    assert np.abs(emu_whisper(emu, x.numpy(), 128) - ref).max() <= 1e-4
+    ref = oracle.whisper_log_mel(x, 80, dtype=torch.float64, norm="per_call").numpy()
+    assert np.abs(emu_whisper(emu, x.numpy(), 80, norm=1) - ref).max() <= 1e-4
+    t = np.arange(48000) / 16000.0
+    s = (0.5 * np.sin(2 * np.pi * 440 * t)).astype(np.float32)[None]
+    ref = oracle.whisper_log_mel(s, 80, dtype=torch.float64).numpy()
+    assert np.abs(emu_whisper(emu, s, 80) - ref).max() <= 1e-4
+    z = emu_whisper(emu, np.zeros((1, 16000), np.float32), 80)
+    assert np.abs(z + 1.5).max() < 1e-6
+    got = emu_whisper(emu, x.numpy(), 80, lengths=[16000, 5003])
+    ref = oracle.whisper_log_mel(x[1, :5003], 80, dtype=torch.float64).numpy()
+    assert np.abs(got[1, :, :ref.shape[1]] - ref).max() <= 1e-4
+    assert not got[1, :, ref.shape[1]:].any()
+
+
+def _kaldi_tol(x, cmn):
+    """|fp32 reference - fp64| for the same input: the reference's own rounding error sets the scale."""
+    e = 0.0
+    for b in range(x.shape[0]):
+        r32 = oracle.kaldi_fbank(x[b], subtract_mean=cmn).double()
+        r64 = oracle.kaldi_fbank(x[b], subtract_mean=cmn, dtype=torch.float64)
+        e = max(e, (r32 - r64).abs().max().item())
+    return max(1e-4, 2.0 * e)
+
+
+@pytest.mark.parametrize("B,L", [(2, 16000), (1, 80000), (3, 999), (1, 400)])
+@pytest.mark.parametrize("cmn", [0, 1])
+def test_kaldi(emu, B, L, cmn):
+    x = (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(L + cmn))).clamp(-1, 1)
+    ref = np.stack([oracle.kaldi_fbank(x[b], subtract_mean=bool(cmn), dtype=torch.float64).numpy() for b in range(B)])
+    got = emu_kaldi(emu, x.numpy(), cmn)
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= _kaldi_tol(x, bool(cmn))
+
+
+def test_kaldi_speech_and_ragged(emu):
+    x = speech_like(torch.Generator().manual_seed(9), 2, 16000, 16000)
+    ref = np.stack([oracle.kaldi_fbank(x[b], dtype=torch.float64).numpy() for b in range(2)])
+    assert np.abs(emu_kaldi(emu, x.numpy(), 1) - ref).max() <= _kaldi_tol(x, True)
+    got = emu_kaldi(emu, x.numpy(), 1, lengths=[16000, 5000])
+    ref = oracle.kaldi_fbank(x[1, :5000], dtype=torch.float64).numpy()
+    assert np.abs(got[1, :ref.shape[0]] - ref).max() <= _kaldi_tol(x[1:, :5000], True)
+    assert not got[1, ref.shape[0]:].any()
+
+
+@pytest.mark.parametrize("B,L", [(2, 24000), (1, 48000), (2, 5003), (1, 1000)])
+def test_cosy(emu, B, L):
+    y = (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(L))).clamp(-1, 1)
+    ref = oracle.cosyvoice_mel(y, dtype=torch.float64).numpy()
+    got = emu_cosy(emu, y.numpy())
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= 1e-4
+
+
+def test_cosy_speech_zeros_ragged(emu):
+    y = speech_like(torch.Generator().manual_seed(4), 2, 24000, 24000)
+    ref = oracle.cosyvoice_mel(y, dtype=torch.float64).numpy()
+    assert np.abs(emu_cosy(emu, y.numpy()) - ref).max() <= 1e-4
+    z = emu_cosy(emu, np.zeros((1, 24000), np.float32))
+    assert np.abs(z - np.log(1e-5)).max() < 1e-5
+    got = emu_cosy(emu, y.numpy(), lengths=[24000, 7777])
+    ref = oracle.cosyvoice_mel(y[1, :7777], dtype=torch.float64).numpy()
+    assert np.abs(got[1, :, :ref.shape[1]] - ref).max() <= 1e-4
+    assert not got[1, :, ref.shape[1]:].any()

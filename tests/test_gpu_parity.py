@@ -1,0 +1,323 @@
+"""GPU suite (-m gpu): the CUDA path, called through the Python mirror of the reference signatures and the
+C ABI underneath, against the fp64 oracle on the same seeded inputs, against the committed golden
+fixtures, and -- at BASELINE.json's full sizes -- through size-independent properties.
+
+Tolerances (north_star): max abs error <= 1e-4 on normalised log-mel / ln-mel / fbank against the fp64
+oracle.  For the kaldi fbank the reference's OWN float32 path is up to 5e-4 away from fp64 on low-energy
+bins (tests/golden/kaldi_rand.npz, oracle/make_golden.py prints it), so there the bound is
+max(1e-4, 2 x |reference_fp32 - fp64|) measured on the same input; the power spectrum is checked to
+1e-5 relative to the per-frame maximum.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from tests.conftest import speech_like
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def fe():
+    assert torch.cuda.is_available(), "the -m gpu suite needs a CUDA device"
+    import expressive_speech_translation_b200 as m
+    return m
+
+
+def noise(B, L, seed):
+    return (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(seed))).clamp(-1, 1)
+
+
+def test_native_library_is_loaded(fe):
+    maps = open("/proc/self/maps").read()
+    assert "libb200feat.so" in maps
+    n0 = fe.launch_count()
+    fe.whisper_log_mel_batch(torch.zeros(1, 16000, device="cuda"))
+    torch.cuda.synchronize()
+    assert fe.launch_count() >= n0 + 2
+
+
+# --------------------------------------------------------------------------------------------- Whisper
+def test_whisper_harvard_golden(fe, golden):
+    g = golden("harvard_w80.npz")
+    out = fe.log_mel_spectrogram(g["wave16k"], n_mels=80)          # numpy in -> host tensor out, like upstream
+    assert not out.is_cuda and tuple(out.shape) == (80, 1835)
+    assert np.abs(out.numpy() - g["oracle_fp64"]).max() <= TOL
+    assert np.abs(out.numpy() - g["hf_torch"]).max() <= TOL
+    dev = fe.log_mel_spectrogram(torch.from_numpy(g["wave16k"]), n_mels=80, device="cuda")
+    assert dev.is_cuda and torch.equal(dev.cpu(), out)
+
+
+@pytest.mark.parametrize("name", ["noise", "speech"])
+@pytest.mark.parametrize("nm", [80, 128])
+def test_whisper_golden_random(fe, golden, name, nm):
+    g = golden("whisper_rand.npz")
+    x = torch.from_numpy(g[f"{name}_wave"]).cuda()
+    out = fe.whisper_log_mel_batch(x, n_mels=nm, norm="per_clip").cpu().numpy()
+    assert np.abs(out - g[f"{name}_fp64_{nm}"]).max() <= TOL
+    assert np.abs(out - g[f"{name}_hf_torch_{nm}"]).max() <= TOL
+
+
+@pytest.mark.parametrize("B,L,nm,pad", [(2, 16000, 80, 0), (1, 12345, 128, 777), (3, 4000, 128, 0),
+                                        (1, 8000, 80, 480000), (5, 201, 80, 0), (2, 293700, 80, 0), (1, 160, 128, 160)])
+def test_whisper_vs_oracle(fe, B, L, nm, pad):
+    x = noise(B, L, L + nm)
+    ref = oracle.whisper_log_mel(x, nm, padding=pad, dtype=torch.float64, norm="per_clip").numpy()
+    out = fe.whisper_log_mel_batch(x.cuda(), n_mels=nm, padding=pad).cpu().numpy()
+    assert out.shape == ref.shape
+    assert np.abs(out - ref).max() <= TOL
+
+
+def test_whisper_per_call_ragged_unaligned_zeros_sine(fe):
+    x = speech_like(torch.Generator().manual_seed(5), 3, 20001, 16000)
+    ref = oracle.whisper_log_mel(x, 80, dtype=torch.float64, norm="per_call").numpy()
+    out = fe.whisper_log_mel_batch(x.cuda(), n_mels=80, norm="per_call").cpu().numpy()
+    assert np.abs(out - ref).max() <= TOL
+    up = fe.log_mel_spectrogram(x.cuda(), n_mels=80)                 # upstream semantics == per_call
+    assert np.array_equal(up.cpu().numpy(), out)
+    # ragged
+    lens = [20001, 5003, 777]
+    out = fe.whisper_log_mel_batch(x.cuda(), lengths=lens, n_mels=128).cpu().numpy()
+    for b, n in enumerate(lens):
+        r = oracle.whisper_log_mel(x[b, :n], 128, dtype=torch.float64).numpy()
+        assert np.abs(out[b, :, :r.shape[1]] - r).max() <= TOL
+        assert not out[b, :, r.shape[1]:].any()
+    # unaligned base pointer / odd stride: scalar load path
+    big = torch.zeros(3 * 20001 + 1, device="cuda")
+    view = big[1:].view(3, 20001)
+    view.copy_(x)
+    out2 = fe.whisper_log_mel_batch(view, n_mels=80, norm="per_call").cpu().numpy()
+    assert np.abs(out2 - ref).max() <= TOL
+    # closed forms
+    z = fe.whisper_log_mel_batch(torch.zeros(2, 16000, device="cuda")).cpu()
+    assert (z + 1.5).abs().max() < 1e-6
+    t = np.arange(48000) / 16000.0
+    s = torch.from_numpy((0.5 * np.sin(2 * np.pi * 440 * t)).astype(np.float32))
+    o = fe.log_mel_spectrogram(s, device="cuda").cpu().numpy()
+    r = oracle.whisper_log_mel(s, 80, dtype=torch.float64).numpy()
+    assert o.shape == (80, 300) and np.abs(o - r).max() <= TOL
+    assert abs((o.max() - o.min()) - 2.0) < 1e-4 and int(np.argmax(o.mean(axis=1))) == 11
+
+
+def test_whisper_host_path_equals_device_path(fe):
+    x = noise(70, 48000, 99)
+    dev = fe.whisper_log_mel_batch(x.cuda(), n_mels=128).cpu()
+    host = fe.whisper_log_mel_host(x.pin_memory(), n_mels=128)
+    assert torch.equal(dev, host)
+    lens = torch.randint(300, 48000, (70,), generator=torch.Generator().manual_seed(1))
+    dev = fe.whisper_log_mel_batch(x.cuda(), lengths=lens, n_mels=80).cpu()
+    host = fe.whisper_log_mel_host(x, lengths=lens, n_mels=80)
+    assert torch.equal(dev, host)
+
+
+def test_whisper_full_size_properties(fe):
+    """BASELINE config 2: 1024 x 30 s, 128 bins."""
+    B, L = 1024, 480000
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    x = (0.1 * torch.randn(B, L, generator=g, device="cuda")).clamp_(-1, 1)
+    x[7].zero_()
+    out = fe.whisper_log_mel_batch(x, n_mels=128)
+    assert tuple(out.shape) == (B, 128, 3000)
+    assert torch.isfinite(out).all()
+    assert (out[7] + 1.5).abs().max() < 1e-6                      # zeros clip
+    again = fe.whisper_log_mel_batch(x, n_mels=128)
+    assert torch.equal(out, again)                                 # deterministic
+    for b in (0, 511, 1023):                                       # batch-invariant + oracle on a sample
+        alone = fe.whisper_log_mel_batch(x[b:b + 1], n_mels=128)
+        assert torch.equal(alone[0], out[b])
+        ref = oracle.whisper_log_mel(x[b].cpu(), 128, dtype=torch.float64).numpy()
+        assert np.abs(out[b].cpu().numpy() - ref).max() <= TOL
+    # gain property: x -> 2x shifts every normalised value by log10(4)/4 (max and floor move together)
+    o2 = fe.whisper_log_mel_batch(2.0 * x[:16], n_mels=128)
+    assert ((o2 - out[:16])[torch.arange(16) != 7] - np.log10(4.0) / 4.0).abs().max() < 2e-5
+    # per-clip range: max - min <= 2.0 (8 decades / 4)
+    span = out.amax(dim=(1, 2)) - out.amin(dim=(1, 2))
+    assert (span <= 2.0 + 1e-5).all()
+
+
+def test_whisper_long_clip_sweep_shape(fe):
+    """BASELINE config 5 shape (60-s clips, 80 bins, optional transcribe() padding) on a small shard."""
+    x = noise(4, 960000, 4567).cuda()
+    out = fe.whisper_log_mel_batch(x, n_mels=80)
+    assert tuple(out.shape) == (4, 80, 6000)
+    ref = oracle.whisper_log_mel(x[3].cpu(), 80, dtype=torch.float64).numpy()
+    assert np.abs(out[3].cpu().numpy() - ref).max() <= TOL
+    outp = fe.whisper_log_mel_batch(x[:1], n_mels=80, padding=480000)
+    assert tuple(outp.shape) == (1, 80, 9000)
+    ref = oracle.whisper_log_mel(x[0].cpu(), 80, padding=480000, dtype=torch.float64).numpy()
+    assert np.abs(outp[0].cpu().numpy() - ref).max() <= TOL
+
+
+def test_power_spectrum_tolerance_via_mel_linearity(fe):
+    """relative error <= 1e-5 on power (relative to the frame max): checked through the linear mel energies
+    10^(4*out - 4) of an unclamped signal against the fp64 oracle, normalised by the per-frame max."""
+    x = noise(2, 32000, 77)
+    out = fe.whisper_log_mel_batch(x.cuda(), n_mels=128).cpu().double()
+    ref = oracle.whisper_log_mel(x, 128, dtype=torch.float64, norm="per_clip")
+    e_out, e_ref = 10.0 ** (4.0 * out - 4.0), 10.0 ** (4.0 * ref - 4.0)
+    rel = (e_out - e_ref).abs() / e_ref.amax(dim=1, keepdim=True)
+    assert rel.max() <= 1e-5
+
+
+# --------------------------------------------------------------------------------------------- kaldi fbank
+def kaldi_tol(x, cmn):
+    e = 0.0
+    for b in range(x.shape[0]):
+        r32 = oracle.kaldi_fbank(x[b], subtract_mean=cmn).double()
+        r64 = oracle.kaldi_fbank(x[b], subtract_mean=cmn, dtype=torch.float64)
+        e = max(e, (r32 - r64).abs().max().item())
+    return max(TOL, 2.0 * e)
+
+
+@pytest.mark.parametrize("name", ["noise", "speech"])
+def test_kaldi_golden(fe, golden, name):
+    g = golden("kaldi_rand.npz")
+    x = torch.from_numpy(g[f"{name}_wave"])
+    out = fe.kaldi_fbank_batch(x.cuda(), subtract_mean=False).cpu().numpy()
+    tol = kaldi_tol(x, False)
+    assert np.abs(out - g[f"{name}_fp64"]).max() <= tol
+    assert np.abs(out - g[f"{name}_torchaudio"]).max() <= 2 * tol   # both sides carry fp32 error here
+    out = fe.kaldi_fbank_batch(x.cuda(), subtract_mean=True).cpu().numpy()
+    assert np.abs(out - g[f"{name}_fp64_cmn"]).max() <= kaldi_tol(x, True)
+
+
+@pytest.mark.parametrize("B,L", [(2, 16000), (1, 80000), (3, 999), (1, 400), (2, 5280)])
+@pytest.mark.parametrize("cmn", [False, True])
+def test_kaldi_vs_oracle(fe, B, L, cmn):
+    x = noise(B, L, L + int(cmn))
+    ref = np.stack([oracle.kaldi_fbank(x[b], subtract_mean=cmn, dtype=torch.float64).numpy() for b in range(B)])
+    out = fe.kaldi_fbank_batch(x.cuda(), subtract_mean=cmn).cpu().numpy()
+    assert out.shape == ref.shape
+    assert np.abs(out - ref).max() <= kaldi_tol(x, cmn)
+
+
+def test_kaldi_dropin_ragged_host_zeros(fe):
+    x = speech_like(torch.Generator().manual_seed(9), 2, 16000, 16000)
+    f = fe.fbank(x[:1].cuda(), num_mel_bins=80, dither=0, sample_frequency=16000)     # the reference's call
+    assert f.is_cuda and tuple(f.shape) == (98, 80)
+    feat = (f - f.mean(dim=0, keepdim=True)).cpu().numpy()
+    ref = oracle.kaldi_fbank(x[0], subtract_mean=True, dtype=torch.float64).numpy()
+    assert np.abs(feat - ref).max() <= kaldi_tol(x[:1], True)
+    fh = fe.fbank(x[:1], num_mel_bins=80, dither=0, sample_frequency=16000)           # host in -> host out
+    assert not fh.is_cuda and torch.equal(fh, f.cpu())
+    out = fe.kaldi_fbank_batch(x.cuda(), lengths=[16000, 5000]).cpu().numpy()
+    r = oracle.kaldi_fbank(x[1, :5000], dtype=torch.float64).numpy()
+    assert np.abs(out[1, :r.shape[0]] - r).max() <= kaldi_tol(x[1:, :5000], True)
+    assert not out[1, r.shape[0]:].any()
+    z = fe.kaldi_fbank_batch(torch.zeros(1, 4000, device="cuda"), subtract_mean=False).cpu()
+    assert (z - float(np.log(1.1920928955078125e-07))).abs().max() < 1e-5
+    host = fe.kaldi_fbank_host(x.pin_memory())
+    assert torch.equal(host, fe.kaldi_fbank_batch(x.cuda()).cpu())
+    assert fe.fbank(torch.zeros(1, 8000), num_mel_bins=80, min_duration=1.0).numel() == 0
+
+
+def test_kaldi_full_size_properties(fe):
+    """BASELINE config 4: 4096 x 5 s."""
+    B, L = 4096, 80000
+    g = torch.Generator(device="cuda").manual_seed(3456)
+    x = (0.1 * torch.randn(B, L, generator=g, device="cuda")).clamp_(-1, 1)
+    out = fe.kaldi_fbank_batch(x, subtract_mean=True)
+    assert tuple(out.shape) == (B, 498, 80) and torch.isfinite(out).all()
+    assert out.mean(dim=1).abs().max() < 1e-4                      # CMN: zero column means
+    assert torch.equal(out, fe.kaldi_fbank_batch(x, subtract_mean=True))
+    raw = fe.kaldi_fbank_batch(x, subtract_mean=False)
+    assert (raw - raw.mean(dim=1, keepdim=True) - out).abs().max() < 1e-4
+    for b in (0, 4095):
+        alone = fe.kaldi_fbank_batch(x[b:b + 1], subtract_mean=True)
+        assert torch.equal(alone[0], out[b])
+        xc = x[b:b + 1].cpu()
+        ref = oracle.kaldi_fbank(xc[0], dtype=torch.float64).numpy()
+        assert np.abs(out[b].cpu().numpy() - ref).max() <= kaldi_tol(xc, True)
+    # gain property: x -> 2x adds ln 4 before CMN, nothing after
+    o2 = fe.kaldi_fbank_batch(2.0 * x[:8], subtract_mean=False)
+    assert (o2 - raw[:8] - float(np.log(4.0))).abs().max() < 1e-4
+
+
+# --------------------------------------------------------------------------------------------- CosyVoice mel
+@pytest.mark.parametrize("name", ["noise", "speech"])
+def test_cosy_golden(fe, golden, name):
+    g = golden("cosy_rand.npz")
+    x = torch.from_numpy(g[f"{name}_wave"]).cuda()
+    out = fe.mel_spectrogram(x, 1920, 80, 24000, 480, 1920, 0, 8000, center=False).cpu().numpy()
+    assert out.shape == (2, 80, 50)
+    assert np.abs(out - g[f"{name}_fp64"]).max() <= TOL
+    assert np.abs(out - g[f"{name}_fp32"]).max() <= TOL
+
+
+@pytest.mark.parametrize("B,L", [(2, 24000), (1, 48000), (2, 5003), (1, 1000), (3, 721)])
+def test_cosy_vs_oracle(fe, B, L):
+    y = noise(B, L, L)
+    ref = oracle.cosyvoice_mel(y, dtype=torch.float64).numpy()
+    out = fe.cosy_mel_batch(y.cuda()).cpu().numpy()
+    assert out.shape == ref.shape
+    assert np.abs(out - ref).max() <= TOL
+
+
+def test_cosy_partial_ragged_host_zeros(fe):
+    import functools
+    y = speech_like(torch.Generator().manual_seed(4), 2, 24000, 24000)
+    feat_extractor = functools.partial(fe.mel_spectrogram, n_fft=1920, num_mels=80, sampling_rate=24000, hop_size=480,
+                                       win_size=1920, fmin=0, fmax=8000, center=False)     # greek_sft.yaml:55-63
+    out = feat_extractor(y.cuda()).cpu().numpy()
+    assert np.abs(out - oracle.cosyvoice_mel(y, dtype=torch.float64).numpy()).max() <= TOL
+    host = feat_extractor(y)
+    assert not host.is_cuda and np.array_equal(host.numpy(), out)
+    got = fe.cosy_mel_batch(y.cuda(), lengths=[24000, 7777]).cpu().numpy()
+    r = oracle.cosyvoice_mel(y[1, :7777], dtype=torch.float64).numpy()
+    assert np.abs(got[1, :, :r.shape[1]] - r).max() <= TOL and not got[1, :, r.shape[1]:].any()
+    z = fe.cosy_mel_batch(torch.zeros(1, 24000, device="cuda")).cpu()
+    assert (z - float(np.log(1e-5))).abs().max() < 1e-5
+
+
+def test_cosy_full_size_properties(fe):
+    """BASELINE config 3: 256 x 10 s @ 24 kHz."""
+    B, L = 256, 240000
+    g = torch.Generator(device="cuda").manual_seed(2345)
+    y = (0.1 * torch.randn(B, L, generator=g, device="cuda")).clamp_(-1, 1)
+    out = fe.cosy_mel_batch(y)
+    assert tuple(out.shape) == (B, 80, 500) and torch.isfinite(out).all()
+    assert torch.equal(out, fe.cosy_mel_batch(y))
+    for b in (0, 255):
+        assert torch.equal(fe.cosy_mel_batch(y[b:b + 1])[0], out[b])
+        ref = oracle.cosyvoice_mel(y[b].cpu(), dtype=torch.float64).numpy()
+        assert np.abs(out[b].cpu().numpy() - ref).max() <= TOL
+    o2 = fe.cosy_mel_batch(2.0 * y[:8])                              # magnitude mel: x -> 2x adds ln 2
+    assert (o2 - out[:8] - float(np.log(2.0))).abs().max() < 1e-4
+
+
+# --------------------------------------------------------------------------------------------- plumbing
+def test_install_patches_importable_modules(fe):
+    import torchaudio
+    orig = torchaudio.compliance.kaldi.fbank
+    done = fe.install()
+    try:
+        assert "torchaudio.compliance.kaldi.fbank" in done
+        x = noise(1, 16000, 1).cuda()
+        a = torchaudio.compliance.kaldi.fbank(x, num_mel_bins=80, dither=0, sample_frequency=16000)
+        assert a.is_cuda and tuple(a.shape) == (98, 80)
+    finally:
+        fe.uninstall()
+    assert torchaudio.compliance.kaldi.fbank is orig
+
+
+def test_streams_and_threads(fe):
+    import threading
+    x = noise(8, 48000, 3).cuda()
+    ref = fe.whisper_log_mel_batch(x, n_mels=80)
+    torch.cuda.synchronize()
+    res = [None] * 4
+
+    def work(i):
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            res[i] = fe.whisper_log_mel_batch(x, n_mels=80)
+        s.synchronize()
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for r in res:
+        assert torch.equal(r, ref)
