@@ -13,6 +13,7 @@ vtln_warp == 1.0, which is the only branch the reference's CosyVoice frontend
 reaches (Docker/debug_trigger_test_cosyvoice.py:102,258 -> campplus.onnx input).
 """
 import math
+import os
 
 import numpy as np
 
@@ -63,14 +64,25 @@ def slaney_mel_filters(sr, n_fft, n_mels, fmin=0.0, fmax=None, dtype=np.float32)
     return w.astype(dtype)
 
 
+_KALDI_TABLE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "kaldi_banks_80x257_f32.npy")
+
+
 def kaldi_mel_banks(num_bins=80, padded_window=512, sample_freq=16000.0, low_freq=20.0,
-                    high_freq=0.0, dtype=np.float32):
+                    high_freq=0.0, dtype=np.float32, recompute=False):
     """(num_bins, padded_window//2 + 1) kaldi triangles in the mel domain; the last
     (Nyquist) column is the zero column torchaudio pads on (kaldi.py:627).
 
-    dtype=float32 reproduces torchaudio's float32 tensor arithmetic step by step
-    (it builds the banks with float32 torch ops); dtype=float64 is the
-    higher-precision twin used for the fp64 ground truth."""
+    The reference's filter IS a float32 table: torchaudio builds it with float32 torch ops, whose `log`
+    may differ by an ulp between CPU types, and one ulp of a mel value moves a weight by ~7e-6 (1e-4
+    relative on the narrow low filters).  So for the reference configuration dtype=float32 returns the
+    table torchaudio.compliance.kaldi.get_mel_banks(80, 512, 16000, 20, 0, 100, -500, 1.0) produced in
+    the authoring container (committed as oracle/kaldi_banks_80x257_f32.npy by oracle/make_golden.py;
+    tests compare it with a live torchaudio when that is importable).  recompute=True (or any other
+    configuration) rebuilds it with numpy float32 arithmetic, step by step as torchaudio does;
+    dtype=float64 is the analytic higher-precision twin."""
+    if (dtype == np.float32 and not recompute and (num_bins, padded_window, sample_freq, low_freq, high_freq)
+            == (80, 512, 16000.0, 20.0, 0.0) and os.path.exists(_KALDI_TABLE)):
+        return np.load(_KALDI_TABLE)
     ft = np.float32 if dtype == np.float32 else np.float64
     nyquist = 0.5 * sample_freq
     if high_freq <= 0.0:

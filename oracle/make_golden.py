@@ -51,6 +51,14 @@ def main():
     import torchaudio
     from scipy.io import wavfile
 
+    # ---------------------------------------------------------------- the kaldi filter table (see oracle/filters.py)
+    tb, _ = torchaudio.compliance.kaldi.get_mel_banks(80, 512, 16000.0, 20.0, 0.0, 100.0, -500.0, 1.0)
+    table = np.zeros((80, 257), dtype=np.float32)
+    table[:, :256] = tb.numpy()
+    np.save(os.path.join(ROOT, "oracle", "kaldi_banks_80x257_f32.npy"), table)
+    baked = np.load(os.path.join(GOLD, "baked_filters.npz"))["kaldi80"]
+    assert np.array_equal(table, baked), "kernel-baked kaldi table != torchaudio's: re-run tools/gen_kernels.py"
+
     # ---------------------------------------------------------------- config 1: harvard.wav
     path = "/root/reference/Backend/harvard.wav"
     sha = hashlib.sha256(open(path, "rb").read()).hexdigest()

@@ -13,7 +13,7 @@ import pytest
 import torch
 
 import oracle
-from tests.conftest import speech_like
+from tests.conftest import speech_like, kaldi_check
 
 pytestmark = pytest.mark.gpu
 
@@ -163,50 +163,50 @@ def test_power_spectrum_tolerance_via_mel_linearity(fe):
 
 
 # --------------------------------------------------------------------------------------------- kaldi fbank
-def kaldi_tol(x, cmn):
-    e = 0.0
-    for b in range(x.shape[0]):
-        r32 = oracle.kaldi_fbank(x[b], subtract_mean=cmn).double()
-        r64 = oracle.kaldi_fbank(x[b], subtract_mean=cmn, dtype=torch.float64)
-        e = max(e, (r32 - r64).abs().max().item())
-    return max(TOL, 2.0 * e)
+def kaldi_cmn_consistent(fe, x_cuda, lengths=None):
+    """CMN output == raw output minus its own per-clip column mean (both from the GPU, fp32)."""
+    raw = fe.kaldi_fbank_batch(x_cuda, lengths=lengths, subtract_mean=False)
+    cmn = fe.kaldi_fbank_batch(x_cuda, lengths=lengths, subtract_mean=True)
+    if lengths is None:
+        assert (raw - raw.mean(dim=1, keepdim=True) - cmn).abs().max() < 2e-5
+    return raw, cmn
 
 
 @pytest.mark.parametrize("name", ["noise", "speech"])
 def test_kaldi_golden(fe, golden, name):
     g = golden("kaldi_rand.npz")
     x = torch.from_numpy(g[f"{name}_wave"])
-    out = fe.kaldi_fbank_batch(x.cuda(), subtract_mean=False).cpu().numpy()
-    tol = kaldi_tol(x, False)
-    assert np.abs(out - g[f"{name}_fp64"]).max() <= tol
-    assert np.abs(out - g[f"{name}_torchaudio"]).max() <= 2 * tol   # both sides carry fp32 error here
-    out = fe.kaldi_fbank_batch(x.cuda(), subtract_mean=True).cpu().numpy()
-    assert np.abs(out - g[f"{name}_fp64_cmn"]).max() <= kaldi_tol(x, True)
+    raw, cmn = kaldi_cmn_consistent(fe, x.cuda())
+    kaldi_check(raw.cpu().numpy(), x, name)
+    # against torchaudio's own float32 output: both sides carry float32 error in the empty bins
+    ta = g[f"{name}_torchaudio"]
+    strong = ta >= ta.max(axis=2, keepdims=True) - 4.6          # within 1e-2 of the frame max
+    assert np.abs(raw.cpu().numpy() - ta)[strong].max() <= 2e-4
 
 
 @pytest.mark.parametrize("B,L", [(2, 16000), (1, 80000), (3, 999), (1, 400), (2, 5280)])
-@pytest.mark.parametrize("cmn", [False, True])
-def test_kaldi_vs_oracle(fe, B, L, cmn):
-    x = noise(B, L, L + int(cmn))
-    ref = np.stack([oracle.kaldi_fbank(x[b], subtract_mean=cmn, dtype=torch.float64).numpy() for b in range(B)])
-    out = fe.kaldi_fbank_batch(x.cuda(), subtract_mean=cmn).cpu().numpy()
-    assert out.shape == ref.shape
-    assert np.abs(out - ref).max() <= kaldi_tol(x, cmn)
+def test_kaldi_vs_oracle(fe, B, L):
+    x = noise(B, L, L)
+    raw, cmn = kaldi_cmn_consistent(fe, x.cuda())
+    assert tuple(raw.shape) == (B, oracle.kaldi_num_frames(L), 80)
+    kaldi_check(raw.cpu().numpy(), x)
 
 
 def test_kaldi_dropin_ragged_host_zeros(fe):
     x = speech_like(torch.Generator().manual_seed(9), 2, 16000, 16000)
     f = fe.fbank(x[:1].cuda(), num_mel_bins=80, dither=0, sample_frequency=16000)     # the reference's call
     assert f.is_cuda and tuple(f.shape) == (98, 80)
-    feat = (f - f.mean(dim=0, keepdim=True)).cpu().numpy()
-    ref = oracle.kaldi_fbank(x[0], subtract_mean=True, dtype=torch.float64).numpy()
-    assert np.abs(feat - ref).max() <= kaldi_tol(x[:1], True)
+    kaldi_check(f[None].cpu().numpy(), x[:1])
     fh = fe.fbank(x[:1], num_mel_bins=80, dither=0, sample_frequency=16000)           # host in -> host out
     assert not fh.is_cuda and torch.equal(fh, f.cpu())
-    out = fe.kaldi_fbank_batch(x.cuda(), lengths=[16000, 5000]).cpu().numpy()
-    r = oracle.kaldi_fbank(x[1, :5000], dtype=torch.float64).numpy()
-    assert np.abs(out[1, :r.shape[0]] - r).max() <= kaldi_tol(x[1:, :5000], True)
-    assert not out[1, r.shape[0]:].any()
+    fm = fe.fbank(x[:1].cuda(), num_mel_bins=80, dither=0, sample_frequency=16000, subtract_mean=True)
+    assert (fm - (f - f.mean(dim=0, keepdim=True))).abs().max() < 2e-5
+    lens = [16000, 5000]
+    raw, cmn = kaldi_cmn_consistent(fe, x.cuda(), lengths=lens)
+    T1 = oracle.kaldi_num_frames(5000)
+    kaldi_check(raw[1:, :T1].cpu().numpy(), x[1:, :5000])
+    assert not raw[1, T1:].any() and not cmn[1, T1:].any()
+    assert (cmn[1, :T1] - (raw[1, :T1] - raw[1, :T1].mean(dim=0, keepdim=True))).abs().max() < 2e-5
     z = fe.kaldi_fbank_batch(torch.zeros(1, 4000, device="cuda"), subtract_mean=False).cpu()
     assert (z - float(np.log(1.1920928955078125e-07))).abs().max() < 1e-5
     host = fe.kaldi_fbank_host(x.pin_memory())
@@ -224,16 +224,16 @@ def test_kaldi_full_size_properties(fe):
     assert out.mean(dim=1).abs().max() < 1e-4                      # CMN: zero column means
     assert torch.equal(out, fe.kaldi_fbank_batch(x, subtract_mean=True))
     raw = fe.kaldi_fbank_batch(x, subtract_mean=False)
-    assert (raw - raw.mean(dim=1, keepdim=True) - out).abs().max() < 1e-4
-    for b in (0, 4095):
+    assert (raw - raw.mean(dim=1, keepdim=True) - out).abs().max() < 2e-5
+    for b in (0, 2047, 4095):
         alone = fe.kaldi_fbank_batch(x[b:b + 1], subtract_mean=True)
         assert torch.equal(alone[0], out[b])
-        xc = x[b:b + 1].cpu()
-        ref = oracle.kaldi_fbank(xc[0], dtype=torch.float64).numpy()
-        assert np.abs(out[b].cpu().numpy() - ref).max() <= kaldi_tol(xc, True)
-    # gain property: x -> 2x adds ln 4 before CMN, nothing after
+        kaldi_check(raw[b:b + 1].cpu().numpy(), x[b:b + 1].cpu(), f"full-size clip {b}")
+    # gain property: x -> 2x adds ln 4 to every feature before CMN
     o2 = fe.kaldi_fbank_batch(2.0 * x[:8], subtract_mean=False)
-    assert (o2 - raw[:8] - float(np.log(4.0))).abs().max() < 1e-4
+    d = (o2 - raw[:8] - float(np.log(4.0))).abs()
+    strong = raw[:8] >= raw[:8].amax(dim=2, keepdim=True) - 4.6
+    assert d[strong].max() < 1e-4
 
 
 # --------------------------------------------------------------------------------------------- CosyVoice mel
