@@ -132,7 +132,7 @@ def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_cl
     if B == 0 or T == 0:
         return out
     ln = _lengths_dev(lengths, B, device)
-    ws, nws = _workspace(KIND_WHISPER, B, L, device)
+    ws, nws = _workspace(KIND_WHISPER, B, L + int(padding), device)
     with torch.cuda.device(device):
         rc = lib.b200feat_whisper_logmel(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
                                          _ptr(out), n_mels * T, T, _ptr(ws), nws, _stream(device))

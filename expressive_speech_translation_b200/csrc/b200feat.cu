@@ -15,63 +15,102 @@
 #include "fe_common.h"
 #include "generated/fe_codelets.h"
 #include "generated/fe_tables.h"
-#include "fe_whisper.cuh"
+#include "fe_whisper2.cuh"
 #include "fe_kaldi.cuh"
 #include "fe_cosy.cuh"
 
 // =====================================================================================================
 // kernels
 // =====================================================================================================
+// named barriers (id 0 is __syncthreads)
+enum { FE_BAR_W_FULL = 1, FE_BAR_W_FREE = 2, FE_BAR_COMPUTE = 3 };
+static __device__ __forceinline__ void fe_bar_sync(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+static __device__ __forceinline__ void fe_bar_arrive(int id, int count) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
+// Persistent, warp-specialised: NLW loader warps run one unit ahead of NCW compute warps.
+//   loader : [wait W_FREE] fill W(u) -> arrive W_FULL
+//   compute: wait W_FULL -> phase A -> arrive W_FREE -> B -> M -> publish (min, max) of the unit
 template <int NMELS>
-__global__ void __launch_bounds__(FeWCfg::NT, 2) fe_whisper_kernel(const FeWhisperParams p) {
+__global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhisper2Params p) {
+    typedef FeW2Cfg C;
     extern __shared__ __align__(16) float sm[];
-    const int tid = threadIdx.x, cta = blockIdx.x;
-    fe_w_phase_load(p, sm, tid, cta);
+    const int tid = threadIdx.x;
+    int* keys = reinterpret_cast<int*>(sm + C::OFF_MISC);  // [0] max key, [1] min key (negated order)
+    if (tid == 0) { keys[0] = FE_KEY_INIT; keys[1] = FE_KEY_INIT; }
     __syncthreads();
-    fe_w_phase_a(p, sm, tid, cta);
-    __syncthreads();
-    fe_w_phase_b(p, sm, tid, cta);
-    __syncthreads();
-    int key = fe_w_phase_mel<NMELS>(p, sm, tid, cta);
+    if (tid >= C::NCT) {
+        const int ltid = tid - C::NCT;
+        bool first = true;
+        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+            if (!first) fe_bar_sync(FE_BAR_W_FREE, C::NT);
+            first = false;
+            const FeW2Unit t = fe_w2_unit(p, u);
+            if (t.t0 < t.T) fe_w2_phase_load(p, sm, ltid, u);
+            fe_bar_arrive(FE_BAR_W_FULL, C::NT);
+        }
+        return;
+    }
+    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const FeW2Unit t = fe_w2_unit(p, u);
+        const bool live = t.t0 < t.T;
+        const bool more = u + (int)gridDim.x < p.total_units;
+        fe_bar_sync(FE_BAR_W_FULL, C::NT);
+        if (live) fe_w2_phase_a(sm, tid);
+        if (more) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
+        if (!live) {
+            if (tid == 0) p.unit_minmax[u] = make_float2(3.0e38f, -3.0e38f);
+            continue;
+        }
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
+        fe_w2_phase_b(sm, tid);
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
+        const fe2 mm = fe_w2_phase_mel<NMELS>(p, sm, tid, u);
+        int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) key = max(key, __shfl_xor_sync(0xffffffffu, key, o));
-    int* smax = reinterpret_cast<int*>(sm + FeWCfg::OFF_MISC);
-    if ((tid & 31) == 0) atomicMax(smax, key);
-    __syncthreads();
-    if (tid == 0) {
-        const int b = p.clip0 + cta / p.tiles_per_clip;
-        atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : b), *smax);
+        for (int o = 16; o > 0; o >>= 1) {
+            kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+            kmin = max(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+        }
+        if ((tid & 31) == 0) { atomicMax(keys + 0, kmax); atomicMax(keys + 1, kmin); }
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
+        if (tid == 0) {
+            const float ymax = fe_key_float(keys[0]), ymin = -fe_key_float(keys[1]);
+            p.unit_minmax[u] = make_float2(ymin, ymax);
+            atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b), keys[0]);
+            keys[0] = FE_KEY_INIT; keys[1] = FE_KEY_INIT;
+        }
     }
 }
 
-// one CTA per (clip, mel row): out = (max(x, gmax - 8) + 4) / 4, zeros past the clip's own frames
-__global__ void __launch_bounds__(256) fe_whisper_norm_kernel(const FeWhisperParams p) {
-    const int row = blockIdx.x;
-    const int b = p.clip0 + row / p.n_mels;
-    const int m = row % p.n_mels;
-    const float gmax = fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : b]);
-    const int64_t len = fe_clip_len(p.lengths, b, p.L);
-    int64_t T = (len + p.padding) / FeWCfg::HOP;
-    if (T > p.T_out) T = p.T_out;
-    float* __restrict__ o = p.out + (int64_t)b * p.out_batch_stride + (int64_t)m * p.T_out;
-    if (p.vec_ok & 2) {
-        float4* o4 = reinterpret_cast<float4*>(o);
-        const int64_t n4 = p.T_out >> 2;
-        for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
-            const int64_t t = i << 2;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (t < T) {
-                v = __ldcg(o4 + i);  // written by the previous kernel: served from L2
-                v.x = fe_w_normalise(v.x, gmax);
-                v.y = (t + 1 < T) ? fe_w_normalise(v.y, gmax) : 0.f;
-                v.z = (t + 2 < T) ? fe_w_normalise(v.z, gmax) : 0.f;
-                v.w = (t + 3 < T) ? fe_w_normalise(v.w, gmax) : 0.f;
+// Fix-up: clamps the units whose minimum lies below max - 8 decades (y < ymax - 2) and zero-fills the
+// frames past a ragged clip's own end.  Everything else is left untouched (one trip to HBM).
+template <int NMELS>
+__global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2Params p) {
+    typedef FeW2Cfg C;
+    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const FeW2Unit t = fe_w2_unit(p, u);
+        int n_in = (int)(p.T_out - t.t0 < C::FT ? p.T_out - t.t0 : C::FT);
+        int n_live = t.T - t.t0;
+        n_live = n_live < 0 ? 0 : (n_live > C::FT ? C::FT : n_live);
+        const float2 mm = p.unit_minmax[u];
+        const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
+        const bool clampu = n_live > 0 && mm.x < thr;
+        if (!clampu && n_live >= n_in) continue;
+        float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + t.t0;
+        for (int i = threadIdx.x; i < NMELS * C::FT; i += blockDim.x) {
+            const int m = i / C::FT, c = i % C::FT;
+            if (c >= n_in) continue;
+            float* q = o + (int64_t)m * p.T_out + c;
+            if (c >= n_live) *q = 0.0f;
+            else if (clampu) {
+                const float v = *q;
+                if (v < thr) *q = thr;
             }
-            o4[i] = v;
         }
-    } else {
-        for (int64_t t = threadIdx.x; t < p.T_out; t += blockDim.x)
-            o[t] = (t < T) ? fe_w_normalise(__ldcg(o + t), gmax) : 0.f;
     }
 }
 
@@ -180,6 +219,8 @@ int fail(int code, const char* fmt, ...) {
                         __FILE__, __LINE__);                                                       \
     } while (0)
 
+int g_num_sms[64];
+
 int64_t l2_wave_bytes() {
     static const int64_t v = [] {
         const char* s = getenv("B200FEAT_L2_WAVE_MB");
@@ -205,8 +246,9 @@ int check_device_arch() {
         FE_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
         state[dev] = (major == 10) ? 1 : -1;
         if (state[dev] == 1) {
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeWCfg::SMEM_BYTES));
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeWCfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            FE_CUDA(cudaDeviceGetAttribute(&g_num_sms[dev < 64 ? dev : 0], cudaDevAttrMultiProcessorCount, dev));
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeKCfg::SMEM_BYTES));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
         }
@@ -265,7 +307,7 @@ int b200feat_profile_end(double* feature_ms, int64_t* feature_launches, double* 
 
 int64_t b200feat_num_frames(int32_t kind, int64_t n, int32_t padding) {
     switch (kind) {
-    case B200FEAT_KIND_WHISPER: return (n + padding) / FeWCfg::HOP;
+    case B200FEAT_KIND_WHISPER: return (n + padding) / FeW2Cfg::HOP;
     case B200FEAT_KIND_COSY: return (n + 2 * FeCCfg::PADL < FeCCfg::N) ? 0 : 1 + (n + 2 * FeCCfg::PADL - FeCCfg::N) / FeCCfg::HOP;
     case B200FEAT_KIND_KALDI: return n < FeKCfg::WIN ? 0 : 1 + (n - FeKCfg::WIN) / FeKCfg::HOP;
     default: return -1;
@@ -275,7 +317,11 @@ int64_t b200feat_num_frames(int32_t kind, int64_t n, int32_t padding) {
 int64_t b200feat_workspace_bytes(int32_t kind, int32_t B, int64_t L) {
     if (B < 0 || L < 0) return -1;
     switch (kind) {
-    case B200FEAT_KIND_WHISPER: return 16 + (int64_t)B * 4;
+    case B200FEAT_KIND_WHISPER: {
+        // L here = samples INCLUDING the padding of the call (or T_out * 160 if the caller's rows are longer)
+        const int64_t units = (L / FeW2Cfg::HOP + 1 + FeW2Cfg::FT - 1) / FeW2Cfg::FT;
+        return 16 + (((int64_t)B * 4 + 15) & ~(int64_t)15) + (int64_t)B * units * 8;
+    }
     case B200FEAT_KIND_COSY: return 16;
     case B200FEAT_KIND_KALDI: {
         const int64_t T = b200feat_num_frames(kind, L, 0);
@@ -295,59 +341,48 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
     if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "whisper_logmel: Unsupported n_mels: %d", n_mels);
     if (padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel: padding %d < 0", padding);
     if (norm_mode != FE_NORM_PER_CLIP && norm_mode != FE_NORM_PER_CALL) return fail(B200FEAT_EINVAL, "whisper_logmel: bad norm_mode %d", norm_mode);
-    const int64_t T_full = (L + padding) / FeWCfg::HOP;
+    const int64_t T_full = (L + padding) / FeW2Cfg::HOP;
     if (T_out < T_full) return fail(B200FEAT_EINVAL, "whisper_logmel: T_out %lld < %lld frames", (long long)T_out, (long long)T_full);
     if (out_batch_stride < (int64_t)n_mels * T_out) return fail(B200FEAT_EINVAL, "whisper_logmel: out_batch_stride too small");
-    if (L + padding <= FeWCfg::PADL && B > 0 && T_out > 0)
+    if (L + padding <= FeW2Cfg::PADL && B > 0 && T_out > 0)
         return fail(B200FEAT_EINVAL, "whisper_logmel: reflect padding (200) needs more than 200 samples, got %lld", (long long)(L + padding));
-    if (workspace_bytes < b200feat_workspace_bytes(B200FEAT_KIND_WHISPER, B, L) || workspace == nullptr)
-        return fail(B200FEAT_EWORKSPACE, "whisper_logmel: workspace too small (%lld bytes)", (long long)workspace_bytes);
+    const int64_t units = (T_out + FeW2Cfg::FT - 1) / FeW2Cfg::FT;
+    const int64_t keys_bytes = 16 + (((int64_t)B * 4 + 15) & ~(int64_t)15);
+    if (workspace == nullptr || workspace_bytes < keys_bytes + (int64_t)B * units * 8)
+        return fail(B200FEAT_EWORKSPACE, "whisper_logmel: workspace too small (%lld bytes, need %lld)",
+                    (long long)workspace_bytes, (long long)(keys_bytes + (int64_t)B * units * 8));
     if (B == 0 || T_out == 0) return 0;
     if (int rc = check_device_arch()) return rc;
+    if ((int64_t)B * units > 0x7fffffff) return fail(B200FEAT_EINVAL, "whisper_logmel: batch too large");
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    int dev = 0;
+    FE_CUDA(cudaGetDevice(&dev));
 
-    FeWhisperParams p;
+    FeWhisper2Params p;
     memset(&p, 0, sizeof(p));
     p.wave = wave; p.lengths = lengths; p.wave_stride = wave_stride; p.L = L; p.B = B;
     p.padding = padding; p.n_mels = n_mels; p.norm_mode = norm_mode;
     p.out = out; p.out_batch_stride = out_batch_stride; p.T_out = T_out;
-    const int64_t tiles = (T_out + FeWCfg::FT - 1) / FeWCfg::FT;
-    if (tiles > 0x7fffffff / 2) return fail(B200FEAT_EINVAL, "whisper_logmel: clip too long");
-    p.tiles_per_clip = (int32_t)tiles;
+    p.units_per_clip = (int32_t)units;
+    p.total_units = (int32_t)(B * units);
     p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
-    if (aligned16(out) && out_batch_stride % 4 == 0 && T_out % 4 == 0) p.vec_ok |= 2;
     p.max_keys = reinterpret_cast<int32_t*>(workspace);
-    FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, 16 + (size_t)B * 4, st));
-
-    // clips go through in waves small enough for the un-normalised log-mel to stay in L2 until the
-    // normalisation kernel of the same wave has consumed it
-    const int64_t clip_bytes = (int64_t)n_mels * T_out * 4;
-    int64_t per_wave = l2_wave_bytes() / clip_bytes;
-    if (per_wave < 1) per_wave = 1;
-    const int64_t max_ctas = 0x7fffffff;
-    if (per_wave * tiles > max_ctas) per_wave = max_ctas / tiles;
-    if (per_wave * n_mels > max_ctas) per_wave = max_ctas / n_mels;
-    for (int pass = 0; pass < 2; ++pass) {
-        // per-clip: feature+norm interleaved per wave (single pass); per-call: all features, then all norms
-        for (int64_t c0 = 0; c0 < B; c0 += per_wave) {
-            const int64_t nc = (B - c0 < per_wave) ? (B - c0) : per_wave;
-            p.clip0 = (int32_t)c0; p.nclips = (int32_t)nc;
-            const bool do_feat = (norm_mode == FE_NORM_PER_CLIP) ? (pass == 0) : (pass == 0);
-            const bool do_norm = (norm_mode == FE_NORM_PER_CLIP) ? (pass == 0) : (pass == 1);
-            if (do_feat) {
-                const unsigned grid = (unsigned)(nc * tiles);
-                ProfScope ps(st, 0);
-                if (n_mels == 80) fe_whisper_kernel<80><<<grid, FeWCfg::NT, FeWCfg::SMEM_BYTES, st>>>(p);
-                else fe_whisper_kernel<128><<<grid, FeWCfg::NT, FeWCfg::SMEM_BYTES, st>>>(p);
-                g_launches++;
-            }
-            if (do_norm) {
-                ProfScope ps(st, 1);
-                fe_whisper_norm_kernel<<<(unsigned)(nc * n_mels), 256, 0, st>>>(p);
-                g_launches++;
-            }
-        }
-        if (norm_mode == FE_NORM_PER_CLIP) break;
+    p.unit_minmax = reinterpret_cast<float2*>(reinterpret_cast<char*>(workspace) + keys_bytes);
+    FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)keys_bytes, st));
+    const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
+    {
+        const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
+        ProfScope ps(st, 0);
+        if (n_mels == 80) fe_whisper2_kernel<80><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        else fe_whisper2_kernel<128><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        g_launches++;
+    }
+    {
+        const unsigned grid = (unsigned)(p.total_units < sms * 8 ? p.total_units : sms * 8);
+        ProfScope ps(st, 1);
+        if (n_mels == 80) fe_whisper2_fixup_kernel<80><<<grid, 256, 0, st>>>(p);
+        else fe_whisper2_fixup_kernel<128><<<grid, 256, 0, st>>>(p);
+        g_launches++;
     }
     FE_CUDA(cudaGetLastError());
     return 0;

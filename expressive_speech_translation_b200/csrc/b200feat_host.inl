@@ -58,7 +58,7 @@ int64_t host_chunk_bytes() {
 
 // launch(d_wave, d_len_or_null, nclips, d_out, d_ws, ws_bytes, stream) -> rc
 template <class Launch>
-int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L, int64_t ws_L,
                   int64_t out_per_clip, float* out_host, int device, bool single_chunk, Launch launch) {
     if (B < 0 || L < 0) return fail(B200FEAT_EINVAL, "host call: negative B or L");
     if (B == 0 || out_per_clip == 0) return 0;
@@ -78,7 +78,7 @@ int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host,
     const size_t s_wave = round_up((size_t)chunk * in_bytes, 256);
     const size_t s_out = round_up((size_t)chunk * out_bytes, 256);
     const size_t s_len = round_up((size_t)chunk * 8, 256);
-    const size_t s_ws = round_up((size_t)b200feat_workspace_bytes(kind, (int32_t)chunk, L), 256);
+    const size_t s_ws = round_up((size_t)b200feat_workspace_bytes(kind, (int32_t)chunk, ws_L), 256);
     const size_t slot_bytes = s_wave + s_out + s_len + s_ws;
     int rc = arena_reserve(a, slot_bytes * nslot);
     if (rc) { cudaSetDevice(prev); return rc; }
@@ -119,8 +119,8 @@ int b200feat_whisper_logmel_host(const float* wave_host, const int64_t* lengths_
                                  int32_t device) {
     if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "whisper_logmel_host: Unsupported n_mels: %d", n_mels);
     if (padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel_host: padding < 0");
-    const int64_t T = (L + padding) / FeWCfg::HOP;
-    return host_pipeline(B200FEAT_KIND_WHISPER, wave_host, lengths_host, B, L, (int64_t)n_mels * T, out_host, device,
+    const int64_t T = (L + padding) / FeW2Cfg::HOP;
+    return host_pipeline(B200FEAT_KIND_WHISPER, wave_host, lengths_host, B, L, L + padding, (int64_t)n_mels * T, out_host, device,
                          norm_mode == FE_NORM_PER_CALL,
                          [=](const float* dw, const int64_t* dl, int32_t nc, float* dout, void* ws, int64_t wsb, cudaStream_t st) {
                              return b200feat_whisper_logmel(dw, dl, nc, L, L, n_mels, padding, norm_mode, dout,
@@ -131,7 +131,7 @@ int b200feat_whisper_logmel_host(const float* wave_host, const int64_t* lengths_
 int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                            float* out_host, int32_t device) {
     const int64_t T = b200feat_num_frames(B200FEAT_KIND_COSY, L, 0);
-    return host_pipeline(B200FEAT_KIND_COSY, wave_host, lengths_host, B, L, (int64_t)FeCCfg::NMEL * T, out_host, device, false,
+    return host_pipeline(B200FEAT_KIND_COSY, wave_host, lengths_host, B, L, L, (int64_t)FeCCfg::NMEL * T, out_host, device, false,
                          [=](const float* dw, const int64_t* dl, int32_t nc, float* dout, void* ws, int64_t wsb, cudaStream_t st) {
                              return b200feat_cosy_mel(dw, dl, nc, L, L, dout, (int64_t)FeCCfg::NMEL * T, T, ws, wsb, st);
                          });
@@ -140,7 +140,7 @@ int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, 
 int b200feat_kaldi_fbank_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                               int32_t subtract_mean, float* out_host, int32_t device) {
     const int64_t T = b200feat_num_frames(B200FEAT_KIND_KALDI, L, 0);
-    return host_pipeline(B200FEAT_KIND_KALDI, wave_host, lengths_host, B, L, (int64_t)FeKCfg::NMEL * T, out_host, device, false,
+    return host_pipeline(B200FEAT_KIND_KALDI, wave_host, lengths_host, B, L, L, (int64_t)FeKCfg::NMEL * T, out_host, device, false,
                          [=](const float* dw, const int64_t* dl, int32_t nc, float* dout, void* ws, int64_t wsb, cudaStream_t st) {
                              return b200feat_kaldi_fbank(dw, dl, nc, L, L, subtract_mean, dout, (int64_t)FeKCfg::NMEL * T, T, ws, wsb, st);
                          });

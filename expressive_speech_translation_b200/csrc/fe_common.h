@@ -31,9 +31,56 @@ static __device__ __forceinline__ float fe_lg2_ftz(float x) {
 struct float2 { float x, y; };
 struct float4 { float x, y, z, w; };
 static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b; return r; }
+static inline float4 make_float4(float a, float b, float c, float d) { float4 r; r.x = a; r.y = b; r.z = c; r.w = d; return r; }
 #endif
 
 #define FE_WARP 32
+
+// ---------------------------------------------------------------------------------------------------
+// Value types of the generated codelets.  `float` = one frame per lane; `fe2` = a PAIR of frames per
+// lane, every add / mul / fma issued once for both as a packed sm_100 instruction (FADD2 / FMUL2 /
+// FFMA2: same FP32 pipe time as two scalar instructions, half the issue slots, scalar constants are
+// broadcast by the instruction itself).  nvcc never contracts the packed intrinsics, so the generator
+// emits fused multiply-adds explicitly (tools/fftgen.py).
+typedef float2 fe2;
+
+template <class V> FE_HD FE_INLINE V fe_zero();
+template <> FE_HD FE_INLINE float fe_zero<float>() { return 0.0f; }
+template <> FE_HD FE_INLINE fe2 fe_zero<fe2>() { fe2 r; r.x = 0.0f; r.y = 0.0f; return r; }
+
+FE_HD FE_INLINE float fe_add(float a, float b) { return a + b; }
+FE_HD FE_INLINE float fe_sub(float a, float b) { return a - b; }
+FE_HD FE_INLINE float fe_neg(float a) { return -a; }
+FE_HD FE_INLINE float fe_mulc(float c, float a) { return c * a; }
+FE_HD FE_INLINE float fe_fmac(float c, float x, float y) { return fmaf(c, x, y); }     // c*x + y
+FE_HD FE_INLINE float fe_fmsc(float c, float x, float y) { return fmaf(c, x, -y); }    // c*x - y
+FE_HD FE_INLINE float fe_fnmac(float c, float x, float y) { return fmaf(-c, x, y); }   // y - c*x
+FE_HD FE_INLINE float fe_mul(float a, float b) { return a * b; }
+FE_HD FE_INLINE float fe_fma(float a, float b, float c) { return fmaf(a, b, c); }
+
+FE_HD FE_INLINE fe2 fe_mk2(float a, float b) { fe2 r; r.x = a; r.y = b; return r; }
+#if defined(__CUDACC__)
+FE_HD FE_INLINE fe2 fe_add(fe2 a, fe2 b) { return __fadd2_rn(a, b); }
+FE_HD FE_INLINE fe2 fe_sub(fe2 a, fe2 b) { return __fadd2_rn(a, fe_mk2(-b.x, -b.y)); }
+FE_HD FE_INLINE fe2 fe_neg(fe2 a) { return fe_mk2(-a.x, -a.y); }
+FE_HD FE_INLINE fe2 fe_mulc(float c, fe2 a) { return __fmul2_rn(a, fe_mk2(c, c)); }
+FE_HD FE_INLINE fe2 fe_fmac(float c, fe2 x, fe2 y) { return __ffma2_rn(x, fe_mk2(c, c), y); }
+FE_HD FE_INLINE fe2 fe_fmsc(float c, fe2 x, fe2 y) { return __ffma2_rn(x, fe_mk2(c, c), fe_mk2(-y.x, -y.y)); }
+FE_HD FE_INLINE fe2 fe_fnmac(float c, fe2 x, fe2 y) { return __ffma2_rn(x, fe_mk2(-c, -c), y); }
+FE_HD FE_INLINE fe2 fe_mul(fe2 a, fe2 b) { return __fmul2_rn(a, b); }
+FE_HD FE_INLINE fe2 fe_fma(fe2 a, fe2 b, fe2 c) { return __ffma2_rn(a, b, c); }
+#else
+FE_HD FE_INLINE fe2 fe_add(fe2 a, fe2 b) { return fe_mk2(a.x + b.x, a.y + b.y); }
+FE_HD FE_INLINE fe2 fe_sub(fe2 a, fe2 b) { return fe_mk2(a.x - b.x, a.y - b.y); }
+FE_HD FE_INLINE fe2 fe_neg(fe2 a) { return fe_mk2(-a.x, -a.y); }
+FE_HD FE_INLINE fe2 fe_mulc(float c, fe2 a) { return fe_mk2(c * a.x, c * a.y); }
+FE_HD FE_INLINE fe2 fe_fmac(float c, fe2 x, fe2 y) { return fe_mk2(fmaf(c, x.x, y.x), fmaf(c, x.y, y.y)); }
+FE_HD FE_INLINE fe2 fe_fmsc(float c, fe2 x, fe2 y) { return fe_mk2(fmaf(c, x.x, -y.x), fmaf(c, x.y, -y.y)); }
+FE_HD FE_INLINE fe2 fe_fnmac(float c, fe2 x, fe2 y) { return fe_mk2(fmaf(-c, x.x, y.x), fmaf(-c, x.y, y.y)); }
+FE_HD FE_INLINE fe2 fe_mul(fe2 a, fe2 b) { return fe_mk2(a.x * b.x, a.y * b.y); }
+FE_HD FE_INLINE fe2 fe_fma(fe2 a, fe2 b, fe2 c) { return fe_mk2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+#endif
+
 
 // order-preserving float <-> int key (signed compare of keys == float compare)
 FE_HD FE_INLINE int fe_float_key(float f) {

@@ -201,7 +201,7 @@ FE_HD FE_INLINE void fe_k_phase_mel(const FeKaldiParams&, float* sm, int tid, in
     auto emit = [&](int m, float v) {
         st[m] = FE_LOG2(fmaxf(v, C::EPS)) * 0.69314718055994531f;  // ln
     };
-    for (int c = warp; c < FE_MELPROJ_KALDI_NCHUNK; c += C::NW) fe_melproj_kaldi<C::PS>(c, sm + lane, emit);
+    for (int c = warp; c < FE_MELPROJ_KALDI_NCHUNK; c += C::NW) fe_melproj_kaldi<float>(c, [&](int k) { return sm[k * C::PS + lane]; }, emit);
 }
 
 // ---------------------------------------------------------------- phase O

@@ -1,0 +1,295 @@
+// Whisper log-mel featurizer, frame-pair kernel: phases of the persistent fused kernel.
+//
+// Replaces whisper/audio.py::log_mel_spectrogram (UPSTREAM openai-whisper; reached from
+// /root/reference/Backend/services/cascaded_backend.py:158, Backend/speech_translation_pipeline.py:140,
+// Backend/gtts_pipeline_fixed.py:64; same arithmetic as
+// transformers/models/whisper/feature_extraction_whisper.py:135-164).
+//
+// Work unit = 64 consecutive frames of one clip.  Lane l of every warp owns the frame PAIR
+// (t0 + l, t0 + 32 + l); the two frames of a pair travel through the whole pipeline side by side in one
+// 64-bit register pair, so every floating-point instruction is a packed FADD2 / FMUL2 / FFMA2 (half the
+// issue slots of the scalar formulation, constants broadcast by the instruction) and every shared-memory
+// access moves both frames at once.  All per-task constants (window, twiddles, mel weights) are uniform
+// across the warp: constant bank or immediates.
+//
+//   loader warps : waveform samples of the unit -> W[i] = (x[g0 + i], x[g0 + 5120 + i]), i < 5360, one pad
+//                  slot per 160 samples (lane stride 161 pairs: conflict-free 64-bit accesses); reflect /
+//                  zero padding resolved here.  Runs one unit ahead of the compute warps.
+//   phase A      : 20 tasks (n2); real radix-20 DFT over n1 (n = 20*n1 + n2) with the Hann window fused into
+//                  the loads, Hermitian half k1 = 0..10, times W_400^(n2*k1)  -> A[lane][k1][n2] (re2, im2)
+//   phase B      : 10 tasks; k1 = 1..9: complex radix-20 DFT over n2, |X|^2 of bins k1 + 20*j and (mirrored)
+//                  (20-k1) + 20*j written IN PLACE over the task's own A row; task 0 does k1 = 0 and k1 = 10.
+//   phase M      : unrolled sparse mel projection (immediates), log10, (x + 4) / 4, coalesced stores, running
+//                  min / max of the unit.
+// The dynamic-range clamp max(x, max - 8) needs the per-clip (or per-call) maximum: the kernel publishes the
+// maximum (atomicMax) and each unit's minimum; a second, tiny kernel re-touches only the units whose minimum
+// lies below max - 8 (none for noise-like audio, the silent stretches for speech) and zero-fills frames past
+// a ragged clip's end.  In the common case every output makes exactly one trip to HBM.
+#pragma once
+#include "fe_common.h"
+
+struct FeWhisper2Params {
+    const float* wave;         // (B, wave_stride) fp32
+    const int64_t* lengths;    // nullable, device: valid samples per clip
+    int64_t wave_stride;
+    int64_t L;                 // samples per clip when lengths == nullptr (also the clamp for lengths)
+    int32_t B;
+    int32_t padding;           // zeros appended to every clip before framing
+    int32_t n_mels;            // 80 | 128
+    int32_t norm_mode;         // FE_NORM_*
+    float* out;                // (B, n_mels, T_out)
+    int64_t out_batch_stride;  // floats between clips in `out`
+    int64_t T_out;             // frames per output row (row stride)
+    int32_t units_per_clip;    // ceil(T_out / 64)
+    int32_t total_units;       // B * units_per_clip
+    int32_t vec_ok;            // wave base 16B-aligned and wave_stride % 4 == 0
+    int32_t* max_keys;         // (B) or (1): order-preserving keys of the running max of (x + 4) / 4
+    float2* unit_minmax;       // (total_units): (min, max) of the unit's live outputs
+};
+
+struct FeW2Cfg {
+    static constexpr int N = 400, HOP = 160, PADL = 200, R = 20;
+    static constexpr int LANES = 32, FT = 64;            // frame pairs / frames per unit
+    static constexpr int SEG = LANES * HOP;              // sample distance between the frames of a pair (5120)
+    static constexpr int NCW = 10, NLW = 2;              // compute / loader warps
+    static constexpr int NCT = NCW * 32, NLT = NLW * 32, NT = NCT + NLT;
+    static constexpr int RT = (LANES - 1) * HOP + N;     // samples per segment of a unit (5360)
+    static constexpr int LS = HOP + 1;                   // lane stride in W (pairs)
+    static constexpr int SW = RT + RT / HOP + 3;         // padded W (pairs), multiple of 2 -> A is 16B-aligned
+    static constexpr int FS = 221;                       // float4 slots per lane in A (11*20 -> odd)
+    static constexpr int OFF_A = SW * 2;                 // in floats
+    static constexpr int OFF_MISC = OFF_A + LANES * FS * 4;
+    static constexpr int SMEM_FLOATS = OFF_MISC + 8;
+    static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
+    static constexpr float LOG_SCALE = 0.07525749891599530f;  // log10(2) / 4
+};
+static_assert(FeW2Cfg::SW % 2 == 0, "A must start 16B-aligned");
+
+struct FeW2Unit {
+    int b;          // clip
+    int t0;         // first frame of the unit
+    int64_t len;    // valid samples
+    int64_t lp;     // len + padding
+    int T;          // frames of this clip (<= T_out)
+};
+
+FE_HD FE_INLINE FeW2Unit fe_w2_unit(const FeWhisper2Params& p, int u) {
+    FeW2Unit t;
+    t.b = u / p.units_per_clip;
+    t.t0 = (u % p.units_per_clip) * FeW2Cfg::FT;
+    t.len = fe_clip_len(p.lengths, t.b, p.L);
+    t.lp = t.len + p.padding;
+    int64_t T = t.lp / FeW2Cfg::HOP;
+    t.T = (int)(T < p.T_out ? T : p.T_out);
+    return t;
+}
+
+// ---------------------------------------------------------------- loader
+// ltid in [0, NLT).  Four consecutive samples of both segments per step; the fast path (unit fully inside
+// the clip, 16B-aligned rows) issues U independent 128-bit loads per segment before the first store.
+FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, float* sm, int ltid, int u) {
+    typedef FeW2Cfg C;
+    const FeW2Unit t = fe_w2_unit(p, u);
+    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
+    const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
+    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
+    constexpr int NQ = C::RT / 4;  // 1340 groups of 4 samples
+    const bool interior = (p.vec_ok & 1) && g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
+    if (interior) {
+        const float4* __restrict__ xa = reinterpret_cast<const float4*>(x + g0);
+        const float4* __restrict__ xb = reinterpret_cast<const float4*>(x + g0 + C::SEG);
+        constexpr int U = 7;
+        for (int q0 = ltid; q0 < NQ; q0 += C::NLT * U) {
+            float4 a[U], b[U];
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int q = q0 + j * C::NLT;
+                if (q < NQ) { a[j] = xa[q]; b[j] = xb[q]; }
+            }
+#pragma unroll
+            for (int j = 0; j < U; ++j) {
+                const int q = q0 + j * C::NLT;
+                if (q < NQ) {
+                    fe2* d = w + 4 * q + (4 * q) / C::HOP;
+                    d[0] = fe_mk2(a[j].x, b[j].x); d[1] = fe_mk2(a[j].y, b[j].y);
+                    d[2] = fe_mk2(a[j].z, b[j].z); d[3] = fe_mk2(a[j].w, b[j].w);
+                }
+            }
+        }
+    } else {
+        for (int q = ltid; q < NQ; q += C::NLT) {
+            const int64_t g = g0 + 4 * q;
+            fe2* d = w + 4 * q + (4 * q) / C::HOP;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                d[j] = fe_mk2(fe_fetch_reflect(x, g + j, t.len, t.lp), fe_fetch_reflect(x, g + C::SEG + j, t.len, t.lp));
+        }
+    }
+}
+
+// ---------------------------------------------------------------- phase A
+FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2) {
+    typedef FeW2Cfg C;
+    const fe2* __restrict__ s = reinterpret_cast<const fe2*>(sm) + C::LS * lane + n2;
+    const float* __restrict__ tab = fe_w2_tab + 40 * n2;
+    fe2 x[C::R];
+#pragma unroll
+    for (int n1 = 0; n1 < C::R; ++n1) {
+        // sample n = 20*n1 + n2 of this lane's frames; (20*n1 + n2) / 160 == n1 / 8 for every n2 < 20
+        x[n1] = fe_mulc(tab[n1], s[C::R * n1 + n1 / (C::HOP / C::R)]);
+    }
+    fe2 yr[11], yi[11];
+    fe_rdft20_h11(x, yr, yi);
+    float4* __restrict__ a = reinterpret_cast<float4*>(sm + C::OFF_A) + C::FS * lane + n2;
+    a[0] = make_float4(yr[0].x, yr[0].y, 0.0f, 0.0f);
+#pragma unroll
+    for (int k1 = 1; k1 < 10; ++k1) {
+        const float wr = tab[18 + 2 * k1], wi = tab[19 + 2 * k1];
+        const fe2 re = fe_fnmac(wi, yi[k1], fe_mulc(wr, yr[k1]));  // wr*yr - wi*yi
+        const fe2 im = fe_fmac(wi, yr[k1], fe_mulc(wr, yi[k1]));   // wr*yi + wi*yr
+        a[C::R * k1] = make_float4(re.x, re.y, im.x, im.y);
+    }
+    {
+        const fe2 re = fe_mulc(tab[38], yr[10]), im = fe_mulc(tab[39], yr[10]);
+        a[C::R * 10] = make_float4(re.x, re.y, im.x, im.y);
+    }
+}
+
+// ctid in [0, NCT)
+FE_HD FE_INLINE void fe_w2_phase_a(float* sm, int ctid) {
+    typedef FeW2Cfg C;
+    const int lane = ctid & 31, warp = ctid >> 5;
+    for (int n2 = warp; n2 < C::R; n2 += C::NCW) fe_w2_stage_a(sm, lane, n2);
+}
+
+// ---------------------------------------------------------------- phase B
+// Power of bin k (k < 200) of this lane's pair lives, after phase B, in the lane's A row as a float2:
+//   kk = k % 20, j = k / 20;  kk <= 10: slot (kk, j), low half;  kk > 10: slot (20 - kk, j), high half
+// and the half index is XORed with bit 3 of the lane (so that 64-bit accesses at a lane stride of an odd
+// number of 16-byte slots stay conflict-free): low half -> pe[2*q], high half -> po[2*q], q = 20*row + j.
+struct FeW2P {
+    fe2* pe;
+    fe2* po;
+};
+FE_HD FE_INLINE FeW2P fe_w2_prow(float* sm, int lane) {
+    typedef FeW2Cfg C;
+    fe2* base = reinterpret_cast<fe2*>(sm + C::OFF_A) + 2 * C::FS * lane;
+    const int s = (lane >> 3) & 1;
+    FeW2P r;
+    r.pe = base + s;
+    r.po = base + 1 - s;
+    return r;
+}
+
+FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1) {
+    typedef FeW2Cfg C;
+    const float4* __restrict__ a = reinterpret_cast<const float4*>(sm + C::OFF_A) + C::FS * lane + C::R * k1;
+    fe2 xr[20], xi[20], yr[20], yi[20];
+#pragma unroll
+    for (int n2 = 0; n2 < 20; ++n2) {
+        const float4 v = a[n2];
+        xr[n2] = fe_mk2(v.x, v.y); xi[n2] = fe_mk2(v.z, v.w);
+    }
+    fe_cdft20(xr, xi, yr, yi);
+    const FeW2P P = fe_w2_prow(sm, lane);
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+        P.pe[2 * (C::R * k1 + j)] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));                      // bin k1 + 20*j
+        P.po[2 * (C::R * k1 + j)] = fe_fma(yr[19 - j], yr[19 - j], fe_mul(yi[19 - j], yi[19 - j]));  // bin (20-k1) + 20*j
+    }
+}
+
+FE_HD FE_INLINE void fe_w2_stage_b_light(float* sm, int lane) {
+    typedef FeW2Cfg C;
+    const float4* __restrict__ a = reinterpret_cast<const float4*>(sm + C::OFF_A) + C::FS * lane;
+    const FeW2P P = fe_w2_prow(sm, lane);
+    {   // k1 = 0: real input, bins 20*j, j = 0..9
+        fe2 xr[20], yr[10], yi[10];
+#pragma unroll
+        for (int n2 = 0; n2 < 20; ++n2) {
+            const float4 v = a[n2];
+            xr[n2] = fe_mk2(v.x, v.y);
+        }
+        yi[0] = fe_zero<fe2>();
+        fe_rdft20_h10(xr, yr, yi);
+#pragma unroll
+        for (int j = 0; j < 10; ++j) P.pe[2 * j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
+    }
+    {   // k1 = 10: bins 10 + 20*j, j = 0..9 (j >= 10 only repeats them mirrored)
+        fe2 xr[20], xi[20], yr[10], yi[10];
+#pragma unroll
+        for (int n2 = 0; n2 < 20; ++n2) {
+            const float4 v = a[C::R * 10 + n2];
+            xr[n2] = fe_mk2(v.x, v.y); xi[n2] = fe_mk2(v.z, v.w);
+        }
+        fe_cdft20_h10(xr, xi, yr, yi);
+#pragma unroll
+        for (int j = 0; j < 10; ++j) P.pe[2 * (C::R * 10 + j)] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
+    }
+}
+
+FE_HD FE_INLINE void fe_w2_phase_b(float* sm, int ctid) {
+    const int lane = ctid & 31, warp = ctid >> 5;
+    if (warp == 0) fe_w2_stage_b_light(sm, lane);
+    else fe_w2_stage_b_heavy(sm, lane, warp);
+}
+
+// ---------------------------------------------------------------- phase M
+FE_HD FE_INLINE float fe_max3(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+#else
+    return fmaxf(fmaxf(a, b), c);
+#endif
+}
+FE_HD FE_INLINE float fe_min3(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+#else
+    return fminf(fminf(a, b), c);
+#endif
+}
+
+// Writes y = (log10(max(mel, 1e-10)) + 4) / 4 for the live frames of the pair and returns this thread's
+// (min, max) over them; dead frames carry NaN through min/max (max.f32 / min.f32 return the other operand).
+template <int NMELS>
+FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, float* sm, int ctid, int u) {
+    typedef FeW2Cfg C;
+    const int lane = ctid & 31, warp = ctid >> 5;
+    const FeW2Unit t = fe_w2_unit(p, u);
+    const int fa = t.t0 + lane, fb = fa + C::LANES;
+    const bool la = fa < t.T, lb = fb < t.T;
+    float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + fa;
+    const int64_t rs = p.T_out;
+    const FeW2P P = fe_w2_prow(sm, lane);
+    union { unsigned u; float f; } qnan;
+    qnan.u = 0x7fc00000u;
+    const fe2 one = fe_mk2(la ? 1.0f : qnan.f, lb ? 1.0f : qnan.f);
+    float mn = 3.0e38f, mx = -3.0e38f;
+    auto ld = [&](int k) -> fe2 {
+        const int kk = k % C::R, j = k / C::R;
+        return (kk <= 10) ? P.pe[2 * (C::R * kk + j)] : P.po[2 * (C::R * (C::R - kk) + j)];
+    };
+    auto emit = [&](int m, fe2 v) {
+        const fe2 lg = fe_mk2(FE_LOG2(fmaxf(v.x, 1e-10f)), FE_LOG2(fmaxf(v.y, 1e-10f)));
+        const fe2 y = fe_fmac(C::LOG_SCALE, lg, one);   // (log10(v) + 4) / 4
+        if (la) o[(int64_t)m * rs] = y.x;
+        if (lb) o[(int64_t)m * rs + C::LANES] = y.y;
+        mx = fe_max3(mx, y.x, y.y);
+        mn = fe_min3(mn, y.x, y.y);
+    };
+    constexpr int NCH = (NMELS == 80) ? FE_MELPROJ_W80_NCHUNK : FE_MELPROJ_W128_NCHUNK;
+    for (int c = warp; c < NCH; c += C::NCW) {
+        if (NMELS == 80) fe_melproj_w80<fe2>(c, ld, emit);
+        else fe_melproj_w128<fe2>(c, ld, emit);
+    }
+    return fe_mk2(mn, mx);
+}
+
+// ---------------------------------------------------------------- fix-up (second kernel)
+// Threshold in the (x + 4) / 4 domain: (max(x, xmax - 8) + 4) / 4 == max(y, ymax - 2).
+FE_HD FE_INLINE float fe_w2_threshold(float ymax) { return ymax - 2.0f; }

@@ -271,10 +271,48 @@ def _flit(c):
     return s + "f"
 
 
-def emit_body(d, outs, in_expr, out_stmt, indent="    "):
+def emit_body(d, outs, in_expr, out_stmt, indent="    ", vtype="V"):
     """in_expr: name -> C expression; out_stmt: (index, expr_string) -> statement string.
-    outs: list of Dag values.  Returns C statements."""
+    outs: list of Dag values.  Returns C statements over the value type `vtype` (float or the packed
+    two-frame type fe2) written with the fe_add / fe_sub / fe_mulc / fe_fmac / fe_fmsc / fe_fnmac / fe_neg
+    helpers of fe_common.h.  A product with exactly one consumer that is an add/sub is contracted into
+    that consumer as an explicit fused multiply-add (the packed intrinsics are never contracted by nvcc)."""
     live = _live(d, outs)
+    uses = {i: 0 for i in live}
+    for i in live:
+        nd = d.nodes[i]
+        if nd[0] in ("add", "sub"):
+            uses[nd[1]] += 1
+            uses[nd[2]] += 1
+        elif nd[0] == "mul":
+            uses[nd[2]] += 1
+    for o in outs:
+        if o is not None:
+            uses[o[1]] += 1
+
+    def fusable(j):
+        return d.nodes[j][0] == "mul" and uses[j] == 1
+
+    fused = set()
+    plan = {}
+    for i in live:
+        nd = d.nodes[i]
+        if nd[0] == "add":
+            a, b = nd[1], nd[2]
+            if fusable(b) and b not in fused:
+                plan[i] = ("fmac", b, a)
+                fused.add(b)
+            elif fusable(a) and a not in fused:
+                plan[i] = ("fmac", a, b)
+                fused.add(a)
+        elif nd[0] == "sub":
+            a, b = nd[1], nd[2]
+            if fusable(b) and b not in fused:
+                plan[i] = ("fnmac", b, a)      # a - c*x
+                fused.add(b)
+            elif fusable(a) and a not in fused:
+                plan[i] = ("fmsc", a, b)       # c*x - b
+                fused.add(a)
     lines = []
     name = {}
     for i in live:
@@ -282,19 +320,25 @@ def emit_body(d, outs, in_expr, out_stmt, indent="    "):
         if nd[0] == "in":
             name[i] = in_expr(nd[1])
             continue
+        if i in fused:
+            continue
         v = f"t{i}"
         name[i] = v
-        if nd[0] == "add":
-            lines.append(f"{indent}const float {v} = {name[nd[1]]} + {name[nd[2]]};")
+        if i in plan:
+            op, m, other = plan[i]
+            mn = d.nodes[m]
+            lines.append(f"{indent}const {vtype} {v} = fe_{op}({_flit(mn[1])}, {name[mn[2]]}, {name[other]});")
+        elif nd[0] == "add":
+            lines.append(f"{indent}const {vtype} {v} = fe_add({name[nd[1]]}, {name[nd[2]]});")
         elif nd[0] == "sub":
-            lines.append(f"{indent}const float {v} = {name[nd[1]]} - {name[nd[2]]};")
+            lines.append(f"{indent}const {vtype} {v} = fe_sub({name[nd[1]]}, {name[nd[2]]});")
         else:
-            lines.append(f"{indent}const float {v} = {_flit(nd[1])} * {name[nd[2]]};")
+            lines.append(f"{indent}const {vtype} {v} = fe_mulc({_flit(nd[1])}, {name[nd[2]]});")
     for k, o in enumerate(outs):
         if o is None:
-            e = "0.0f"
+            e = f"fe_zero<{vtype}>()"
         else:
-            e = name[o[1]] if o[0] > 0 else f"-{name[o[1]]}"
+            e = name[o[1]] if o[0] > 0 else f"fe_neg({name[o[1]]})"
         st = out_stmt(k, e)
         if st:
             lines.append(indent + st)

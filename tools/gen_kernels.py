@@ -117,11 +117,13 @@ def gen_codelet(name, n, real_in=False, nz=None, outs=None, real_out=()):
         return f"y{s[0]}[{s[1]}] = {e};"
 
     body = g.emit_body(d, vals, in_expr, out_stmt)
-    args = "const float* __restrict__ xr, " + ("" if real_in else "const float* __restrict__ xi, ")
-    args += "float* __restrict__ yr, float* __restrict__ yi"
+    n_fma = body.count("fe_fmac(") + body.count("fe_fmsc(") + body.count("fe_fnmac(")
+    n_ops = body.count("= fe_")
+    args = "const V* __restrict__ xr, " + ("" if real_in else "const V* __restrict__ xi, ")
+    args += "V* __restrict__ yr, V* __restrict__ yi"
     hdr = (f"// DFT-{n} {'real' if real_in else 'complex'} input ({nz} non-zero), outputs k={outs[0]}..{outs[-1]}"
-           f"  [{ops['add'] + ops['sub']} add/sub, {ops['mul']} mul before FMA contraction]\n")
-    return hdr + f"FE_HD FE_INLINE void {name}({args}) {{\n{body}\n}}\n"
+           f"  [{ops['add'] + ops['sub']} add/sub + {ops['mul']} mul -> {n_ops} instructions, {n_fma} of them fused]\n")
+    return hdr + f"template <class V>\nFE_HD FE_INLINE void {name}({args}) {{\n{body}\n}}\n"
 
 
 # ------------------------------------------------------------------ mel projection
@@ -166,9 +168,9 @@ def partition(costs, nch):
 
 
 def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
-    """template<int PS, class Emit> void name(int chunk, const float* P, Emit&& emit)
-    P points at this lane's column: bin k lives at P[k*PS].  emit(m, value) is called once per
-    filter of the chunk."""
+    """template<class V, class Load, class Emit> void name(int chunk, Load&& ld, Emit&& emit)
+    ld(k) returns this lane's power (V = float, or fe2 for a frame pair) at FFT bin k.  emit(m, value)
+    is called once per filter of the chunk."""
     n_mels = filt.shape[0]
     assert not np.any(filt[:, max_bin + 1:]), "filter weight beyond max_bin"
     costs = []
@@ -178,8 +180,8 @@ def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
     bounds = partition(costs, nch)
     out = [f"// sparse mel projection, {n_mels} filters, {int(np.count_nonzero(filt))} non-zeros, {len(bounds)} chunks",
            f"#define {name.upper()}_NCHUNK {len(bounds)}",
-           "template <int PS, class Emit>",
-           f"FE_HD FE_INLINE void {name}(int chunk, const float* __restrict__ P, Emit&& emit) {{",
+           "template <class V, class Load, class Emit>",
+           f"FE_HD FE_INLINE void {name}(int chunk, Load&& ld, Emit&& emit) {{",
            "    switch (chunk) {"]
     for c, (a, b) in enumerate(bounds):
         out.append(f"    case {c}: {{  // filters {a}..{b - 1}")
@@ -187,17 +189,17 @@ def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
         body = []
         decl = set()
         for k in bins:
-            body.append(f"        {{ const float p = P[{k} * PS];")
+            body.append(f"        {{ const V p = ld({k});")
             for m in range(a, b):
                 w = filt[m, k]
                 if w != 0:
                     if m in decl:
-                        body.append(f"          a{m} = fmaf(p, {flit(w)}, a{m});")
+                        body.append(f"          a{m} = fe_fmac({flit(w)}, p, a{m});")
                     else:
-                        body.append(f"          a{m} = p * {flit(w)};")
+                        body.append(f"          a{m} = fe_mulc({flit(w)}, p);")
                         decl.add(m)
             body.append("        }")
-        out.append("        float " + ", ".join(f"a{m} = 0.0f" for m in range(a, b)) + ";")
+        out.append("        V " + ", ".join(f"a{m} = fe_zero<V>()" for m in range(a, b)) + ";")
         out.extend(body)
         for m in range(a, b):
             out.append(f"        emit({m}, a{m});")
@@ -251,6 +253,16 @@ def main():
     tb.append(emit_array("fe_win_cosy", 0.5 - 0.5 * np.cos(2 * np.pi * n / 1920.0)))
     tb.append("// Whisper stage-A twiddles W_400^(n2*k1), [n2 = 0..19][k1 = 0..10] (re, im)")
     tb.append(emit_array("fe_tw_whisper", twiddle_table(400, 20, 11)))
+    # packed Whisper kernel: per n2 one row of 40 floats = window w[20*n1 + n2] (n1 = 0..19), then the
+    # stage-A twiddles W_400^(n2*k1) as (re, im) for k1 = 1..10
+    w400 = 0.5 - 0.5 * np.cos(2 * np.pi * np.arange(400, dtype=np.float64) / 400.0)
+    tw = twiddle_table(400, 20, 11)
+    rows = np.zeros((20, 40), dtype=np.float64)
+    for n2 in range(20):
+        rows[n2, :20] = w400[20 * np.arange(20) + n2]
+        rows[n2, 20:] = tw[n2, 1:11].reshape(-1)
+    tb.append("// Whisper (frame-pair kernel) stage-A constants [n2][window(n1 = 0..19) | W_400^(n2*k1) (re, im), k1 = 1..10]")
+    tb.append(emit_array("fe_w2_tab", rows))
     tb.append("// kaldi stage-A twiddles W_512^(n2*k1), [n2 = 0..15][k1 = 0..16]")
     tb.append(emit_array("fe_tw_kaldi", twiddle_table(512, 16, 17)))
     tb.append("// CosyVoice stage-A twiddles W_1920^(m*k1), [m = 0..119][k1 = 0..8]")
