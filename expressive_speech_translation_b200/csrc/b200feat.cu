@@ -32,56 +32,60 @@ static __device__ __forceinline__ void fe_bar_arrive(int id, int count) {
 }
 
 // Persistent, warp-specialised: NLW loader warps run one unit ahead of NCW compute warps.
-//   loader : [wait W_FREE] fill W(u) -> arrive W_FULL
+//   loader : [wait W_FREE] fill W(u), publish the unit's (clip, first frame, frame count) -> arrive W_FULL
 //   compute: wait W_FULL -> phase A -> arrive W_FREE -> B -> M -> publish (min, max) of the unit
 template <int NMELS>
 __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhisper2Params p) {
     typedef FeW2Cfg C;
     extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x;
-    int* keys = reinterpret_cast<int*>(sm + C::OFF_MISC);  // [0] max key, [1] min key (negated order)
-    if (tid == 0) { keys[0] = FE_KEY_INIT; keys[1] = FE_KEY_INIT; }
+    const int lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
+    int* misc = reinterpret_cast<int*>(sm + C::OFF_MISC);     // [0] max key, [1] key of -min, [4 + 4*par ..] unit info
+    if (tid == 0) { misc[0] = FE_KEY_INIT; misc[1] = FE_KEY_INIT; }
     __syncthreads();
-    if (tid >= C::NCT) {
+    if (warp >= C::NCW) {
         const int ltid = tid - C::NCT;
-        bool first = true;
-        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
-            if (!first) fe_bar_sync(FE_BAR_W_FREE, C::NT);
-            first = false;
+        int par = 0;
+        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1) {
+            if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
             const FeW2Unit t = fe_w2_unit(p, u);
-            if (t.t0 < t.T) fe_w2_phase_load(p, sm, ltid, u);
+            if (t.t0 < t.T) fe_w2_phase_load(p, t, sm, ltid);
+            if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
             fe_bar_arrive(FE_BAR_W_FULL, C::NT);
         }
         return;
     }
-    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
-        const FeW2Unit t = fe_w2_unit(p, u);
-        const bool live = t.t0 < t.T;
+    int par = 0;
+    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1) {
         const bool more = u + (int)gridDim.x < p.total_units;
         fe_bar_sync(FE_BAR_W_FULL, C::NT);
-        if (live) fe_w2_phase_a(sm, tid);
+        FeW2Unit t;
+        t.b = misc[4 + 4 * par]; t.t0 = misc[5 + 4 * par]; t.T = misc[6 + 4 * par];
+        const bool live = t.t0 < t.T;
+        if (live) fe_w2_phase_a(sm, lane, warp);
         if (more) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
         if (!live) {
             if (tid == 0) p.unit_minmax[u] = make_float2(3.0e38f, -3.0e38f);
             continue;
         }
         fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
-        fe_w2_phase_b(sm, tid);
+        fe_w2_phase_b(sm, lane, warp);
         fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
-        const fe2 mm = fe_w2_phase_mel<NMELS>(p, sm, tid, u);
+        const fe2 mm = fe_w2_phase_mel<NMELS>(p, t, sm, lane, warp);
         int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
             kmin = max(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
         }
-        if ((tid & 31) == 0) { atomicMax(keys + 0, kmax); atomicMax(keys + 1, kmin); }
+        if (lane == 0) { atomicMax(misc + 0, kmax); atomicMax(misc + 1, kmin); }
         fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
         if (tid == 0) {
-            const float ymax = fe_key_float(keys[0]), ymin = -fe_key_float(keys[1]);
+            const float ymax = fe_key_float(misc[0]), ymin = -fe_key_float(misc[1]);
             p.unit_minmax[u] = make_float2(ymin, ymax);
-            atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b), keys[0]);
-            keys[0] = FE_KEY_INIT; keys[1] = FE_KEY_INIT;
+            atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b), misc[0]);
+            misc[0] = FE_KEY_INIT; misc[1] = FE_KEY_INIT;
         }
     }
 }
@@ -354,6 +358,7 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
     if (B == 0 || T_out == 0) return 0;
     if (int rc = check_device_arch()) return rc;
     if ((int64_t)B * units > 0x7fffffff) return fail(B200FEAT_EINVAL, "whisper_logmel: batch too large");
+    if (T_out >= (1 << 24)) return fail(B200FEAT_EINVAL, "whisper_logmel: T_out %lld >= 2^24", (long long)T_out);
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
     int dev = 0;
     FE_CUDA(cudaGetDevice(&dev));

@@ -16,15 +16,17 @@
 //                  slot per 160 samples (lane stride 161 pairs: conflict-free 64-bit accesses); reflect /
 //                  zero padding resolved here.  Runs one unit ahead of the compute warps.
 //   phase A      : 20 tasks (n2); real radix-20 DFT over n1 (n = 20*n1 + n2) with the Hann window fused into
-//                  the loads, Hermitian half k1 = 0..10, times W_400^(n2*k1)  -> A[lane][k1][n2] (re2, im2)
-//   phase B      : 10 tasks; k1 = 1..9: complex radix-20 DFT over n2, |X|^2 of bins k1 + 20*j and (mirrored)
-//                  (20-k1) + 20*j written IN PLACE over the task's own A row; task 0 does k1 = 0 and k1 = 10.
+//                  the loads, Hermitian half k1 = 0..10, times W_400^(n2*k1)  -> Ar/Ai[lane][k1][n2] (pairs)
+//   phase B      : 11 tasks; k1 = 1..9: complex radix-20 DFT over n2, |X|^2 of bins k1 + 20*j and (mirrored)
+//                  (20-k1) + 20*j written IN PLACE over the task's own row of the real plane; k1 = 0 (real
+//                  input) and k1 = 10 (self-mirrored) are two lighter tasks.
 //   phase M      : unrolled sparse mel projection (immediates), log10, (x + 4) / 4, coalesced stores, running
 //                  min / max of the unit.
-// The dynamic-range clamp max(x, max - 8) needs the per-clip (or per-call) maximum: the kernel publishes the
-// maximum (atomicMax) and each unit's minimum; a second, tiny kernel re-touches only the units whose minimum
-// lies below max - 8 (none for noise-like audio, the silent stretches for speech) and zero-fills frames past
-// a ragged clip's end.  In the common case every output makes exactly one trip to HBM.
+// The 1e-10 floor and the dynamic-range clamp max(x, max - 8) need the per-clip (or per-call) maximum: the
+// kernel publishes the maximum (atomicMax) and each unit's minimum; a second, tiny kernel re-touches only the
+// units whose minimum lies below the threshold (none for noise-like audio, the silent stretches for speech)
+// and zero-fills frames past a ragged clip's end.  In the common case every output makes exactly one trip
+// to HBM.
 #pragma once
 #include "fe_common.h"
 
@@ -51,32 +53,33 @@ struct FeW2Cfg {
     static constexpr int N = 400, HOP = 160, PADL = 200, R = 20;
     static constexpr int LANES = 32, FT = 64;            // frame pairs / frames per unit
     static constexpr int SEG = LANES * HOP;              // sample distance between the frames of a pair (5120)
-    static constexpr int NCW = 10, NLW = 2;              // compute / loader warps
+    static constexpr int NCW = 12, NLW = 2;              // compute / loader warps
     static constexpr int NCT = NCW * 32, NLT = NLW * 32, NT = NCT + NLT;
     static constexpr int RT = (LANES - 1) * HOP + N;     // samples per segment of a unit (5360)
     static constexpr int LS = HOP + 1;                   // lane stride in W (pairs)
-    static constexpr int SW = RT + RT / HOP + 3;         // padded W (pairs), multiple of 2 -> A is 16B-aligned
-    static constexpr int FS = 221;                       // float4 slots per lane in A (11*20 -> odd)
-    static constexpr int OFF_A = SW * 2;                 // in floats
-    static constexpr int OFF_MISC = OFF_A + LANES * FS * 4;
-    static constexpr int SMEM_FLOATS = OFF_MISC + 8;
+    static constexpr int SW = RT + RT / HOP + 3;         // padded W (pairs)
+    static constexpr int FS = 221;                       // pairs per lane in each A plane (11*20 + 1 -> odd)
+    static constexpr int OFF_AR = SW * 2;                // in floats: real plane (later: the power spectrum)
+    static constexpr int OFF_AI = OFF_AR + LANES * FS * 2;   // imaginary plane
+    static constexpr int OFF_MISC = OFF_AI + LANES * FS * 2; // ints: [0] max key [1] min key [4..7], [8..11] unit info
+    static constexpr int SMEM_FLOATS = OFF_MISC + 16;
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
     static constexpr float LOG_SCALE = 0.07525749891599530f;  // log10(2) / 4
+    static constexpr float Y_FLOOR = -1.5f;                   // (log10(1e-10) + 4) / 4
 };
-static_assert(FeW2Cfg::SW % 2 == 0, "A must start 16B-aligned");
 
 struct FeW2Unit {
     int b;          // clip
     int t0;         // first frame of the unit
+    int T;          // frames of this clip (<= T_out)
     int64_t len;    // valid samples
     int64_t lp;     // len + padding
-    int T;          // frames of this clip (<= T_out)
 };
 
 FE_HD FE_INLINE FeW2Unit fe_w2_unit(const FeWhisper2Params& p, int u) {
     FeW2Unit t;
     t.b = u / p.units_per_clip;
-    t.t0 = (u % p.units_per_clip) * FeW2Cfg::FT;
+    t.t0 = (u - t.b * p.units_per_clip) * FeW2Cfg::FT;
     t.len = fe_clip_len(p.lengths, t.b, p.L);
     t.lp = t.len + p.padding;
     int64_t T = t.lp / FeW2Cfg::HOP;
@@ -87,18 +90,19 @@ FE_HD FE_INLINE FeW2Unit fe_w2_unit(const FeWhisper2Params& p, int u) {
 // ---------------------------------------------------------------- loader
 // ltid in [0, NLT).  Four consecutive samples of both segments per step; the fast path (unit fully inside
 // the clip, 16B-aligned rows) issues U independent 128-bit loads per segment before the first store.
-FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, float* sm, int ltid, int u) {
+FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
     typedef FeW2Cfg C;
-    const FeW2Unit t = fe_w2_unit(p, u);
     const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
     const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
     fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
-    constexpr int NQ = C::RT / 4;  // 1340 groups of 4 samples
+    constexpr int NQ = C::RT / 4;        // 1340 groups of 4 samples
+    constexpr int QPB = C::HOP / 4;      // 40 groups per 160-sample block (one pad slot after each)
     const bool interior = (p.vec_ok & 1) && g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
     if (interior) {
         const float4* __restrict__ xa = reinterpret_cast<const float4*>(x + g0);
-        const float4* __restrict__ xb = reinterpret_cast<const float4*>(x + g0 + C::SEG);
+        const float4* __restrict__ xb = xa + C::SEG / 4;
         constexpr int U = 7;
+#pragma unroll 1
         for (int q0 = ltid; q0 < NQ; q0 += C::NLT * U) {
             float4 a[U], b[U];
 #pragma unroll
@@ -108,9 +112,9 @@ FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, float* sm, int 
             }
 #pragma unroll
             for (int j = 0; j < U; ++j) {
-                const int q = q0 + j * C::NLT;
-                if (q < NQ) {
-                    fe2* d = w + 4 * q + (4 * q) / C::HOP;
+                const unsigned q = (unsigned)(q0 + j * C::NLT);
+                if (q < (unsigned)NQ) {
+                    fe2* d = w + 4u * q + q / (unsigned)QPB;
                     d[0] = fe_mk2(a[j].x, b[j].x); d[1] = fe_mk2(a[j].y, b[j].y);
                     d[2] = fe_mk2(a[j].z, b[j].z); d[3] = fe_mk2(a[j].w, b[j].w);
                 }
@@ -119,7 +123,7 @@ FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, float* sm, int 
     } else {
         for (int q = ltid; q < NQ; q += C::NLT) {
             const int64_t g = g0 + 4 * q;
-            fe2* d = w + 4 * q + (4 * q) / C::HOP;
+            fe2* d = w + 4 * q + q / QPB;
 #pragma unroll
             for (int j = 0; j < 4; ++j)
                 d[j] = fe_mk2(fe_fetch_reflect(x, g + j, t.len, t.lp), fe_fetch_reflect(x, g + C::SEG + j, t.len, t.lp));
@@ -128,6 +132,7 @@ FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, float* sm, int 
 }
 
 // ---------------------------------------------------------------- phase A
+// A planes: Ar[lane][20*k1 + n2], Ai[lane][20*k1 + n2] (pairs), lane stride FS (odd: conflict-free 64-bit)
 FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2) {
     typedef FeW2Cfg C;
     const fe2* __restrict__ s = reinterpret_cast<const fe2*>(sm) + C::LS * lane + n2;
@@ -140,98 +145,72 @@ FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2) {
     }
     fe2 yr[11], yi[11];
     fe_rdft20_h11(x, yr, yi);
-    float4* __restrict__ a = reinterpret_cast<float4*>(sm + C::OFF_A) + C::FS * lane + n2;
-    a[0] = make_float4(yr[0].x, yr[0].y, 0.0f, 0.0f);
+    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + n2;
+    fe2* __restrict__ ai = reinterpret_cast<fe2*>(sm + C::OFF_AI) + C::FS * lane + n2;
+    ar[0] = yr[0];
 #pragma unroll
     for (int k1 = 1; k1 < 10; ++k1) {
         const float wr = tab[18 + 2 * k1], wi = tab[19 + 2 * k1];
-        const fe2 re = fe_fnmac(wi, yi[k1], fe_mulc(wr, yr[k1]));  // wr*yr - wi*yi
-        const fe2 im = fe_fmac(wi, yr[k1], fe_mulc(wr, yi[k1]));   // wr*yi + wi*yr
-        a[C::R * k1] = make_float4(re.x, re.y, im.x, im.y);
+        ar[C::R * k1] = fe_fnmac(wi, yi[k1], fe_mulc(wr, yr[k1]));  // wr*yr - wi*yi
+        ai[C::R * k1] = fe_fmac(wi, yr[k1], fe_mulc(wr, yi[k1]));   // wr*yi + wi*yr
     }
-    {
-        const fe2 re = fe_mulc(tab[38], yr[10]), im = fe_mulc(tab[39], yr[10]);
-        a[C::R * 10] = make_float4(re.x, re.y, im.x, im.y);
-    }
+    ar[C::R * 10] = fe_mulc(tab[38], yr[10]);
+    ai[C::R * 10] = fe_mulc(tab[39], yr[10]);
 }
 
-// ctid in [0, NCT)
-FE_HD FE_INLINE void fe_w2_phase_a(float* sm, int ctid) {
+// warp in [0, NCW): tasks n2 = warp, warp + NCW (< 20)
+FE_HD FE_INLINE void fe_w2_phase_a(float* sm, int lane, int warp) {
     typedef FeW2Cfg C;
-    const int lane = ctid & 31, warp = ctid >> 5;
     for (int n2 = warp; n2 < C::R; n2 += C::NCW) fe_w2_stage_a(sm, lane, n2);
 }
 
 // ---------------------------------------------------------------- phase B
-// Power of bin k (k < 200) of this lane's pair lives, after phase B, in the lane's A row as a float2:
-//   kk = k % 20, j = k / 20;  kk <= 10: slot (kk, j), low half;  kk > 10: slot (20 - kk, j), high half
-// and the half index is XORed with bit 3 of the lane (so that 64-bit accesses at a lane stride of an odd
-// number of 16-byte slots stay conflict-free): low half -> pe[2*q], high half -> po[2*q], q = 20*row + j.
-struct FeW2P {
-    fe2* pe;
-    fe2* po;
-};
-FE_HD FE_INLINE FeW2P fe_w2_prow(float* sm, int lane) {
-    typedef FeW2Cfg C;
-    fe2* base = reinterpret_cast<fe2*>(sm + C::OFF_A) + 2 * C::FS * lane;
-    const int s = (lane >> 3) & 1;
-    FeW2P r;
-    r.pe = base + s;
-    r.po = base + 1 - s;
-    return r;
-}
-
+// Power of bin k (k < 200) of this lane's pair lives, after phase B, in the REAL plane (in place over the
+// task's own row): kk = k % 20, j = k / 20;  kk <= 10: Ar[20*kk + j];  kk > 10: Ar[20*(20 - kk) + 10 + j].
 FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1) {
     typedef FeW2Cfg C;
-    const float4* __restrict__ a = reinterpret_cast<const float4*>(sm + C::OFF_A) + C::FS * lane + C::R * k1;
+    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * k1;
+    const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * k1;
     fe2 xr[20], xi[20], yr[20], yi[20];
 #pragma unroll
-    for (int n2 = 0; n2 < 20; ++n2) {
-        const float4 v = a[n2];
-        xr[n2] = fe_mk2(v.x, v.y); xi[n2] = fe_mk2(v.z, v.w);
-    }
+    for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
     fe_cdft20(xr, xi, yr, yi);
-    const FeW2P P = fe_w2_prow(sm, lane);
 #pragma unroll
     for (int j = 0; j < 10; ++j) {
-        P.pe[2 * (C::R * k1 + j)] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));                      // bin k1 + 20*j
-        P.po[2 * (C::R * k1 + j)] = fe_fma(yr[19 - j], yr[19 - j], fe_mul(yi[19 - j], yi[19 - j]));  // bin (20-k1) + 20*j
+        ar[j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));                           // bin k1 + 20*j
+        ar[10 + j] = fe_fma(yr[19 - j], yr[19 - j], fe_mul(yi[19 - j], yi[19 - j]));  // bin (20-k1) + 20*j
     }
 }
 
-FE_HD FE_INLINE void fe_w2_stage_b_light(float* sm, int lane) {
+FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane) {   // k1 = 0: real input, bins 20*j, j = 0..9
     typedef FeW2Cfg C;
-    const float4* __restrict__ a = reinterpret_cast<const float4*>(sm + C::OFF_A) + C::FS * lane;
-    const FeW2P P = fe_w2_prow(sm, lane);
-    {   // k1 = 0: real input, bins 20*j, j = 0..9
-        fe2 xr[20], yr[10], yi[10];
+    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane;
+    fe2 xr[20], yr[10], yi[10];
 #pragma unroll
-        for (int n2 = 0; n2 < 20; ++n2) {
-            const float4 v = a[n2];
-            xr[n2] = fe_mk2(v.x, v.y);
-        }
-        yi[0] = fe_zero<fe2>();
-        fe_rdft20_h10(xr, yr, yi);
+    for (int n2 = 0; n2 < 20; ++n2) xr[n2] = ar[n2];
+    yi[0] = fe_zero<fe2>();
+    fe_rdft20_h10(xr, yr, yi);
 #pragma unroll
-        for (int j = 0; j < 10; ++j) P.pe[2 * j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
-    }
-    {   // k1 = 10: bins 10 + 20*j, j = 0..9 (j >= 10 only repeats them mirrored)
-        fe2 xr[20], xi[20], yr[10], yi[10];
-#pragma unroll
-        for (int n2 = 0; n2 < 20; ++n2) {
-            const float4 v = a[C::R * 10 + n2];
-            xr[n2] = fe_mk2(v.x, v.y); xi[n2] = fe_mk2(v.z, v.w);
-        }
-        fe_cdft20_h10(xr, xi, yr, yi);
-#pragma unroll
-        for (int j = 0; j < 10; ++j) P.pe[2 * (C::R * 10 + j)] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
-    }
+    for (int j = 0; j < 10; ++j) ar[j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
 }
 
-FE_HD FE_INLINE void fe_w2_phase_b(float* sm, int ctid) {
-    const int lane = ctid & 31, warp = ctid >> 5;
-    if (warp == 0) fe_w2_stage_b_light(sm, lane);
-    else fe_w2_stage_b_heavy(sm, lane, warp);
+FE_HD FE_INLINE void fe_w2_stage_b_k10(float* sm, int lane) {  // k1 = 10: bins 10 + 20*j, j = 0..9
+    typedef FeW2Cfg C;
+    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * 10;
+    const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * 10;
+    fe2 xr[20], xi[20], yr[10], yi[10];
+#pragma unroll
+    for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
+    fe_cdft20_h10(xr, xi, yr, yi);
+#pragma unroll
+    for (int j = 0; j < 10; ++j) ar[j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
+}
+
+// 11 tasks: warp 0 -> k1 = 0, warps 1..9 -> k1 = warp, warp 10 -> k1 = 10, warp 11 idle
+FE_HD FE_INLINE void fe_w2_phase_b(float* sm, int lane, int warp) {
+    if (warp == 0) fe_w2_stage_b_k0(sm, lane);
+    else if (warp < 10) fe_w2_stage_b_heavy(sm, lane, warp);
+    else if (warp == 10) fe_w2_stage_b_k10(sm, lane);
 }
 
 // ---------------------------------------------------------------- phase M
@@ -253,32 +232,39 @@ FE_HD FE_INLINE float fe_min3(float a, float b, float c) {
     return fminf(fminf(a, b), c);
 #endif
 }
+// log2 without the 1e-10 floor: 0 (and flushed subnormals) -> -inf; the floor is applied with the clamp
+FE_HD FE_INLINE float fe_w2_lg2(float v) {
+#if defined(__CUDA_ARCH__)
+    return fe_lg2_ftz(v);
+#else
+    return v < 1.1754944e-38f ? -INFINITY : log2f(v);
+#endif
+}
 
-// Writes y = (log10(max(mel, 1e-10)) + 4) / 4 for the live frames of the pair and returns this thread's
-// (min, max) over them; dead frames carry NaN through min/max (max.f32 / min.f32 return the other operand).
+// Writes y = (log10(mel) + 4) / 4 for the live frames of the pair (NO floor, NO clamp: both are applied by
+// the fix-up pass, which only touches units whose minimum needs them) and returns this thread's (min, max)
+// over them; dead frames carry NaN through min/max (max.f32 / min.f32 return the non-NaN operand).
 template <int NMELS>
-FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, float* sm, int ctid, int u) {
+FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
     typedef FeW2Cfg C;
-    const int lane = ctid & 31, warp = ctid >> 5;
-    const FeW2Unit t = fe_w2_unit(p, u);
     const int fa = t.t0 + lane, fb = fa + C::LANES;
     const bool la = fa < t.T, lb = fb < t.T;
     float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + fa;
-    const int64_t rs = p.T_out;
-    const FeW2P P = fe_w2_prow(sm, lane);
+    const unsigned rs = (unsigned)p.T_out;   // host guarantees n_mels * T_out < 2^31
+    const fe2* __restrict__ P = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane;
     union { unsigned u; float f; } qnan;
     qnan.u = 0x7fc00000u;
     const fe2 one = fe_mk2(la ? 1.0f : qnan.f, lb ? 1.0f : qnan.f);
     float mn = 3.0e38f, mx = -3.0e38f;
     auto ld = [&](int k) -> fe2 {
         const int kk = k % C::R, j = k / C::R;
-        return (kk <= 10) ? P.pe[2 * (C::R * kk + j)] : P.po[2 * (C::R * (C::R - kk) + j)];
+        return (kk <= 10) ? P[C::R * kk + j] : P[C::R * (C::R - kk) + 10 + j];
     };
     auto emit = [&](int m, fe2 v) {
-        const fe2 lg = fe_mk2(FE_LOG2(fmaxf(v.x, 1e-10f)), FE_LOG2(fmaxf(v.y, 1e-10f)));
-        const fe2 y = fe_fmac(C::LOG_SCALE, lg, one);   // (log10(v) + 4) / 4
-        if (la) o[(int64_t)m * rs] = y.x;
-        if (lb) o[(int64_t)m * rs + C::LANES] = y.y;
+        const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(v.x), fe_w2_lg2(v.y)), one);   // (log10(v) + 4) / 4
+        float* q = o + (unsigned)m * rs;
+        if (la) q[0] = y.x;
+        if (lb) q[C::LANES] = y.y;
         mx = fe_max3(mx, y.x, y.y);
         mn = fe_min3(mn, y.x, y.y);
     };
@@ -291,5 +277,10 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, float* sm, int ct
 }
 
 // ---------------------------------------------------------------- fix-up (second kernel)
-// Threshold in the (x + 4) / 4 domain: (max(x, xmax - 8) + 4) / 4 == max(y, ymax - 2).
-FE_HD FE_INLINE float fe_w2_threshold(float ymax) { return ymax - 2.0f; }
+// Floor and clamp in the y = (x + 4) / 4 domain, with x = log10(mel) un-floored:
+//   (max(max(x, -10), xmax' - 8) + 4) / 4 == max(y, thr),  thr = max(-1.5, max(ymax, -1.5) - 2)
+// where xmax' is the maximum of the floored values, ymax the published maximum of the un-floored ones.
+FE_HD FE_INLINE float fe_w2_threshold(float ymax) {
+    const float ym = fmaxf(ymax, FeW2Cfg::Y_FLOOR);
+    return fmaxf(FeW2Cfg::Y_FLOOR, ym - 2.0f);
+}

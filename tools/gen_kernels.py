@@ -273,8 +273,8 @@ def main():
     w128 = slaney(16000, 400, 128, 0.0, 8000.0)
     cz = slaney(24000, 1920, 80, 0.0, 8000.0)
     kb = kaldi_banks()
-    tb.append(gen_melproj("fe_melproj_w80", w80, 10, 199))
-    tb.append(gen_melproj("fe_melproj_w128", w128, 10, 199))
+    tb.append(gen_melproj("fe_melproj_w80", w80, 12, 199, epi_cost=8))
+    tb.append(gen_melproj("fe_melproj_w128", w128, 12, 199, epi_cost=8))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     tb.append(gen_melproj("fe_melproj_cosy", cz, 16, 639))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
