@@ -232,6 +232,25 @@ FE_HD FE_INLINE float fe_min3(float a, float b, float c) {
     return fminf(fminf(a, b), c);
 #endif
 }
+// base + m * row_bytes in ONE instruction (IMAD.WIDE.U32 with the immediate m); row_bytes < 2^26
+FE_HD FE_INLINE float* fe_row_ptr(float* base, unsigned row_bytes, unsigned m) {
+#if defined(__CUDA_ARCH__)
+    float* r;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(row_bytes), "r"(m), "l"(base));
+    return r;
+#else
+    return reinterpret_cast<float*>(reinterpret_cast<char*>(base) + (size_t)row_bytes * m);
+#endif
+}
+// global stores through a pointer built by fe_row_ptr (keeps the address space: STG, not generic ST)
+template <int BYTE_OFF>
+FE_HD FE_INLINE void fe_stg(float* q, float v) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.f32 [%0+%1], %2;" ::"l"(q), "n"(BYTE_OFF), "f"(v) : "memory");
+#else
+    *reinterpret_cast<float*>(reinterpret_cast<char*>(q) + BYTE_OFF) = v;
+#endif
+}
 // log2 without the 1e-10 floor: 0 (and flushed subnormals) -> -inf; the floor is applied with the clamp
 FE_HD FE_INLINE float fe_w2_lg2(float v) {
 #if defined(__CUDA_ARCH__)
@@ -250,19 +269,23 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     const int fa = t.t0 + lane, fb = fa + C::LANES;
     const bool la = fa < t.T, lb = fb < t.T;
     float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + fa;
-    const unsigned rs = (unsigned)p.T_out;   // host guarantees n_mels * T_out < 2^31
+    const unsigned rs4 = (unsigned)p.T_out * 4u;   // row pitch in bytes; the host guarantees T_out < 2^24
     const fe2* __restrict__ P = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane;
     union { unsigned u; float f; } qnan;
     qnan.u = 0x7fc00000u;
     const fe2 one = fe_mk2(la ? 1.0f : qnan.f, lb ? 1.0f : qnan.f);
     float mn = 3.0e38f, mx = -3.0e38f;
+    float* q = o;
+    int qm = 0;
     auto ld = [&](int k) -> fe2 {
         const int kk = k % C::R, j = k / C::R;
         return (kk <= 10) ? P[C::R * kk + j] : P[C::R * (C::R - kk) + 10 + j];
     };
     auto emit = [&](int m, fe2 v) {
         const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(v.x), fe_w2_lg2(v.y)), one);   // (log10(v) + 4) / 4
-        float* q = o + (unsigned)m * rs;
+        // rows of a chunk are consecutive: after the first one this is a 64-bit add of the row pitch
+        q = reinterpret_cast<float*>(reinterpret_cast<char*>(q) + (size_t)rs4 * (unsigned)(m - qm));
+        qm = m;
         if (la) q[0] = y.x;
         if (lb) q[C::LANES] = y.y;
         mx = fe_max3(mx, y.x, y.y);
