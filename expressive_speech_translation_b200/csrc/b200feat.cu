@@ -47,12 +47,23 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
     if (warp >= C::NCW) {
         const int ltid = tid - C::NCT;
         int par = 0;
+        FeW2Stage stage;
+        FeW2Unit t = fe_w2_unit(p, blockIdx.x);
+        bool live = t.t0 < t.T, fast = live && fe_w2_interior(p, t);
+        if (fast) fe_w2_load_issue(p, t, ltid, stage);
         for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1) {
             if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
-            const FeW2Unit t = fe_w2_unit(p, u);
-            if (t.t0 < t.T) fe_w2_phase_load(p, t, sm, ltid);
+            if (fast) fe_w2_load_store(sm, ltid, stage);
+            else if (live) fe_w2_load_edge(p, t, sm, ltid);
             if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
             fe_bar_arrive(FE_BAR_W_FULL, C::NT);
+            const int un = u + (int)gridDim.x;
+            if (un < p.total_units) {   // next unit: loads go in flight now, stores wait for W_FREE
+                t = fe_w2_unit(p, un);
+                live = t.t0 < t.T;
+                fast = live && fe_w2_interior(p, t);
+                if (fast) fe_w2_load_issue(p, t, ltid, stage);
+            }
         }
         return;
     }

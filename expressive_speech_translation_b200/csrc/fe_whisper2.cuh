@@ -53,7 +53,7 @@ struct FeW2Cfg {
     static constexpr int N = 400, HOP = 160, PADL = 200, R = 20;
     static constexpr int LANES = 32, FT = 64;            // frame pairs / frames per unit
     static constexpr int SEG = LANES * HOP;              // sample distance between the frames of a pair (5120)
-    static constexpr int NCW = 12, NLW = 2;              // compute / loader warps
+    static constexpr int NCW = 12, NLW = 4;              // compute / loader warps
     static constexpr int NCT = NCW * 32, NLT = NLW * 32, NT = NCT + NLT;
     static constexpr int RT = (LANES - 1) * HOP + N;     // samples per segment of a unit (5360)
     static constexpr int LS = HOP + 1;                   // lane stride in W (pairs)
@@ -88,46 +88,64 @@ FE_HD FE_INLINE FeW2Unit fe_w2_unit(const FeWhisper2Params& p, int u) {
 }
 
 // ---------------------------------------------------------------- loader
-// ltid in [0, NLT).  Four consecutive samples of both segments per step; the fast path (unit fully inside
-// the clip, 16B-aligned rows) issues U independent 128-bit loads per segment before the first store.
-FE_HD FE_INLINE void fe_w2_phase_load(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
+// ltid in [0, NLT).  Four consecutive samples of both segments per step.  Interior units (fully inside the
+// clip, 16B-aligned rows) are fetched in two halves: fe_w2_load_issue puts every 128-bit load of the unit in
+// flight at once (it runs BEFORE the loader waits for W to be released, so the HBM latency hides behind the
+// compute warps' phase A of the previous unit); fe_w2_load_store writes the pairs once W is free.
+struct FeW2Stage {
+    static constexpr int U = (FeW2Cfg::RT / 4 + FeW2Cfg::NLT - 1) / FeW2Cfg::NLT;  // groups per loader thread
+    float4 a[U], b[U];
+};
+
+FE_HD FE_INLINE bool fe_w2_interior(const FeWhisper2Params& p, const FeW2Unit& t) {
     typedef FeW2Cfg C;
+    const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
+    return (p.vec_ok & 1) && g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
+}
+
+FE_HD FE_INLINE void fe_w2_load_issue(const FeWhisper2Params& p, const FeW2Unit& t, int ltid, FeW2Stage& r) {
+    typedef FeW2Cfg C;
+    constexpr int NQ = C::RT / 4;        // 1340 groups of 4 samples
+    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL);
+    const float4* __restrict__ xa = reinterpret_cast<const float4*>(x);
+    const float4* __restrict__ xb = xa + C::SEG / 4;
+#pragma unroll
+    for (int j = 0; j < FeW2Stage::U; ++j) {
+        const int q = ltid + j * C::NLT;
+        if (j + 1 < FeW2Stage::U || q < NQ) { r.a[j] = xa[q]; r.b[j] = xb[q]; }
+    }
+}
+
+FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
+    typedef FeW2Cfg C;
+    constexpr int NQ = C::RT / 4;
+    constexpr int QPB = C::HOP / 4;      // 40 groups per 160-sample block (one pad slot after each)
+    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
+#pragma unroll
+    for (int j = 0; j < FeW2Stage::U; ++j) {
+        const unsigned q = (unsigned)(ltid + j * C::NLT);
+        if (j + 1 < FeW2Stage::U || q < (unsigned)NQ) {
+            fe2* d = w + 4u * q + q / (unsigned)QPB;
+            d[0] = fe_mk2(r.a[j].x, r.b[j].x); d[1] = fe_mk2(r.a[j].y, r.b[j].y);
+            d[2] = fe_mk2(r.a[j].z, r.b[j].z); d[3] = fe_mk2(r.a[j].w, r.b[j].w);
+        }
+    }
+}
+
+// edge units (reflect / zero padding, ragged ends, unaligned rows): element-wise, after W is free
+FE_HD FE_INLINE void fe_w2_load_edge(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
+    typedef FeW2Cfg C;
+    constexpr int NQ = C::RT / 4;
+    constexpr int QPB = C::HOP / 4;
     const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
     const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
     fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
-    constexpr int NQ = C::RT / 4;        // 1340 groups of 4 samples
-    constexpr int QPB = C::HOP / 4;      // 40 groups per 160-sample block (one pad slot after each)
-    const bool interior = (p.vec_ok & 1) && g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
-    if (interior) {
-        const float4* __restrict__ xa = reinterpret_cast<const float4*>(x + g0);
-        const float4* __restrict__ xb = xa + C::SEG / 4;
-        constexpr int U = 7;
-#pragma unroll 1
-        for (int q0 = ltid; q0 < NQ; q0 += C::NLT * U) {
-            float4 a[U], b[U];
+    for (int q = ltid; q < NQ; q += C::NLT) {
+        const int64_t g = g0 + 4 * q;
+        fe2* d = w + 4 * q + q / QPB;
 #pragma unroll
-            for (int j = 0; j < U; ++j) {
-                const int q = q0 + j * C::NLT;
-                if (q < NQ) { a[j] = xa[q]; b[j] = xb[q]; }
-            }
-#pragma unroll
-            for (int j = 0; j < U; ++j) {
-                const unsigned q = (unsigned)(q0 + j * C::NLT);
-                if (q < (unsigned)NQ) {
-                    fe2* d = w + 4u * q + q / (unsigned)QPB;
-                    d[0] = fe_mk2(a[j].x, b[j].x); d[1] = fe_mk2(a[j].y, b[j].y);
-                    d[2] = fe_mk2(a[j].z, b[j].z); d[3] = fe_mk2(a[j].w, b[j].w);
-                }
-            }
-        }
-    } else {
-        for (int q = ltid; q < NQ; q += C::NLT) {
-            const int64_t g = g0 + 4 * q;
-            fe2* d = w + 4 * q + q / QPB;
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-                d[j] = fe_mk2(fe_fetch_reflect(x, g + j, t.len, t.lp), fe_fetch_reflect(x, g + C::SEG + j, t.len, t.lp));
-        }
+        for (int j = 0; j < 4; ++j)
+            d[j] = fe_mk2(fe_fetch_reflect(x, g + j, t.len, t.lp), fe_fetch_reflect(x, g + C::SEG + j, t.len, t.lp));
     }
 }
 
