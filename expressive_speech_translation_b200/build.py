@@ -11,7 +11,6 @@ DEPS = [
     SRC,
     os.path.join(HERE, "csrc", "b200feat_host.inl"),
     os.path.join(HERE, "csrc", "fe_common.h"),
-    os.path.join(HERE, "csrc", "fe_whisper.cuh"),
     os.path.join(HERE, "csrc", "fe_kaldi.cuh"),
     os.path.join(HERE, "csrc", "fe_cosy.cuh"),
     os.path.join(HERE, "csrc", "generated", "fe_codelets.h"),

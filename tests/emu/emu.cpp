@@ -7,44 +7,61 @@
 #include "fe_common.h"
 #include "generated/fe_codelets.h"
 #include "generated/fe_tables.h"
-#include "fe_whisper.cuh"
+#include "fe_whisper2.cuh"
 
+// one unit at a time: loader threads, then the compute warps phase by phase (what the named barriers order on the GPU)
 template <int NMELS>
-static void run_whisper(FeWhisperParams p) {
-    typedef FeWCfg C;
+static void run_whisper(const FeWhisper2Params& p) {
+    typedef FeW2Cfg C;
     std::vector<float> sm(C::SMEM_FLOATS);
-    const int ncta = p.nclips * p.tiles_per_clip;
-    for (int cta = 0; cta < ncta; ++cta) {
-        for (int tid = 0; tid < C::NT; ++tid) fe_w_phase_load(p, sm.data(), tid, cta);
-        for (int tid = 0; tid < C::NT; ++tid) fe_w_phase_a(p, sm.data(), tid, cta);
-        for (int tid = 0; tid < C::NT; ++tid) fe_w_phase_b(p, sm.data(), tid, cta);
-        int key = FE_KEY_INIT;
-        for (int tid = 0; tid < C::NT; ++tid) key = std::max(key, fe_w_phase_mel<NMELS>(p, sm.data(), tid, cta));
-        const FeWTile t = fe_w_tile(p, cta);
+    for (int u = 0; u < p.total_units; ++u) {
+        const FeW2Unit t = fe_w2_unit(p, u);
+        float mn = 3.0e38f, mx = -3.0e38f;
+        if (t.t0 < t.T) {
+            if (fe_w2_interior(p, t)) {
+                for (int l = 0; l < C::NLT; ++l) {
+                    FeW2Stage st;
+                    fe_w2_load_issue(p, t, l, st);
+                    fe_w2_load_store(sm.data(), l, st);
+                }
+            } else {
+                for (int l = 0; l < C::NLT; ++l) fe_w2_load_edge(p, t, sm.data(), l);
+            }
+            for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_a(sm.data(), l, w);
+            for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_b(sm.data(), l, w);
+            for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) {
+                const fe2 mm = fe_w2_phase_mel<NMELS>(p, t, sm.data(), l, w);
+                mn = std::min(mn, mm.x); mx = std::max(mx, mm.y);
+            }
+        }
+        p.unit_minmax[u] = make_float2(mn, mx);
         int* slot = p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b);
-        *slot = std::max(*slot, key);
+        *slot = std::max(*slot, fe_float_key(mx));
     }
 }
 
 extern "C" int emu_whisper(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
                            int n_mels, int padding, int norm_mode, float* out, int64_t T_out) {
-    std::vector<int> keys(B, FE_KEY_INIT);
-    FeWhisperParams p;
+    typedef FeW2Cfg C;
+    std::vector<int> keys(B > 0 ? B : 1, FE_KEY_INIT);
+    FeWhisper2Params p;
     memset(&p, 0, sizeof(p));
     p.wave = wave; p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B; p.padding = padding;
     p.n_mels = n_mels; p.norm_mode = norm_mode; p.out = out; p.out_batch_stride = (int64_t)n_mels * T_out;
-    p.T_out = T_out; p.tiles_per_clip = (int)((T_out + 31) / 32);
+    p.T_out = T_out; p.units_per_clip = (int)((T_out + C::FT - 1) / C::FT); p.total_units = B * p.units_per_clip;
     p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
-    p.max_keys = keys.data(); p.clip0 = 0; p.nclips = B;
+    std::vector<float2> mm((size_t)std::max(p.total_units, 1));
+    p.max_keys = keys.data(); p.unit_minmax = mm.data();
     if (n_mels == 80) run_whisper<80>(p); else if (n_mels == 128) run_whisper<128>(p); else return -1;
+    // the fix-up kernel's arithmetic, applied to every element
     for (int b = 0; b < B; ++b) {
-        const float gmax = fe_key_float(keys[norm_mode == FE_NORM_PER_CALL ? 0 : b]);
+        const float thr = fe_w2_threshold(fe_key_float(keys[norm_mode == FE_NORM_PER_CALL ? 0 : b]));
         const int64_t len = fe_clip_len(lengths, b, L);
         const int64_t Tb = std::min<int64_t>((len + padding) / 160, T_out);
         for (int m = 0; m < n_mels; ++m)
             for (int64_t t = 0; t < T_out; ++t) {
                 float& v = out[(int64_t)b * p.out_batch_stride + m * T_out + t];
-                v = t < Tb ? fe_w_normalise(v, gmax) : 0.0f;
+                v = t < Tb ? (v < thr ? thr : v) : 0.0f;
             }
     }
     return 0;

@@ -49,7 +49,8 @@ def test_version_frames_workspace(lib):
     assert lib.b200feat_num_frames(2, 80000, 0) == 498
     assert lib.b200feat_num_frames(2, 399, 0) == 0
     assert lib.b200feat_num_frames(9, 1, 0) == -1
-    assert lib.b200feat_workspace_bytes(0, 1024, 480000) == 16 + 4096
+    # Whisper: 16 + keys (4 B per clip, 16-aligned) + (min, max) per 64-frame unit; L includes the padding
+    assert lib.b200feat_workspace_bytes(0, 1024, 480000) == 16 + 4096 + 1024 * 47 * 8
     assert lib.b200feat_workspace_bytes(1, 256, 240000) == 16
     assert lib.b200feat_workspace_bytes(2, 4096, 80000) == 16 + 4096 * 16 * 80 * 4
     assert lib.b200feat_launch_count() >= 0
