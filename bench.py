@@ -210,10 +210,10 @@ def run_ours(args, rank, world, local_rank):
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get("fe_whisper_kernel_128_dram_bytes_per_launch")
+            traffic = json.load(f).get("fe_whisper2_kernel_128_dram_bytes_per_1024_clips")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "fe_whisper_kernel<128>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "fe_whisper2_kernel<128>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_per_launch": k_ms, "clips_per_launch": clips_per_launch,
                 "algorithmic_bytes_per_launch": clips_per_launch * BYTES_PER_CLIP,

@@ -1,0 +1,49 @@
+"""Clip sharding for the batch sweep.
+
+The reference's batch driver runs one manifest row = one clip = one process
+(/root/reference/Batch-Processing/submit_slurm_job.sh:10,41,53: SLURM array task i reads CSV row i + 1).  Here one
+process per GPU takes a CONTIGUOUS block of rows; clips are independent, so there is no collective on the data
+path.  The only exchange is an all-gather of three int64 per rank (clips, frames, samples) for the sweep report.
+"""
+import csv
+
+import torch
+
+
+def shard_rows(n_rows, rank, world):
+    """rows [lo, hi) of rank `rank` out of `world`: lo = rank*n // world (contiguous, sizes differ by <= 1)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    if n_rows < 0:
+        raise ValueError("n_rows < 0")
+    return rank * n_rows // world, (rank + 1) * n_rows // world
+
+
+def read_manifest(path):
+    """rows of a Batch-Processing manifest (job_id, dataset, source_video_path; header row skipped), as written by
+    /root/reference/Batch-Processing/create_batch_manifest.py:52-56."""
+    with open(path, newline="") as f:
+        rows = list(csv.reader(f))
+    if rows and rows[0] and rows[0][0].strip().lower() == "job_id":
+        rows = rows[1:]
+    return [r for r in rows if r]
+
+
+def sub_batches(lo, hi, max_clips):
+    """[lo, hi) cut into consecutive sub-batches of at most max_clips clips (bounds device residency)."""
+    if max_clips < 1:
+        raise ValueError("max_clips < 1")
+    return [(a, min(a + max_clips, hi)) for a in range(lo, hi, max_clips)]
+
+
+def gather_counts(clips, frames, samples, device=None, group=None):
+    """-> (world, 3) int64 tensor of every rank's (clips, frames, samples).  Works on gloo (CPU tensors) and nccl
+    (pass the rank's cuda device).  Without an initialised process group it returns the local row."""
+    import torch.distributed as dist
+    mine = torch.tensor([int(clips), int(frames), int(samples)], dtype=torch.int64, device=device)
+    if not (dist.is_available() and dist.is_initialized()):
+        return mine.unsqueeze(0)
+    world = dist.get_world_size(group)
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    return torch.stack(out)
