@@ -67,23 +67,35 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
         }
         return;
     }
+    // compute warps.  Software pipeline over the CTA's units u0, u1, ...:
+    //   prologue: A(u0)
+    //   per unit: B(u) | barrier | M(u) then A(u+1) back to back (P has its own buffer, so the next unit's phase A
+    //             overlaps the mel phase of slower warps) | barrier | publish (min, max) of u
+    const int u0 = blockIdx.x, du = gridDim.x;
     int par = 0;
-    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1) {
-        const bool more = u + (int)gridDim.x < p.total_units;
+    {
         fe_bar_sync(FE_BAR_W_FULL, C::NT);
+        const bool live0 = misc[5] < misc[6];
+        if (live0) fe_w2_phase_a(sm, lane, warp);
+        if (u0 + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
+    }
+    for (int u = u0; u < p.total_units; u += du, par ^= 1) {
         FeW2Unit t;
         t.b = misc[4 + 4 * par]; t.t0 = misc[5 + 4 * par]; t.T = misc[6 + 4 * par];
         const bool live = t.t0 < t.T;
-        if (live) fe_w2_phase_a(sm, lane, warp);
-        if (more) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
-        if (!live) {
-            if (tid == 0) p.unit_minmax[u] = make_float2(3.0e38f, -3.0e38f);
-            continue;
+        const int un = u + du;
+        const bool has_next = un < p.total_units;
+        if (live) fe_w2_phase_b(sm, lane, warp);
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);                   // P(u) complete, Ar / Ai free
+        fe2 mm = fe_mk2(3.0e38f, -3.0e38f);
+        if (live) mm = fe_w2_phase_mel<NMELS>(p, t, sm, lane, warp);
+        if (has_next) {
+            fe_bar_sync(FE_BAR_W_FULL, C::NT);                 // W(next) and its descriptor are in place
+            const bool live_n = misc[5 + 4 * (par ^ 1)] < misc[6 + 4 * (par ^ 1)];
+            if (live_n) fe_w2_phase_a(sm, lane, warp);
+            if (un + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
         }
-        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
-        fe_w2_phase_b(sm, lane, warp);
-        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
-        const fe2 mm = fe_w2_phase_mel<NMELS>(p, t, sm, lane, warp);
         int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -91,15 +103,16 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
             kmin = max(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
         }
         if (lane == 0) { atomicMax(misc + 0, kmax); atomicMax(misc + 1, kmin); }
-        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);                   // M(u) done with P, A(next) complete, keys final
         if (tid == 0) {
             const float ymax = fe_key_float(misc[0]), ymin = -fe_key_float(misc[1]);
             p.unit_minmax[u] = make_float2(ymin, ymax);
-            atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b), misc[0]);
+            if (live) atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b), misc[0]);
             misc[0] = FE_KEY_INIT; misc[1] = FE_KEY_INIT;
         }
     }
 }
+
 
 // Fix-up: clamps the units whose minimum lies below max - 8 decades (y < ymax - 2) and zero-fills the
 // frames past a ragged clip's own end.  Everything else is left untouched (one trip to HBM).

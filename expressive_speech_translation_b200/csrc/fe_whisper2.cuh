@@ -59,9 +59,12 @@ struct FeW2Cfg {
     static constexpr int LS = HOP + 1;                   // lane stride in W (pairs)
     static constexpr int SW = RT + RT / HOP + 3;         // padded W (pairs)
     static constexpr int FS = 221;                       // pairs per lane in each A plane (11*20 + 1 -> odd)
-    static constexpr int OFF_AR = SW * 2;                // in floats: real plane (later: the power spectrum)
+    static constexpr int PSZ = 201;                      // pairs per lane in P (200 bins + 1 -> odd)
+    static constexpr int OFF_AR = SW * 2;                // in floats: real plane
     static constexpr int OFF_AI = OFF_AR + LANES * FS * 2;   // imaginary plane
-    static constexpr int OFF_MISC = OFF_AI + LANES * FS * 2; // ints: [0] max key [1] min key [4..7], [8..11] unit info
+    static constexpr int OFF_P = OFF_AI + LANES * FS * 2;    // power spectrum P[lane][bin] (pairs); own buffer so
+                                                             // that phase A of the next unit can overlap phase M
+    static constexpr int OFF_MISC = OFF_P + LANES * PSZ * 2; // ints: [0] max key [1] min key [4..7], [8..11] unit info
     static constexpr int SMEM_FLOATS = OFF_MISC + 16;
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
     static constexpr float LOG_SCALE = 0.07525749891599530f;  // log10(2) / 4
@@ -183,45 +186,48 @@ FE_HD FE_INLINE void fe_w2_phase_a(float* sm, int lane, int warp) {
 }
 
 // ---------------------------------------------------------------- phase B
-// Power of bin k (k < 200) of this lane's pair lives, after phase B, in the REAL plane (in place over the
-// task's own row): kk = k % 20, j = k / 20;  kk <= 10: Ar[20*kk + j];  kk > 10: Ar[20*(20 - kk) + 10 + j].
+// Power of bin k (k < 200) of this lane's pair goes to P[lane][k] (lane stride PSZ pairs, odd).
 FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1) {
     typedef FeW2Cfg C;
-    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * k1;
+    const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * k1;
     const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * k1;
     fe2 xr[20], xi[20], yr[20], yi[20];
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
     fe_cdft20(xr, xi, yr, yi);
+    fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + k1;          // bins k1 + 20*j
+    fe2* __restrict__ pb = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + (C::R - k1);  // bins (20-k1) + 20*j
 #pragma unroll
     for (int j = 0; j < 10; ++j) {
-        ar[j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));                           // bin k1 + 20*j
-        ar[10 + j] = fe_fma(yr[19 - j], yr[19 - j], fe_mul(yi[19 - j], yi[19 - j]));  // bin (20-k1) + 20*j
+        pa[C::R * j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
+        pb[C::R * j] = fe_fma(yr[19 - j], yr[19 - j], fe_mul(yi[19 - j], yi[19 - j]));
     }
 }
 
 FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane) {   // k1 = 0: real input, bins 20*j, j = 0..9
     typedef FeW2Cfg C;
-    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane;
+    const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane;
     fe2 xr[20], yr[10], yi[10];
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) xr[n2] = ar[n2];
     yi[0] = fe_zero<fe2>();
     fe_rdft20_h10(xr, yr, yi);
+    fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane;
 #pragma unroll
-    for (int j = 0; j < 10; ++j) ar[j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
+    for (int j = 0; j < 10; ++j) pa[C::R * j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
 }
 
 FE_HD FE_INLINE void fe_w2_stage_b_k10(float* sm, int lane) {  // k1 = 10: bins 10 + 20*j, j = 0..9
     typedef FeW2Cfg C;
-    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * 10;
+    const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * 10;
     const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * 10;
     fe2 xr[20], xi[20], yr[10], yi[10];
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
     fe_cdft20_h10(xr, xi, yr, yi);
+    fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + 10;
 #pragma unroll
-    for (int j = 0; j < 10; ++j) ar[j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
+    for (int j = 0; j < 10; ++j) pa[C::R * j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
 }
 
 // 11 tasks: warp 0 -> k1 = 0, warps 1..9 -> k1 = warp, warp 10 -> k1 = 10, warp 11 idle
@@ -288,17 +294,14 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     const bool la = fa < t.T, lb = fb < t.T;
     float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + fa;
     const unsigned rs4 = (unsigned)p.T_out * 4u;   // row pitch in bytes; the host guarantees T_out < 2^24
-    const fe2* __restrict__ P = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane;
+    const fe2* __restrict__ P = reinterpret_cast<const fe2*>(sm + C::OFF_P) + C::PSZ * lane;
     union { unsigned u; float f; } qnan;
     qnan.u = 0x7fc00000u;
     const fe2 one = fe_mk2(la ? 1.0f : qnan.f, lb ? 1.0f : qnan.f);
     float mn = 3.0e38f, mx = -3.0e38f;
     float* q = o;
     int qm = 0;
-    auto ld = [&](int k) -> fe2 {
-        const int kk = k % C::R, j = k / C::R;
-        return (kk <= 10) ? P[C::R * kk + j] : P[C::R * (C::R - kk) + 10 + j];
-    };
+    auto ld = [&](int k) -> fe2 { return P[k]; };
     auto emit = [&](int m, fe2 v) {
         const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(v.x), fe_w2_lg2(v.y)), one);   // (log10(v) + 4) / 4
         // rows of a chunk are consecutive: after the first one this is a 64-bit add of the row pitch
