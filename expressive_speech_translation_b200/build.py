@@ -11,6 +11,7 @@ DEPS = [
     SRC,
     os.path.join(HERE, "csrc", "b200feat_host.inl"),
     os.path.join(HERE, "csrc", "fe_common.h"),
+    os.path.join(HERE, "csrc", "fe_whisper2.cuh"),
     os.path.join(HERE, "csrc", "fe_kaldi.cuh"),
     os.path.join(HERE, "csrc", "fe_cosy.cuh"),
     os.path.join(HERE, "csrc", "generated", "fe_codelets.h"),

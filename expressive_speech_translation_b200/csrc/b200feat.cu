@@ -24,16 +24,69 @@
 // =====================================================================================================
 // named barriers (id 0 is __syncthreads)
 enum { FE_BAR_W_FULL = 1, FE_BAR_W_FREE = 2, FE_BAR_COMPUTE = 3 };
+#ifdef FE_W2_NOSYNC   // timing experiment only (free-running warps, garbage results): tools/trace_w2.py
+static __device__ __forceinline__ void fe_bar_sync(int, int) { asm volatile("" ::: "memory"); }
+static __device__ __forceinline__ void fe_bar_arrive(int, int) { asm volatile("" ::: "memory"); }
+#else
 static __device__ __forceinline__ void fe_bar_sync(int id, int count) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
 static __device__ __forceinline__ void fe_bar_arrive(int id, int count) {
     asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
+#endif
+
+#ifdef FE_W2_TRACE
+// debug build only (tools/trace_w2.py): clock64 stamps of CTA 0's warps at the phase boundaries
+#define FE_TR_UNITS 12
+#define FE_TR_EV 8
+__device__ long long fe_w2_trace_buf[FE_TR_UNITS * 16 * FE_TR_EV];
+#define FE_TR(iter, ev) do { if (blockIdx.x == 0 && (unsigned)(iter) < FE_TR_UNITS && lane == 0) \
+    fe_w2_trace_buf[((iter) * 16 + warp) * FE_TR_EV + (ev)] = clock64(); } while (0)
+#else
+#define FE_TR(iter, ev) do { } while (0)
+#endif
+
+// mbarriers in shared memory (32-bit shared-window addresses)
+static __device__ __forceinline__ void fe_mbar_init(unsigned addr, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(addr), "r"(count) : "memory");
+}
+static __device__ __forceinline__ void fe_mbar_arrive(unsigned addr) {   // release.cta: orders the thread's prior accesses
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(addr) : "memory");
+}
+static __device__ __forceinline__ void fe_mbar_wait(unsigned addr, unsigned parity) {
+#ifdef FE_W2_NOSYNC
+    asm volatile("" ::: "memory");
+    return;
+#endif
+    asm volatile(
+        "{\n\t.reg .pred p;\n"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n\t}" ::"r"(addr), "r"(parity) : "memory");
+}
+// one arrival per warp, after every lane's prior shared-memory accesses
+struct FeWarpArrive {
+    unsigned addr; int lane;
+    __device__ __forceinline__ void operator()() const {
+        __syncwarp();
+        if (lane == 0) fe_mbar_arrive(addr);
+    }
+};
+struct FeMbarWait {
+    unsigned addr, parity;
+    __device__ __forceinline__ void operator()() const { fe_mbar_wait(addr, parity); }
+};
 
 // Persistent, warp-specialised: NLW loader warps run one unit ahead of NCW compute warps.
 //   loader : [wait W_FREE] fill W(u), publish the unit's (clip, first frame, frame count) -> arrive W_FULL
-//   compute: wait W_FULL -> phase A -> arrive W_FREE -> B -> M -> publish (min, max) of the unit
+//   compute: ONE CTA-wide barrier per unit.  Between two barriers every compute warp runs, in its own order,
+//            its task of phase B(u), its tasks of phase A(u+1) and its chunk of phase M(u); two mbarriers carry the
+//            dependencies inside the interval ("B(u) has read the A planes" before A(u+1) stores into them,
+//            "P(u) complete" before M(u) reads it).  Warps of one SM sub-partition are in different phases at any
+//            time, so the shared-memory bursts of one overlap the FP32 work of another.
 template <int NMELS>
 __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhisper2Params p) {
     typedef FeW2Cfg C;
@@ -42,59 +95,121 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
     const int lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // warp-uniform for the compiler
     int* misc = reinterpret_cast<int*>(sm + C::OFF_MISC);     // [0] max key, [1] key of -min, [4 + 4*par ..] unit info
-    if (tid == 0) { misc[0] = FE_KEY_INIT; misc[1] = FE_KEY_INIT; }
+    const unsigned mb_bl = (unsigned)__cvta_generic_to_shared(sm + C::OFF_MBAR);   // B(u) loads done
+    const unsigned mb_pb = mb_bl + 8;                                               // P(u) complete
+    if (tid == 0) {
+        misc[0] = FE_KEY_INIT; misc[1] = FE_KEY_INIT;
+        fe_mbar_init(mb_bl, C::NCW);
+        fe_mbar_init(mb_pb, C::NCW);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    fe_w2_copy_tables<NMELS>(sm, tid, C::NT);
     __syncthreads();
     if (warp >= C::NCW) {
         const int ltid = tid - C::NCT;
         int par = 0;
+        int it = 0;
+#ifdef FE_W2_LOADER_ASYNC
+        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1, ++it) {
+            const FeW2Unit t = fe_w2_unit(p, u);
+            FE_TR(it, 0);
+            if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
+            FE_TR(it, 1);
+            if (t.t0 < t.T) {
+                if (fe_w2_interior(p, t)) fe_w2_load_async(p, t, sm, ltid);
+                else fe_w2_load_edge(p, t, sm, ltid);
+            }
+            if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
+            FE_TR(it, 2);
+            fe_bar_arrive(FE_BAR_W_FULL, C::NT);
+            FE_TR(it, 3);
+        }
+#else
         FeW2Stage stage;
         FeW2Unit t = fe_w2_unit(p, blockIdx.x);
         bool live = t.t0 < t.T, fast = live && fe_w2_interior(p, t);
+#ifdef FE_W2_EXP_NOLOAD
+        live = false;
+#endif
         if (fast) fe_w2_load_issue(p, t, ltid, stage);
-        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1) {
+        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1, ++it) {
+            FE_TR(it, 0);
             if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
+            FE_TR(it, 1);
             if (fast) fe_w2_load_store(sm, ltid, stage);
             else if (live) fe_w2_load_edge(p, t, sm, ltid);
             if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
+            FE_TR(it, 2);
             fe_bar_arrive(FE_BAR_W_FULL, C::NT);
             const int un = u + (int)gridDim.x;
             if (un < p.total_units) {   // next unit: loads go in flight now, stores wait for W_FREE
                 t = fe_w2_unit(p, un);
                 live = t.t0 < t.T;
                 fast = live && fe_w2_interior(p, t);
+#ifdef FE_W2_EXP_NOLOAD
+                fast = false; live = false;
+#endif
                 if (fast) fe_w2_load_issue(p, t, ltid, stage);
             }
+            FE_TR(it, 3);
         }
+#endif
         return;
     }
-    // compute warps.  Software pipeline over the CTA's units u0, u1, ...:
-    //   prologue: A(u0)
-    //   per unit: B(u) | barrier | M(u) then A(u+1) back to back (P has its own buffer, so the next unit's phase A
-    //             overlaps the mel phase of slower warps) | barrier | publish (min, max) of u
+    // ---- compute warps
     const int u0 = blockIdx.x, du = gridDim.x;
-    int par = 0;
-    {
-        fe_bar_sync(FE_BAR_W_FULL, C::NT);
-        const bool live0 = misc[5] < misc[6];
-        if (live0) fe_w2_phase_a(sm, lane, warp);
-        if (u0 + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
-        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);
-    }
-    for (int u = u0; u < p.total_units; u += du, par ^= 1) {
-        FeW2Unit t;
-        t.b = misc[4 + 4 * par]; t.t0 = misc[5 + 4 * par]; t.T = misc[6 + 4 * par];
-        const bool live = t.t0 < t.T;
+    const int n2b = fe_w2_a_second(warp);
+    // order of the three steps after B, by warp group (every SM sub-partition holds one warp of each group, so its
+    // warps are in different phases: shared-memory bursts, FP32 work and the latency-bound mel loop overlap):
+    //   warps 0-3, 8-11: A1 A2 M     warps 4-7: A1 M A2        (codes: 1 = A1, 2 = M, 3 = A2)
+    // (M before A1 was measured slower: it delays the release of W and with it the loader)
+    const unsigned order = (warp & 4) ? 0x321u : 0x231u;
+    FeW2Unit cur;
+    cur.b = 0; cur.t0 = 0; cur.T = 0; cur.len = 0; cur.lp = 0;
+    // iteration -1 is the prologue: only the A(u0) tasks run (same code as in the steady state)
+    int it = -1;
+    for (int u = u0 - du; u < p.total_units; u += du, ++it) {
+        FE_TR(it, 0);
+        const bool first = it < 0;
+        const bool live = cur.t0 < cur.T;
         const int un = u + du;
         const bool has_next = un < p.total_units;
-        if (live) fe_w2_phase_b(sm, lane, warp);
-        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);                   // P(u) complete, Ar / Ai free
+        const unsigned parity = (unsigned)(it & 1);                // -1 -> 1: passes on the fresh mbarrier
+        FeW2Unit nxt = cur;
+        bool live_n = false;
         fe2 mm = fe_mk2(3.0e38f, -3.0e38f);
-        if (live) mm = fe_w2_phase_mel<NMELS>(p, t, sm, lane, warp);
-        if (has_next) {
-            fe_bar_sync(FE_BAR_W_FULL, C::NT);                 // W(next) and its descriptor are in place
-            const bool live_n = misc[5 + 4 * (par ^ 1)] < misc[6 + 4 * (par ^ 1)];
-            if (live_n) fe_w2_phase_a(sm, lane, warp);
-            if (un + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
+#pragma unroll 1
+        for (int step = 0; step < 4; ++step) {
+            // 0: B(u)   then, in the warp's order: 1 = first A(u+1) task, 2 = M(u), 3 = second A(u+1) task
+            const int op = step == 0 ? 0 : (int)((order >> (4 * (step - 1))) & 0xfu);
+            if (op == 0) {
+                if (!first) {
+                    const FeWarpArrive loads_done{mb_bl, lane};
+                    if (live) fe_w2_phase_b(sm, lane, warp, loads_done);
+                    else loads_done();
+                    const FeWarpArrive p_done{mb_pb, lane};
+                    p_done();
+                }
+            } else if (op == 2) {
+                if (!first) {
+                    fe_mbar_wait(mb_pb, parity);
+                    if (live) mm = fe_w2_phase_mel<NMELS>(p, cur, sm, lane, warp);
+                }
+            } else if (has_next) {
+                if (op == 1) {
+                    fe_bar_sync(FE_BAR_W_FULL, C::NT);             // W(next) and its descriptor are in place
+                    const int np = (it + 1) & 1;
+                    nxt.b = misc[4 + 4 * np]; nxt.t0 = misc[5 + 4 * np]; nxt.T = misc[6 + 4 * np];
+#ifdef FE_W2_NOSYNC
+                    nxt = fe_w2_unit(p, un);
+#endif
+                    live_n = nxt.t0 < nxt.T;
+                }
+                const int n2 = op == 1 ? warp : n2b;
+                if (live_n && n2 >= 0) fe_w2_stage_a(sm, lane, n2, FeMbarWait{mb_bl, parity});
+                if (op == 3 && un + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
+            }
+            FE_TR(it, 1 + step);
         }
         int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
 #pragma unroll
@@ -103,13 +218,16 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
             kmin = max(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
         }
         if (lane == 0) { atomicMax(misc + 0, kmax); atomicMax(misc + 1, kmin); }
-        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);                   // M(u) done with P, A(next) complete, keys final
-        if (tid == 0) {
+        FE_TR(it, 5);
+        fe_bar_sync(FE_BAR_COMPUTE, C::NCT);                   // P(u) consumed, A(next) complete, keys final
+        FE_TR(it, 6);
+        if (tid == 0 && !first) {
             const float ymax = fe_key_float(misc[0]), ymin = -fe_key_float(misc[1]);
             p.unit_minmax[u] = make_float2(ymin, ymax);
-            if (live) atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b), misc[0]);
+            if (live) atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : cur.b), misc[0]);
             misc[0] = FE_KEY_INIT; misc[1] = FE_KEY_INIT;
         }
+        cur = nxt;
     }
 }
 
@@ -300,6 +418,12 @@ extern "C" {
 int b200feat_version(void) { return B200FEAT_VERSION; }
 const char* b200feat_last_error(void) { return g_err.c_str(); }
 int64_t b200feat_launch_count(void) { return g_launches.load(); }
+
+#ifdef FE_W2_TRACE
+int b200feat_debug_trace(long long* host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, fe_w2_trace_buf, sizeof(long long) * FE_TR_UNITS * 16 * FE_TR_EV);
+}
+#endif
 
 int b200feat_profile_begin(void) {
     std::lock_guard<std::mutex> lk(g_prof_mu);

@@ -30,6 +30,7 @@ static __device__ __forceinline__ float fe_lg2_ftz(float x) {
 #define FE_SQRT(x) sqrtf(x)
 struct float2 { float x, y; };
 struct float4 { float x, y, z, w; };
+struct int2 { int x, y; };
 static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b; return r; }
 static inline float4 make_float4(float a, float b, float c, float d) { float4 r; r.x = a; r.y = b; r.z = c; r.w = d; return r; }
 #endif

@@ -63,9 +63,19 @@ struct FeW2Cfg {
     static constexpr int OFF_AR = SW * 2;                // in floats: real plane
     static constexpr int OFF_AI = OFF_AR + LANES * FS * 2;   // imaginary plane
     static constexpr int OFF_P = OFF_AI + LANES * FS * 2;    // power spectrum P[lane][bin] (pairs); own buffer so
-                                                             // that phase A of the next unit can overlap phase M
+                                                             // that phase A of the next unit can overlap B and M
     static constexpr int OFF_MISC = OFF_P + LANES * PSZ * 2; // ints: [0] max key [1] min key [4..7], [8..11] unit info
-    static constexpr int SMEM_FLOATS = OFF_MISC + 16;
+    static constexpr int OFF_MBAR = OFF_MISC + 12;           // two 8-byte mbarriers: [0] "B(u) has read its rows of
+                                                             // the A planes", [1] "P(u) is complete"
+    // constant tables, copied once per CTA (register-indexed constant loads are far too slow for the hot loops):
+    static constexpr int OFF_TABA = OFF_MISC + 16;           // fe_w2_tab: [n2][window(20) | twiddles(20)]
+    static constexpr int OFF_MDESC = OFF_TABA + 800;         // fe_melloop_*_desc (2 ints per filter, <= 128 filters)
+    static constexpr int OFF_MW = OFF_MDESC + 256;           // fe_melloop_*_w (padded taps)
+    static constexpr int MW_MAX = 576;
+    static constexpr int SMEM_FLOATS = OFF_MW + MW_MAX;
+    static_assert(OFF_MBAR % 2 == 0, "mbarriers need 8-byte alignment");
+    static_assert(OFF_TABA % 4 == 0 && OFF_MW % 4 == 0, "tables are read with 128-bit loads");
+    static_assert(SMEM_FLOATS * 4 <= 232448, "more than 227 KB of shared memory");
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
     static constexpr float LOG_SCALE = 0.07525749891599530f;  // log10(2) / 4
     static constexpr float Y_FLOOR = -1.5f;                   // (log10(1e-10) + 4) / 4
@@ -91,47 +101,58 @@ FE_HD FE_INLINE FeW2Unit fe_w2_unit(const FeWhisper2Params& p, int u) {
 }
 
 // ---------------------------------------------------------------- loader
-// ltid in [0, NLT).  Four consecutive samples of both segments per step.  Interior units (fully inside the
-// clip, 16B-aligned rows) are fetched in two halves: fe_w2_load_issue puts every 128-bit load of the unit in
-// flight at once (it runs BEFORE the loader waits for W to be released, so the HBM latency hides behind the
-// compute warps' phase A of the previous unit); fe_w2_load_store writes the pairs once W is free.
-struct FeW2Stage {
-    static constexpr int U = (FeW2Cfg::RT / 4 + FeW2Cfg::NLT - 1) / FeW2Cfg::NLT;  // groups per loader thread
-    float4 a[U], b[U];
-};
-
+// ltid in [0, NLT).  Interior units (fully inside the clip) are copied with 4-byte cp.async, one sample of each
+// segment per step: a warp reads two coalesced 128-byte rows and scatters them into 32 consecutive pairs.  No
+// staging registers, a rolled loop (small code), the copies of a whole unit in flight at once.  W is released
+// by the compute warps right after their last phase-A loads, most of a unit period before it is needed again.
 FE_HD FE_INLINE bool fe_w2_interior(const FeWhisper2Params& p, const FeW2Unit& t) {
     typedef FeW2Cfg C;
     const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
-    return (p.vec_ok & 1) && g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
+    return g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
 }
+
+FE_HD FE_INLINE void fe_w2_load_async(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
+    typedef FeW2Cfg C;
+    const float* __restrict__ xa = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL);
+    const float* __restrict__ xb = xa + C::SEG;
+    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
+#if defined(__CUDA_ARCH__)
+    const unsigned w0 = (unsigned)__cvta_generic_to_shared(w);
+#pragma unroll 2
+    for (unsigned i = (unsigned)ltid; i < (unsigned)C::RT; i += (unsigned)C::NLT) {
+        const unsigned d = w0 + 8u * (i + i / (unsigned)C::HOP);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(xa + i) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u), "l"(xb + i) : "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+#else
+    for (int i = ltid; i < C::RT; i += C::NLT) w[i + i / C::HOP] = fe_mk2(xa[i], xb[i]);
+#endif
+}
+
+// register-staged variant: fe_w2_load_issue puts every load of the unit in flight (it runs BEFORE the loader
+// waits for W to be released); fe_w2_load_store writes the pairs once W is free (conflict-free 64-bit stores)
+struct FeW2Stage {
+    static constexpr int U = (FeW2Cfg::RT + FeW2Cfg::NLT - 1) / FeW2Cfg::NLT;  // samples per loader thread and segment
+    float a[U], b[U];
+};
 
 FE_HD FE_INLINE void fe_w2_load_issue(const FeWhisper2Params& p, const FeW2Unit& t, int ltid, FeW2Stage& r) {
     typedef FeW2Cfg C;
-    constexpr int NQ = C::RT / 4;        // 1340 groups of 4 samples
-    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL);
-    const float4* __restrict__ xa = reinterpret_cast<const float4*>(x);
-    const float4* __restrict__ xb = xa + C::SEG / 4;
+    const float* __restrict__ xa = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL) + ltid;
 #pragma unroll
     for (int j = 0; j < FeW2Stage::U; ++j) {
-        const int q = ltid + j * C::NLT;
-        if (j + 1 < FeW2Stage::U || q < NQ) { r.a[j] = xa[q]; r.b[j] = xb[q]; }
+        if (j + 1 < FeW2Stage::U || ltid + j * C::NLT < C::RT) { r.a[j] = xa[j * C::NLT]; r.b[j] = xa[j * C::NLT + C::SEG]; }
     }
 }
 
 FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
     typedef FeW2Cfg C;
-    constexpr int NQ = C::RT / 4;
-    constexpr int QPB = C::HOP / 4;      // 40 groups per 160-sample block (one pad slot after each)
     fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
 #pragma unroll
     for (int j = 0; j < FeW2Stage::U; ++j) {
-        const unsigned q = (unsigned)(ltid + j * C::NLT);
-        if (j + 1 < FeW2Stage::U || q < (unsigned)NQ) {
-            fe2* d = w + 4u * q + q / (unsigned)QPB;
-            d[0] = fe_mk2(r.a[j].x, r.b[j].x); d[1] = fe_mk2(r.a[j].y, r.b[j].y);
-            d[2] = fe_mk2(r.a[j].z, r.b[j].z); d[3] = fe_mk2(r.a[j].w, r.b[j].w);
-        }
+        const unsigned i = (unsigned)(ltid + j * C::NLT);
+        if (j + 1 < FeW2Stage::U || i < (unsigned)C::RT) w[i + i / (unsigned)C::HOP] = fe_mk2(r.a[j], r.b[j]);
     }
 }
 
@@ -152,12 +173,45 @@ FE_HD FE_INLINE void fe_w2_load_edge(const FeWhisper2Params& p, const FeW2Unit& 
     }
 }
 
+// copies the constant tables into shared memory; every thread of the CTA calls it, a barrier must follow
+template <int NMELS>
+FE_HD FE_INLINE void fe_w2_copy_tables(float* sm, int tid, int nthreads) {
+    typedef FeW2Cfg C;
+    static_assert(FE_MELLOOP_W80_NW <= C::MW_MAX && FE_MELLOOP_W128_NW <= C::MW_MAX, "MW_MAX too small");
+    const int* __restrict__ desc = NMELS == 80 ? fe_melloop_w80_desc : fe_melloop_w128_desc;
+    const float* __restrict__ w = NMELS == 80 ? fe_melloop_w80_w : fe_melloop_w128_w;
+    const int nw = NMELS == 80 ? FE_MELLOOP_W80_NW : FE_MELLOOP_W128_NW;
+    for (int i = tid; i < 800; i += nthreads) sm[C::OFF_TABA + i] = fe_w2_tab[i];
+    int* d = reinterpret_cast<int*>(sm + C::OFF_MDESC);
+    for (int i = tid; i < 2 * NMELS; i += nthreads) d[i] = desc[i];
+    for (int i = tid; i < nw; i += nthreads) sm[C::OFF_MW + i] = w[i];
+}
+
+struct FeNoHook { FE_HD FE_INLINE void operator()() const {} };
+
+// Task map of the compute warps (one CTA-wide barrier per unit, see fe_whisper2_kernel):
+//   phase B: warp 0 -> k1 = 0, warps 1..9 -> k1 = warp, warp 10 -> k1 = 10, warp 11 none
+//   phase A: first task n2 = warp; a second task for warps 0-4, 6, 7, 11 (n2 = 12..19), chosen so that the four
+//            SM sub-partitions (warp % 4) carry about the same FP32 work over A + B
+FE_HD FE_INLINE int fe_w2_a_second(int warp) {
+    return warp < 5 ? warp + 12 : (warp == 6 ? 17 : (warp == 7 ? 18 : (warp == 11 ? 19 : -1)));
+}
+
 // ---------------------------------------------------------------- phase A
 // A planes: Ar[lane][20*k1 + n2], Ai[lane][20*k1 + n2] (pairs), lane stride FS (odd: conflict-free 64-bit)
-FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2) {
+template <class PreStore>
+FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2, PreStore pre_store) {
     typedef FeW2Cfg C;
     const fe2* __restrict__ s = reinterpret_cast<const fe2*>(sm) + C::LS * lane + n2;
-    const float* __restrict__ tab = fe_w2_tab + 40 * n2;
+    float tab[40];   // this task's window and twiddles: ten 128-bit broadcast loads
+    {
+        const float4* __restrict__ t4 = reinterpret_cast<const float4*>(sm + C::OFF_TABA + 40 * n2);
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+            const float4 v = t4[i];
+            tab[4 * i] = v.x; tab[4 * i + 1] = v.y; tab[4 * i + 2] = v.z; tab[4 * i + 3] = v.w;
+        }
+    }
     fe2 x[C::R];
 #pragma unroll
     for (int n1 = 0; n1 < C::R; ++n1) {
@@ -168,6 +222,7 @@ FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2) {
     fe_rdft20_h11(x, yr, yi);
     fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + n2;
     fe2* __restrict__ ai = reinterpret_cast<fe2*>(sm + C::OFF_AI) + C::FS * lane + n2;
+    pre_store();   // the A planes may still be read by phase B of the previous unit
     ar[0] = yr[0];
 #pragma unroll
     for (int k1 = 1; k1 < 10; ++k1) {
@@ -179,21 +234,24 @@ FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2) {
     ai[C::R * 10] = fe_mulc(tab[39], yr[10]);
 }
 
-// warp in [0, NCW): tasks n2 = warp, warp + NCW (< 20)
+// all phase-A tasks of one warp, in order (prologue of the kernel; host emulation)
 FE_HD FE_INLINE void fe_w2_phase_a(float* sm, int lane, int warp) {
-    typedef FeW2Cfg C;
-    for (int n2 = warp; n2 < C::R; n2 += C::NCW) fe_w2_stage_a(sm, lane, n2);
+    fe_w2_stage_a(sm, lane, warp, FeNoHook());
+    const int n2b = fe_w2_a_second(warp);
+    if (n2b >= 0) fe_w2_stage_a(sm, lane, n2b, FeNoHook());
 }
 
 // ---------------------------------------------------------------- phase B
 // Power of bin k (k < 200) of this lane's pair goes to P[lane][k] (lane stride PSZ pairs, odd).
-FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1) {
+template <class PostLoad>
+FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1, PostLoad post_load) {
     typedef FeW2Cfg C;
     const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * k1;
     const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * k1;
     fe2 xr[20], xi[20], yr[20], yi[20];
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
+    post_load();
     fe_cdft20(xr, xi, yr, yi);
     fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + k1;          // bins k1 + 20*j
     fe2* __restrict__ pb = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + (C::R - k1);  // bins (20-k1) + 20*j
@@ -204,12 +262,14 @@ FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1) {
     }
 }
 
-FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane) {   // k1 = 0: real input, bins 20*j, j = 0..9
+template <class PostLoad>
+FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane, PostLoad post_load) {   // k1 = 0: real input, bins 20*j, j = 0..9
     typedef FeW2Cfg C;
     const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane;
     fe2 xr[20], yr[10], yi[10];
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) xr[n2] = ar[n2];
+    post_load();
     yi[0] = fe_zero<fe2>();
     fe_rdft20_h10(xr, yr, yi);
     fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane;
@@ -217,13 +277,15 @@ FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane) {   // k1 = 0: real i
     for (int j = 0; j < 10; ++j) pa[C::R * j] = fe_fma(yr[j], yr[j], fe_mul(yi[j], yi[j]));
 }
 
-FE_HD FE_INLINE void fe_w2_stage_b_k10(float* sm, int lane) {  // k1 = 10: bins 10 + 20*j, j = 0..9
+template <class PostLoad>
+FE_HD FE_INLINE void fe_w2_stage_b_k10(float* sm, int lane, PostLoad post_load) {  // k1 = 10: bins 10 + 20*j, j = 0..9
     typedef FeW2Cfg C;
     const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * 10;
     const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * 10;
     fe2 xr[20], xi[20], yr[10], yi[10];
 #pragma unroll
     for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
+    post_load();
     fe_cdft20_h10(xr, xi, yr, yi);
     fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + 10;
 #pragma unroll
@@ -231,11 +293,15 @@ FE_HD FE_INLINE void fe_w2_stage_b_k10(float* sm, int lane) {  // k1 = 10: bins 
 }
 
 // 11 tasks: warp 0 -> k1 = 0, warps 1..9 -> k1 = warp, warp 10 -> k1 = 10, warp 11 idle
-FE_HD FE_INLINE void fe_w2_phase_b(float* sm, int lane, int warp) {
-    if (warp == 0) fe_w2_stage_b_k0(sm, lane);
-    else if (warp < 10) fe_w2_stage_b_heavy(sm, lane, warp);
-    else if (warp == 10) fe_w2_stage_b_k10(sm, lane);
+// post_load runs once per warp, after the task's rows of the A planes are in registers (also for warp 11)
+template <class PostLoad>
+FE_HD FE_INLINE void fe_w2_phase_b(float* sm, int lane, int warp, PostLoad post_load) {
+    if (warp == 0) fe_w2_stage_b_k0(sm, lane, post_load);
+    else if (warp < 10) fe_w2_stage_b_heavy(sm, lane, warp, post_load);
+    else if (warp == 10) fe_w2_stage_b_k10(sm, lane, post_load);
+    else post_load();
 }
+FE_HD FE_INLINE void fe_w2_phase_b(float* sm, int lane, int warp) { fe_w2_phase_b(sm, lane, warp, FeNoHook()); }
 
 // ---------------------------------------------------------------- phase M
 FE_HD FE_INLINE float fe_max3(float a, float b, float c) {
@@ -266,11 +332,12 @@ FE_HD FE_INLINE float* fe_row_ptr(float* base, unsigned row_bytes, unsigned m) {
     return reinterpret_cast<float*>(reinterpret_cast<char*>(base) + (size_t)row_bytes * m);
 #endif
 }
-// global stores through a pointer built by fe_row_ptr (keeps the address space: STG, not generic ST)
+// global stores through a pointer built by fe_row_ptr: STG instead of a generic ST, and no "memory" clobber --
+// the output is write-only for this kernel, so shared-memory loads of the next filter may move above the store
 template <int BYTE_OFF>
 FE_HD FE_INLINE void fe_stg(float* q, float v) {
 #if defined(__CUDA_ARCH__)
-    asm volatile("st.global.f32 [%0+%1], %2;" ::"l"(q), "n"(BYTE_OFF), "f"(v) : "memory");
+    asm volatile("st.global.f32 [%0+%1], %2;" ::"l"(q), "n"(BYTE_OFF), "f"(v));
 #else
     *reinterpret_cast<float*>(reinterpret_cast<char*>(q) + BYTE_OFF) = v;
 #endif
@@ -287,13 +354,67 @@ FE_HD FE_INLINE float fe_w2_lg2(float v) {
 // Writes y = (log10(mel) + 4) / 4 for the live frames of the pair (NO floor, NO clamp: both are applied by
 // the fix-up pass, which only touches units whose minimum needs them) and returns this thread's (min, max)
 // over them; dead frames carry NaN through min/max (max.f32 / min.f32 return the non-NaN operand).
+// Rolled form: the warp's filters are sorted into four classes by tap count (caps 2, 4, 8, CAP3; zero-padded),
+// each class is a branch-free loop over descriptors in shared memory (generated/fe_tables.h: fe_melloop_*).
+// The fully unrolled projection was ~2100 instructions -- with the FFT codelets far beyond the 32 KB
+// instruction cache, and every warp ran a different part of it: the whole kernel starved on instruction fetch.
+struct FeW2MelCtx {
+    const char* Pl;      // this lane's row of power pairs
+    const char* wtab;    // padded weights (shared memory)
+    const int2* desc;    // descriptors (shared memory)
+    float* obase;        // out + clip offset + first frame of the pair
+    unsigned rs4;        // output row pitch in bytes
+    fe2 one;             // 1 for live frames, NaN for dead ones
+    bool la, lb;
+    float mn, mx;
+};
+
+template <int CAP>
+FE_HD FE_INLINE void fe_w2_mel_class(FeW2MelCtx& c, int i0, int i1) {
+    typedef FeW2Cfg C;
+#pragma unroll(CAP <= 4 ? 4 : 2)
+    for (int i = i0; i < i1; ++i) {
+        const int2 d = c.desc[i];
+        const fe2* __restrict__ P = reinterpret_cast<const fe2*>(c.Pl + (d.x & 0xffff));
+        float w[CAP];
+        if (CAP == 2) {
+            const float2 v = *reinterpret_cast<const float2*>(c.wtab + d.y);
+            w[0] = v.x; w[1] = v.y;
+        } else {
+            const float4* __restrict__ w4 = reinterpret_cast<const float4*>(c.wtab + d.y);
+#pragma unroll
+            for (int j = 0; j < CAP / 4; ++j) {
+                const float4 v = w4[j];
+                w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
+            }
+        }
+        fe2 acc = fe_mulc(w[0], P[0]);
+        fe2 acc2 = fe_mulc(w[1], P[1]);                  // two chains: half the dependent latency
+#pragma unroll
+        for (int j = 2; j < CAP; j += 2) {
+            acc = fe_fmac(w[j], P[j], acc);
+            acc2 = fe_fmac(w[j + 1], P[j + 1], acc2);
+        }
+        acc = fe_add(acc, acc2);
+        const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(acc.x), fe_w2_lg2(acc.y)), c.one);   // (log10(v) + 4) / 4
+        float* o = fe_row_ptr(c.obase, c.rs4, (unsigned)d.x >> 16);
+#ifndef FE_W2_EXP_NOSTG
+        if (c.la) fe_stg<0>(o, y.x);
+        if (c.lb) fe_stg<4 * C::LANES>(o, y.y);
+#endif
+        c.mx = fe_max3(c.mx, y.x, y.y);
+        c.mn = fe_min3(c.mn, y.x, y.y);
+    }
+}
+
+#ifdef FE_W2_MEL_UNROLLED
 template <int NMELS>
 FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
     typedef FeW2Cfg C;
     const int fa = t.t0 + lane, fb = fa + C::LANES;
     const bool la = fa < t.T, lb = fb < t.T;
     float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + fa;
-    const unsigned rs4 = (unsigned)p.T_out * 4u;   // row pitch in bytes; the host guarantees T_out < 2^24
+    const unsigned rs4 = (unsigned)p.T_out * 4u;
     const fe2* __restrict__ P = reinterpret_cast<const fe2*>(sm + C::OFF_P) + C::PSZ * lane;
     union { unsigned u; float f; } qnan;
     qnan.u = 0x7fc00000u;
@@ -303,8 +424,7 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     int qm = 0;
     auto ld = [&](int k) -> fe2 { return P[k]; };
     auto emit = [&](int m, fe2 v) {
-        const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(v.x), fe_w2_lg2(v.y)), one);   // (log10(v) + 4) / 4
-        // rows of a chunk are consecutive: after the first one this is a 64-bit add of the row pitch
+        const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(v.x), fe_w2_lg2(v.y)), one);
         q = reinterpret_cast<float*>(reinterpret_cast<char*>(q) + (size_t)rs4 * (unsigned)(m - qm));
         qm = m;
         if (la) q[0] = y.x;
@@ -312,13 +432,36 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
         mx = fe_max3(mx, y.x, y.y);
         mn = fe_min3(mn, y.x, y.y);
     };
-    constexpr int NCH = (NMELS == 80) ? FE_MELPROJ_W80_NCHUNK : FE_MELPROJ_W128_NCHUNK;
-    for (int c = warp; c < NCH; c += C::NCW) {
-        if (NMELS == 80) fe_melproj_w80<fe2>(c, ld, emit);
-        else fe_melproj_w128<fe2>(c, ld, emit);
-    }
+    if (NMELS == 80) fe_melproj_w80<fe2>(warp, ld, emit);
+    else fe_melproj_w128<fe2>(warp, ld, emit);
     return fe_mk2(mn, mx);
 }
+#else
+template <int NMELS>
+FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
+    typedef FeW2Cfg C;
+    constexpr int CAP3 = NMELS == 80 ? FE_MELLOOP_W80_CAP3 : FE_MELLOOP_W128_CAP3;
+    const int* __restrict__ ranges = (NMELS == 80 ? fe_melloop_w80_ranges : fe_melloop_w128_ranges) + 5 * warp;
+    const int fa = t.t0 + lane, fb = fa + C::LANES;
+    FeW2MelCtx c;
+    c.la = fa < t.T; c.lb = fb < t.T;
+    c.Pl = reinterpret_cast<const char*>(reinterpret_cast<const fe2*>(sm + C::OFF_P) + C::PSZ * lane);
+    c.wtab = reinterpret_cast<const char*>(sm + C::OFF_MW);
+    c.desc = reinterpret_cast<const int2*>(sm + C::OFF_MDESC);
+    c.obase = p.out + (int64_t)t.b * p.out_batch_stride + fa;
+    c.rs4 = (unsigned)p.T_out * 4u;                // row pitch in bytes; the host guarantees T_out < 2^24
+    union { unsigned u; float f; } qnan;
+    qnan.u = 0x7fc00000u;
+    c.one = fe_mk2(c.la ? 1.0f : qnan.f, c.lb ? 1.0f : qnan.f);
+    c.mn = 3.0e38f; c.mx = -3.0e38f;
+    const int r0 = ranges[0], r1 = ranges[1], r2 = ranges[2], r3 = ranges[3], r4 = ranges[4];
+    fe_w2_mel_class<2>(c, r0, r1);
+    fe_w2_mel_class<4>(c, r1, r2);
+    fe_w2_mel_class<8>(c, r2, r3);
+    fe_w2_mel_class<CAP3>(c, r3, r4);
+    return fe_mk2(c.mn, c.mx);
+}
+#endif
 
 // ---------------------------------------------------------------- fix-up (second kernel)
 // Floor and clamp in the y = (x + 4) / 4 domain, with x = log10(mel) un-floored:

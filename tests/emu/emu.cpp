@@ -14,6 +14,7 @@ template <int NMELS>
 static void run_whisper(const FeWhisper2Params& p) {
     typedef FeW2Cfg C;
     std::vector<float> sm(C::SMEM_FLOATS);
+    fe_w2_copy_tables<NMELS>(sm.data(), 0, 1);
     for (int u = 0; u < p.total_units; ++u) {
         const FeW2Unit t = fe_w2_unit(p, u);
         float mn = 3.0e38f, mx = -3.0e38f;

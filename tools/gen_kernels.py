@@ -78,7 +78,10 @@ def flit(v):
 
 
 def emit_array(name, arr, per_line=8, ctype="float"):
-    flat = [flit(v) for v in np.asarray(arr).reshape(-1)]
+    if ctype == "int":
+        flat = [str(int(v)) for v in np.asarray(arr).reshape(-1)]
+    else:
+        flat = [flit(v) for v in np.asarray(arr).reshape(-1)]
     lines = [f"FE_CONSTANT {ctype} {name}[{len(flat)}] = {{"]
     for i in range(0, len(flat), per_line):
         lines.append("    " + ", ".join(flat[i:i + per_line]) + ",")
@@ -210,6 +213,69 @@ def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
     return "\n".join(out) + "\n"
 
 
+def gen_melloop(name, filt, nch, n_bins=200, emit_cost=17, chunk_weight=None):
+    """tables for the rolled mel projection of the Whisper frame-pair kernel.  (The fully unrolled form does
+    not fit the instruction cache next to the FFT codelets.)  Filters are sorted into classes by tap count,
+    caps (2, 4, 8, round_up(max, 4)); a filter is zero-padded to its cap, so each class is a branch-free loop:
+      name_desc[2*i]   = 8 * k0 | m << 16   (byte offset of the first tap in a row of power pairs, mel row)
+      name_desc[2*i+1] = 4 * off            (byte offset of the first weight in name_w; 8-byte aligned for
+                                             the 2-tap class, 16-byte aligned otherwise)
+      name_w           = weights, cap per filter
+      name_ranges[5*c + k] = first descriptor of class k in chunk c (k = 4: end of the chunk); descriptors
+                             are ordered chunk by chunk, class by class; a chunk's share of the filters
+                             follows chunk_weight (cost model 2 * cap + emit_cost).  The kernel copies desc
+                             and w to shared memory."""
+    n_mels = filt.shape[0]
+    nmax = max(int(np.count_nonzero(r)) for r in filt)
+    caps = [2, 4, 8, (max(nmax, 9) + 3) // 4 * 4]
+    info = []
+    for m in range(n_mels):
+        nz = np.nonzero(filt[m])[0]
+        if len(nz) == 0:
+            k0, n = 0, 0
+        else:
+            k0, n = int(nz[0]), int(nz[-1] - nz[0] + 1)
+            assert np.all(filt[m, k0:k0 + n] != 0), "taps of a filter must be contiguous"
+        cls = next(i for i, c in enumerate(caps) if n <= c)
+        cap = caps[cls]
+        k0 = min(k0, n_bins - cap)           # padded taps must stay inside the row
+        info.append((m, cls, cap, k0, [float(v) for v in filt[m, k0:k0 + cap]]))
+        assert np.count_nonzero(filt[m, :k0]) == 0 and np.count_nonzero(filt[m, k0 + cap:]) == 0
+    # weighted longest-processing-time assignment of filters to chunks (rows are independent, so a chunk need
+    # not be a contiguous range); chunk_weight[c] = share of the mel work chunk c should carry
+    cw = chunk_weight if chunk_weight is not None else [1.0] * nch
+    assert len(cw) == nch
+    load = [0.0] * nch
+    chunks = [[] for _ in range(nch)]
+    for it in sorted(info, key=lambda t: -(2 * t[2] + emit_cost)):
+        c = min(range(nch), key=lambda q: (load[q] + 2 * it[2] + emit_cost) / cw[q])
+        chunks[c].append(it)
+        load[c] += 2 * it[2] + emit_cost
+    desc, wts, ranges = [], [], []
+    for c in range(nch):
+        chunks[c].sort(key=lambda t: t[0])
+        for cls in range(4):
+            ranges.append(len(desc) // 2)
+            for m, c_, cap, k0, w in chunks[c]:
+                if c_ != cls:
+                    continue
+                while len(wts) % min(cap, 4):
+                    wts.append(0.0)
+                desc += [8 * k0 | (m << 16), 4 * len(wts)]
+                wts += w
+        ranges.append(len(desc) // 2)
+    while len(wts) % 4:
+        wts.append(0.0)
+    out = [f"// rolled mel projection tables, {n_mels} filters, {int(np.count_nonzero(filt))} taps ({sum(i[2] for i in info)} padded), "
+           f"class caps {caps}",
+           f"#define {name.upper()}_CAP3 {caps[3]}",
+           f"#define {name.upper()}_NW {len(wts)}",
+           emit_array(name + "_desc", np.array(desc, dtype=np.int64), per_line=8, ctype="int"),
+           emit_array(name + "_w", np.array(wts, dtype=np.float64)),
+           emit_array(name + "_ranges", np.array(ranges, dtype=np.int64), per_line=5, ctype="int")]
+    return "\n".join(out) + "\n"
+
+
 def twiddle_table(N, rows, cols):
     """float2 table T[row][col] = exp(-2*pi*i*row*col/N), rows x cols."""
     t = np.zeros((rows, cols, 2), dtype=np.float64)
@@ -275,6 +341,13 @@ def main():
     kb = kaldi_banks()
     tb.append(gen_melproj("fe_melproj_w80", w80, 12, 199, epi_cost=8))
     tb.append(gen_melproj("fe_melproj_w128", w128, 12, 199, epi_cost=8))
+    # compute warps 5, 8, 9, 10 run one phase-A task per unit, the others two (fe_w2_a_second): they take
+    # a larger share of the mel projection so that all warps reach the unit's barrier together
+    mel_share = [1.0] * 12
+    for w_ in (5, 8, 9, 10):
+        mel_share[w_] = 1.8
+    tb.append(gen_melloop("fe_melloop_w80", w80, 12, chunk_weight=mel_share))
+    tb.append(gen_melloop("fe_melloop_w128", w128, 12, chunk_weight=mel_share))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     tb.append(gen_melproj("fe_melproj_cosy", cz, 16, 639))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
