@@ -40,9 +40,9 @@ static __device__ __forceinline__ void fe_bar_arrive(int id, int count) {
 // debug build only (tools/trace_w2.py): clock64 stamps of CTA 0's warps at the phase boundaries
 #define FE_TR_UNITS 12
 #define FE_TR_EV 8
-__device__ long long fe_w2_trace_buf[FE_TR_UNITS * 16 * FE_TR_EV];
+__device__ long long fe_w2_trace_buf[FE_TR_UNITS * 20 * FE_TR_EV];
 #define FE_TR(iter, ev) do { if (blockIdx.x == 0 && (unsigned)(iter) < FE_TR_UNITS && lane == 0) \
-    fe_w2_trace_buf[((iter) * 16 + warp) * FE_TR_EV + (ev)] = clock64(); } while (0)
+    fe_w2_trace_buf[((iter) * 20 + warp) * FE_TR_EV + (ev)] = clock64(); } while (0)
 #else
 #define FE_TR(iter, ev) do { } while (0)
 #endif
@@ -159,11 +159,11 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
     // ---- compute warps
     const int u0 = blockIdx.x, du = gridDim.x;
     const int n2b = fe_w2_a_second(warp);
-    // order of the three steps after B, by warp group (every SM sub-partition holds one warp of each group, so its
-    // warps are in different phases: shared-memory bursts, FP32 work and the latency-bound mel loop overlap):
-    //   warps 0-3, 8-11: A1 A2 M     warps 4-7: A1 M A2        (codes: 1 = A1, 2 = M, 3 = A2)
-    // (M before A1 was measured slower: it delays the release of W and with it the loader)
-    const unsigned order = (warp & 4) ? 0x321u : 0x231u;
+    // Order of the steps after B and the first A task, by warp: warps 4-7 run M(u) before their second A(u+1) task,
+    // the others after it.  Every SM sub-partition then holds warps in different phases, so the shared-memory
+    // bursts of one overlap the FP32 work of another and the latency-bound mel loop fills the gaps.  (M before
+    // the first A task was measured slower: it delays the release of W and with it the loader.)
+    const bool m_before_a2 = (warp & 4) != 0;
     FeW2Unit cur;
     cur.b = 0; cur.t0 = 0; cur.T = 0; cur.len = 0; cur.lp = 0;
     // iteration -1 is the prologue: only the A(u0) tasks run (same code as in the steady state)
@@ -178,45 +178,43 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
         FeW2Unit nxt = cur;
         bool live_n = false;
         fe2 mm = fe_mk2(3.0e38f, -3.0e38f);
-#pragma unroll 1
-        for (int step = 0; step < 4; ++step) {
-            // 0: B(u)   then, in the warp's order: 1 = first A(u+1) task, 2 = M(u), 3 = second A(u+1) task
-            const int op = step == 0 ? 0 : (int)((order >> (4 * (step - 1))) & 0xfu);
-            if (op == 0) {
-                if (!first) {
-                    const FeWarpArrive loads_done{mb_bl, lane};
-                    if (live) fe_w2_phase_b(sm, lane, warp, loads_done);
-                    else loads_done();
-                    const FeWarpArrive p_done{mb_pb, lane};
-                    p_done();
-                }
-            } else if (op == 2) {
-                if (!first) {
-                    fe_mbar_wait(mb_pb, parity);
-                    if (live) mm = fe_w2_phase_mel<NMELS>(p, cur, sm, lane, warp);
-                }
-            } else if (has_next) {
-                if (op == 1) {
-                    fe_bar_sync(FE_BAR_W_FULL, C::NT);             // W(next) and its descriptor are in place
-                    const int np = (it + 1) & 1;
-                    nxt.b = misc[4 + 4 * np]; nxt.t0 = misc[5 + 4 * np]; nxt.T = misc[6 + 4 * np];
+        // ---- B(u)
+        if (!first) {
+            const FeWarpArrive loads_done{mb_bl, lane};
+            if (live) fe_w2_phase_b(sm, lane, warp, loads_done);
+            else loads_done();
+            const FeWarpArrive p_done{mb_pb, lane};
+            p_done();
+        }
+        FE_TR(it, 1);
+        // ---- first A(u+1) task
+        if (has_next) {
+            fe_bar_sync(FE_BAR_W_FULL, C::NT);                     // W(next) and its descriptor are in place
+            const int np = (it + 1) & 1;
+            nxt.b = misc[4 + 4 * np]; nxt.t0 = misc[5 + 4 * np]; nxt.T = misc[6 + 4 * np];
 #ifdef FE_W2_NOSYNC
-                    nxt = fe_w2_unit(p, un);
+            nxt = fe_w2_unit(p, un);
 #endif
-                    live_n = nxt.t0 < nxt.T;
-                }
-                const int n2 = op == 1 ? warp : n2b;
-                if (live_n && n2 >= 0) fe_w2_stage_a(sm, lane, n2, FeMbarWait{mb_bl, parity});
-                if (op == 3 && un + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);
+            live_n = nxt.t0 < nxt.T;
+            if (live_n) fe_w2_stage_a(sm, lane, warp, FeMbarWait{mb_bl, parity});
+        }
+        FE_TR(it, 2);
+        // ---- M(u) and the second A(u+1) task, in the warp's order (one call site each)
+#pragma unroll 1
+        for (int k = 0; k < 2; ++k) {
+            if ((k == 1) == m_before_a2 && has_next) {
+                if (live_n && n2b >= 0) fe_w2_stage_a(sm, lane, n2b, FeMbarWait{mb_bl, parity});
+                if (un + du < p.total_units) fe_bar_arrive(FE_BAR_W_FREE, C::NT);   // last read of W(next)
             }
-            FE_TR(it, 1 + step);
+            if (k == 0 && !first) {
+                fe_mbar_wait(mb_pb, parity);
+                if (live) mm = fe_w2_phase_mel<NMELS>(p, cur, sm, lane, warp);
+            }
+            FE_TR(it, 3 + k);
         }
         int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
-            kmin = max(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
-        }
+        kmax = __reduce_max_sync(0xffffffffu, kmax);
+        kmin = __reduce_max_sync(0xffffffffu, kmin);
         if (lane == 0) { atomicMax(misc + 0, kmax); atomicMax(misc + 1, kmin); }
         FE_TR(it, 5);
         fe_bar_sync(FE_BAR_COMPUTE, C::NCT);                   // P(u) consumed, A(next) complete, keys final
@@ -421,7 +419,7 @@ int64_t b200feat_launch_count(void) { return g_launches.load(); }
 
 #ifdef FE_W2_TRACE
 int b200feat_debug_trace(long long* host_out) {
-    return (int)cudaMemcpyFromSymbol(host_out, fe_w2_trace_buf, sizeof(long long) * FE_TR_UNITS * 16 * FE_TR_EV);
+    return (int)cudaMemcpyFromSymbol(host_out, fe_w2_trace_buf, sizeof(long long) * FE_TR_UNITS * 20 * FE_TR_EV);
 }
 #endif
 

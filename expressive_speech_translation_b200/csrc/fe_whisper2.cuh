@@ -53,7 +53,8 @@ struct FeW2Cfg {
     static constexpr int N = 400, HOP = 160, PADL = 200, R = 20;
     static constexpr int LANES = 32, FT = 64;            // frame pairs / frames per unit
     static constexpr int SEG = LANES * HOP;              // sample distance between the frames of a pair (5120)
-    static constexpr int NCW = 12, NLW = 4;              // compute / loader warps
+    static constexpr int NCW = 12, NLW = 4;              // compute / loader warps.  (Measured: 12 + 5 and 15 + 5
+                                                         // warps cap the kernel at 96 registers and are slower.)
     static constexpr int NCT = NCW * 32, NLT = NLW * 32, NT = NCT + NLT;
     static constexpr int RT = (LANES - 1) * HOP + N;     // samples per segment of a unit (5360)
     static constexpr int LS = HOP + 1;                   // lane stride in W (pairs)
@@ -193,6 +194,7 @@ struct FeNoHook { FE_HD FE_INLINE void operator()() const {} };
 //   phase B: warp 0 -> k1 = 0, warps 1..9 -> k1 = warp, warp 10 -> k1 = 10, warp 11 none
 //   phase A: first task n2 = warp; a second task for warps 0-4, 6, 7, 11 (n2 = 12..19), chosen so that the four
 //            SM sub-partitions (warp % 4) carry about the same FP32 work over A + B
+//   phase M: chunk = warp (generated/fe_tables.h: fe_melloop_*_ranges)
 FE_HD FE_INLINE int fe_w2_a_second(int warp) {
     return warp < 5 ? warp + 12 : (warp == 6 ? 17 : (warp == 7 ? 18 : (warp == 11 ? 19 : -1)));
 }
@@ -354,8 +356,8 @@ FE_HD FE_INLINE float fe_w2_lg2(float v) {
 // Writes y = (log10(mel) + 4) / 4 for the live frames of the pair (NO floor, NO clamp: both are applied by
 // the fix-up pass, which only touches units whose minimum needs them) and returns this thread's (min, max)
 // over them; dead frames carry NaN through min/max (max.f32 / min.f32 return the non-NaN operand).
-// Rolled form: the warp's filters are sorted into four classes by tap count (caps 2, 4, 8, CAP3; zero-padded),
-// each class is a branch-free loop over descriptors in shared memory (generated/fe_tables.h: fe_melloop_*).
+// Rolled form: the warp's filters are sorted into classes by tap count (zero-padded to the class cap), each
+// class is a branch-free loop over descriptors in shared memory (generated/fe_tables.h: fe_melloop_*).
 // The fully unrolled projection was ~2100 instructions -- with the FFT codelets far beyond the 32 KB
 // instruction cache, and every warp ran a different part of it: the whole kernel starved on instruction fetch.
 struct FeW2MelCtx {
@@ -372,30 +374,34 @@ struct FeW2MelCtx {
 template <int CAP>
 FE_HD FE_INLINE void fe_w2_mel_class(FeW2MelCtx& c, int i0, int i1) {
     typedef FeW2Cfg C;
-#pragma unroll(CAP <= 4 ? 4 : 2)
+#pragma unroll(CAP <= 2 ? 4 : 2)
     for (int i = i0; i < i1; ++i) {
         const int2 d = c.desc[i];
         const fe2* __restrict__ P = reinterpret_cast<const fe2*>(c.Pl + (d.x & 0xffff));
-        float w[CAP];
-        if (CAP == 2) {
+        float w[(CAP + 3) / 4 * 4];
+        if (CAP == 1) {
+            w[0] = *reinterpret_cast<const float*>(c.wtab + d.y);
+        } else if (CAP == 2) {
             const float2 v = *reinterpret_cast<const float2*>(c.wtab + d.y);
             w[0] = v.x; w[1] = v.y;
         } else {
             const float4* __restrict__ w4 = reinterpret_cast<const float4*>(c.wtab + d.y);
 #pragma unroll
-            for (int j = 0; j < CAP / 4; ++j) {
+            for (int j = 0; j < (CAP + 3) / 4; ++j) {
                 const float4 v = w4[j];
                 w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
             }
         }
         fe2 acc = fe_mulc(w[0], P[0]);
-        fe2 acc2 = fe_mulc(w[1], P[1]);                  // two chains: half the dependent latency
+        if (CAP > 1) {
+            fe2 acc2 = fe_mulc(w[1], P[1]);              // two chains: half the dependent latency
 #pragma unroll
-        for (int j = 2; j < CAP; j += 2) {
-            acc = fe_fmac(w[j], P[j], acc);
-            acc2 = fe_fmac(w[j + 1], P[j + 1], acc2);
+            for (int j = 2; j < CAP; ++j) {
+                if (j & 1) acc2 = fe_fmac(w[j], P[j], acc2);
+                else acc = fe_fmac(w[j], P[j], acc);
+            }
+            acc = fe_add(acc, acc2);
         }
-        acc = fe_add(acc, acc2);
         const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(acc.x), fe_w2_lg2(acc.y)), c.one);   // (log10(v) + 4) / 4
         float* o = fe_row_ptr(c.obase, c.rs4, (unsigned)d.x >> 16);
 #ifndef FE_W2_EXP_NOSTG
@@ -406,6 +412,28 @@ FE_HD FE_INLINE void fe_w2_mel_class(FeW2MelCtx& c, int i0, int i1) {
         c.mn = fe_min3(c.mn, y.x, y.y);
     }
 }
+
+// class caps of the generated tables, and the compile-time walk over the classes
+template <int NMELS> struct FeW2MelCaps;
+template <> struct FeW2MelCaps<80> {
+    static constexpr int N = FE_MELLOOP_W80_NCLS;
+    static FE_HD constexpr int cap(int k) { constexpr int c[N] = {FE_MELLOOP_W80_CAPS}; return c[k]; }
+};
+template <> struct FeW2MelCaps<128> {
+    static constexpr int N = FE_MELLOOP_W128_NCLS;
+    static FE_HD constexpr int cap(int k) { constexpr int c[N] = {FE_MELLOOP_W128_CAPS}; return c[k]; }
+};
+template <int NMELS, int K, bool END = (K == FeW2MelCaps<NMELS>::N)>
+struct FeW2MelRun {
+    static FE_HD FE_INLINE void run(FeW2MelCtx& c, const int* r) {
+        fe_w2_mel_class<FeW2MelCaps<NMELS>::cap(K)>(c, r[K], r[K + 1]);
+        FeW2MelRun<NMELS, K + 1>::run(c, r);
+    }
+};
+template <int NMELS, int K>
+struct FeW2MelRun<NMELS, K, true> {
+    static FE_HD FE_INLINE void run(FeW2MelCtx&, const int*) {}
+};
 
 #ifdef FE_W2_MEL_UNROLLED
 template <int NMELS>
@@ -440,8 +468,8 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
 template <int NMELS>
 FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
     typedef FeW2Cfg C;
-    constexpr int CAP3 = NMELS == 80 ? FE_MELLOOP_W80_CAP3 : FE_MELLOOP_W128_CAP3;
-    const int* __restrict__ ranges = (NMELS == 80 ? fe_melloop_w80_ranges : fe_melloop_w128_ranges) + 5 * warp;
+    constexpr int NCLS = FeW2MelCaps<NMELS>::N;
+    const int* __restrict__ ranges = (NMELS == 80 ? fe_melloop_w80_ranges : fe_melloop_w128_ranges) + (NCLS + 1) * warp;
     const int fa = t.t0 + lane, fb = fa + C::LANES;
     FeW2MelCtx c;
     c.la = fa < t.T; c.lb = fb < t.T;
@@ -454,11 +482,10 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     qnan.u = 0x7fc00000u;
     c.one = fe_mk2(c.la ? 1.0f : qnan.f, c.lb ? 1.0f : qnan.f);
     c.mn = 3.0e38f; c.mx = -3.0e38f;
-    const int r0 = ranges[0], r1 = ranges[1], r2 = ranges[2], r3 = ranges[3], r4 = ranges[4];
-    fe_w2_mel_class<2>(c, r0, r1);
-    fe_w2_mel_class<4>(c, r1, r2);
-    fe_w2_mel_class<8>(c, r2, r3);
-    fe_w2_mel_class<CAP3>(c, r3, r4);
+    int r[NCLS + 1];
+#pragma unroll
+    for (int k = 0; k <= NCLS; ++k) r[k] = ranges[k];
+    FeW2MelRun<NMELS, 0>::run(c, r);
     return fe_mk2(c.mn, c.mx);
 }
 #endif

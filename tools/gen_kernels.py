@@ -213,21 +213,22 @@ def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
     return "\n".join(out) + "\n"
 
 
-def gen_melloop(name, filt, nch, n_bins=200, emit_cost=17, chunk_weight=None):
+def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=None):
     """tables for the rolled mel projection of the Whisper frame-pair kernel.  (The fully unrolled form does
-    not fit the instruction cache next to the FFT codelets.)  Filters are sorted into classes by tap count,
-    caps (2, 4, 8, round_up(max, 4)); a filter is zero-padded to its cap, so each class is a branch-free loop:
+    not fit the instruction cache next to the FFT codelets.)  Filters are sorted into classes by tap count
+    (`caps`, ascending); a filter is zero-padded to the cap of its class, so each class is a branch-free loop:
       name_desc[2*i]   = 8 * k0 | m << 16   (byte offset of the first tap in a row of power pairs, mel row)
-      name_desc[2*i+1] = 4 * off            (byte offset of the first weight in name_w; 8-byte aligned for
-                                             the 2-tap class, 16-byte aligned otherwise)
+      name_desc[2*i+1] = 4 * off            (byte offset of the first weight in name_w; 4- / 8-byte aligned for
+                                             the 1- / 2-tap classes, 16-byte aligned otherwise)
       name_w           = weights, cap per filter
-      name_ranges[5*c + k] = first descriptor of class k in chunk c (k = 4: end of the chunk); descriptors
+      name_ranges[(NCLS+1)*c + k] = first descriptor of class k in chunk c (k = NCLS: end of the chunk); descriptors
                              are ordered chunk by chunk, class by class; a chunk's share of the filters
                              follows chunk_weight (cost model 2 * cap + emit_cost).  The kernel copies desc
                              and w to shared memory."""
     n_mels = filt.shape[0]
     nmax = max(int(np.count_nonzero(r)) for r in filt)
-    caps = [2, 4, 8, (max(nmax, 9) + 3) // 4 * 4]
+    ncls = len(caps)
+    assert caps[-1] >= nmax and list(caps) == sorted(caps)
     info = []
     for m in range(n_mels):
         nz = np.nonzero(filt[m])[0]
@@ -254,25 +255,27 @@ def gen_melloop(name, filt, nch, n_bins=200, emit_cost=17, chunk_weight=None):
     desc, wts, ranges = [], [], []
     for c in range(nch):
         chunks[c].sort(key=lambda t: t[0])
-        for cls in range(4):
+        for cls in range(ncls):
             ranges.append(len(desc) // 2)
             for m, c_, cap, k0, w in chunks[c]:
                 if c_ != cls:
                     continue
-                while len(wts) % min(cap, 4):
+                walign = 1 if cap == 1 else (2 if cap == 2 else 4)     # 32- / 64- / 128-bit weight loads
+                while len(wts) % walign:
                     wts.append(0.0)
                 desc += [8 * k0 | (m << 16), 4 * len(wts)]
-                wts += w
+                wts += w + [0.0] * ((-cap) % walign)
         ranges.append(len(desc) // 2)
     while len(wts) % 4:
         wts.append(0.0)
     out = [f"// rolled mel projection tables, {n_mels} filters, {int(np.count_nonzero(filt))} taps ({sum(i[2] for i in info)} padded), "
            f"class caps {caps}",
-           f"#define {name.upper()}_CAP3 {caps[3]}",
+           f"#define {name.upper()}_NCLS {ncls}",
+           f"#define {name.upper()}_CAPS {', '.join(str(c) for c in caps)}",
            f"#define {name.upper()}_NW {len(wts)}",
            emit_array(name + "_desc", np.array(desc, dtype=np.int64), per_line=8, ctype="int"),
            emit_array(name + "_w", np.array(wts, dtype=np.float64)),
-           emit_array(name + "_ranges", np.array(ranges, dtype=np.int64), per_line=5, ctype="int")]
+           emit_array(name + "_ranges", np.array(ranges, dtype=np.int64), per_line=ncls + 1, ctype="int")]
     return "\n".join(out) + "\n"
 
 
@@ -346,8 +349,8 @@ def main():
     mel_share = [1.0] * 12
     for w_ in (5, 8, 9, 10):
         mel_share[w_] = 1.8
-    tb.append(gen_melloop("fe_melloop_w80", w80, 12, chunk_weight=mel_share))
-    tb.append(gen_melloop("fe_melloop_w128", w128, 12, chunk_weight=mel_share))
+    tb.append(gen_melloop("fe_melloop_w80", w80, 12, (2, 3, 4, 6, 8, 11, 14), chunk_weight=mel_share))
+    tb.append(gen_melloop("fe_melloop_w128", w128, 12, (1, 2, 3, 4, 6, 7, 9), chunk_weight=mel_share))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     tb.append(gen_melproj("fe_melproj_cosy", cz, 16, 639))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:

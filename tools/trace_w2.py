@@ -11,7 +11,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "expressive_speech_translation_b200")
 LIB = os.environ.get("TR_LIB", os.path.join(PKG, "lib", "libb200feat_trace.so"))
-UNITS, WARPS, EV = 12, 16, 8
+UNITS, WARPS, EV = 12, 20, 8  # 20 = trace slots per iteration (>= warps)
 
 if sys.argv[1] == "build":
     cmd = ["nvcc", "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-DFE_W2_TRACE",
@@ -58,8 +58,7 @@ lines = []
 
 
 def ops(w):
-    a2_first = True
-    return ["B", "A1", "A2" if a2_first else "M", "M" if a2_first else "A2", "keys", "bar"]
+    return ["B", "A1", "A2+M" if not (w & 4) else "M", "-" if not (w & 4) else "A2", "keys", "bar"]
 
 
 for it in range(2, 8):
