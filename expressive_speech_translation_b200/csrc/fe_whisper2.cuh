@@ -157,21 +157,50 @@ FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
     }
 }
 
-// edge units (reflect / zero padding, ragged ends, unaligned rows): element-wise, after W is free
+// edge units (reflect / zero padding, ragged ends): element-wise, after W is free.  One sample of each segment
+// per step like the fast path (coalesced reads, conflict-free pair slots), issued as 4-byte cp.async so that the
+// copies of the whole unit are in flight at once (a rolled loop of dependent loads would pay the HBM latency
+// 42 times); samples beyond the clip are zero-filled by a zero source size.
+template <class I>
+FE_HD FE_INLINE I fe_w2_reflect(I g, I lp) {
+    if (g < 0) g = -g;
+    if (g >= lp) g = 2 * (lp - 1) - g;
+    if (g < 0) g = 0;               // degenerate clips shorter than the pad: stay in bounds
+    if (g >= lp) g = lp - 1;
+    return g;
+}
+
+template <class I>
+FE_HD FE_INLINE void fe_w2_load_edge_t(const float* __restrict__ x, I g0, I len, I lp, float* sm, int ltid) {
+    typedef FeW2Cfg C;
+    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
+#if defined(__CUDA_ARCH__)
+    const unsigned w0 = (unsigned)__cvta_generic_to_shared(w);
+#pragma unroll 1
+    for (int i = ltid; i < C::RT; i += C::NLT) {
+        const unsigned d = w0 + 8u * (unsigned)(i + i / C::HOP);
+        const I ga = fe_w2_reflect<I>(g0 + i, lp), gb = fe_w2_reflect<I>(g0 + C::SEG + i, lp);
+        const unsigned na = ga < len ? 4u : 0u, nb = gb < len ? 4u : 0u;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(x + (na ? ga : 0)), "r"(na) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d + 4u), "l"(x + (nb ? gb : 0)), "r"(nb) : "memory");
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+#else
+    for (int i = ltid; i < C::RT; i += C::NLT) {
+        const I ga = fe_w2_reflect<I>(g0 + i, lp), gb = fe_w2_reflect<I>(g0 + C::SEG + i, lp);
+        w[i + i / C::HOP] = fe_mk2(ga < len ? x[ga] : 0.0f, gb < len ? x[gb] : 0.0f);
+    }
+#endif
+}
+
 FE_HD FE_INLINE void fe_w2_load_edge(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
     typedef FeW2Cfg C;
-    constexpr int NQ = C::RT / 4;
-    constexpr int QPB = C::HOP / 4;
     const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
     const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
-    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
-    for (int q = ltid; q < NQ; q += C::NLT) {
-        const int64_t g = g0 + 4 * q;
-        fe2* d = w + 4 * q + q / QPB;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            d[j] = fe_mk2(fe_fetch_reflect(x, g + j, t.len, t.lp), fe_fetch_reflect(x, g + C::SEG + j, t.len, t.lp));
-    }
+    if (t.lp < ((int64_t)1 << 30) && g0 < ((int64_t)1 << 30))
+        fe_w2_load_edge_t<int>(x, (int)g0, (int)t.len, (int)t.lp, sm, ltid);
+    else
+        fe_w2_load_edge_t<int64_t>(x, g0, t.len, t.lp, sm, ltid);
 }
 
 // copies the constant tables into shared memory; every thread of the CTA calls it, a barrier must follow
