@@ -232,29 +232,49 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
 
 // Fix-up: clamps the units whose minimum lies below max - 8 decades (y < ymax - 2) and zero-fills the
 // frames past a ragged clip's own end.  Everything else is left untouched (one trip to HBM).
+// One thread checks one unit (coalesced read of its (min, max)); the units that need work -- few or none for
+// noise-like audio of full length -- are then rewritten by the whole CTA, one after the other.
 template <int NMELS>
 __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2Params p) {
     typedef FeW2Cfg C;
-    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
-        const FeW2Unit t = fe_w2_unit(p, u);
-        int n_in = (int)(p.T_out - t.t0 < C::FT ? p.T_out - t.t0 : C::FT);
-        int n_live = t.T - t.t0;
-        n_live = n_live < 0 ? 0 : (n_live > C::FT ? C::FT : n_live);
-        const float2 mm = p.unit_minmax[u];
-        const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
-        const bool clampu = n_live > 0 && mm.x < thr;
-        if (!clampu && n_live >= n_in) continue;
-        float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + t.t0;
-        for (int i = threadIdx.x; i < NMELS * C::FT; i += blockDim.x) {
-            const int m = i / C::FT, c = i % C::FT;
-            if (c >= n_in) continue;
-            float* q = o + (int64_t)m * p.T_out + c;
-            if (c >= n_live) *q = 0.0f;
-            else if (clampu) {
-                const float v = *q;
-                if (v < thr) *q = thr;
+    __shared__ int list[256];
+    __shared__ int count;
+    for (int base = blockIdx.x * blockDim.x; base < p.total_units; base += gridDim.x * blockDim.x) {
+        if (threadIdx.x == 0) count = 0;
+        __syncthreads();
+        const int u = base + threadIdx.x;
+        if (u < p.total_units) {
+            const FeW2Unit t = fe_w2_unit(p, u);
+            const int n_in = (int)(p.T_out - t.t0 < C::FT ? p.T_out - t.t0 : C::FT);
+            const int n_live = t.T - t.t0;
+            const float2 mm = p.unit_minmax[u];
+            const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
+            if ((n_live > 0 && mm.x < thr) || n_live < n_in) list[atomicAdd(&count, 1)] = u;
+        }
+        __syncthreads();
+        const int n = count;
+        for (int j = 0; j < n; ++j) {
+            const int uu = list[j];
+            const FeW2Unit t = fe_w2_unit(p, uu);
+            const int n_in = (int)(p.T_out - t.t0 < C::FT ? p.T_out - t.t0 : C::FT);
+            int n_live = t.T - t.t0;
+            n_live = n_live < 0 ? 0 : (n_live > C::FT ? C::FT : n_live);
+            const float2 mm = p.unit_minmax[uu];
+            const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
+            const bool clampu = n_live > 0 && mm.x < thr;
+            float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + t.t0;
+            for (int i = threadIdx.x; i < NMELS * C::FT; i += blockDim.x) {
+                const int m = i / C::FT, c = i % C::FT;
+                if (c >= n_in) continue;
+                float* q = o + (int64_t)m * p.T_out + c;
+                if (c >= n_live) *q = 0.0f;
+                else if (clampu) {
+                    const float v = *q;
+                    if (v < thr) *q = thr;
+                }
             }
         }
+        __syncthreads();
     }
 }
 
@@ -529,7 +549,9 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
         g_launches++;
     }
     {
-        const unsigned grid = (unsigned)(p.total_units < sms * 8 ? p.total_units : sms * 8);
+        // 64 units per CTA-pass would leave most SMs idle for small batches: spread the checks over all SMs
+        const int need = (p.total_units + 255) / 256;
+        const unsigned grid = (unsigned)(need < sms * 8 ? need : sms * 8);
         ProfScope ps(st, 1);
         if (n_mels == 80) fe_whisper2_fixup_kernel<80><<<grid, 256, 0, st>>>(p);
         else fe_whisper2_fixup_kernel<128><<<grid, 256, 0, st>>>(p);

@@ -68,14 +68,13 @@ struct FeW2Cfg {
     static constexpr int OFF_MISC = OFF_P + LANES * PSZ * 2; // ints: [0] max key [1] min key [4..7], [8..11] unit info
     static constexpr int OFF_MBAR = OFF_MISC + 12;           // two 8-byte mbarriers: [0] "B(u) has read its rows of
                                                              // the A planes", [1] "P(u) is complete"
-    // constant tables, copied once per CTA (register-indexed constant loads are far too slow for the hot loops):
-    static constexpr int OFF_TABA = OFF_MISC + 16;           // fe_w2_tab: [n2][window(20) | twiddles(20)]
-    static constexpr int OFF_MDESC = OFF_TABA + 800;         // fe_melloop_*_desc (2 ints per filter, <= 128 filters)
+    // mel tables, copied once per CTA (the mel loop reads them with per-filter offsets):
+    static constexpr int OFF_MDESC = OFF_MISC + 16;          // fe_melloop_*_desc (2 ints per filter, <= 128 filters)
     static constexpr int OFF_MW = OFF_MDESC + 256;           // fe_melloop_*_w (padded taps)
     static constexpr int MW_MAX = 576;
     static constexpr int SMEM_FLOATS = OFF_MW + MW_MAX;
     static_assert(OFF_MBAR % 2 == 0, "mbarriers need 8-byte alignment");
-    static_assert(OFF_TABA % 4 == 0 && OFF_MW % 4 == 0, "tables are read with 128-bit loads");
+    static_assert(OFF_MDESC % 4 == 0 && OFF_MW % 4 == 0, "tables are read with 128-bit loads");
     static_assert(SMEM_FLOATS * 4 <= 232448, "more than 227 KB of shared memory");
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
     static constexpr float LOG_SCALE = 0.07525749891599530f;  // log10(2) / 4
@@ -211,7 +210,6 @@ FE_HD FE_INLINE void fe_w2_copy_tables(float* sm, int tid, int nthreads) {
     const int* __restrict__ desc = NMELS == 80 ? fe_melloop_w80_desc : fe_melloop_w128_desc;
     const float* __restrict__ w = NMELS == 80 ? fe_melloop_w80_w : fe_melloop_w128_w;
     const int nw = NMELS == 80 ? FE_MELLOOP_W80_NW : FE_MELLOOP_W128_NW;
-    for (int i = tid; i < 800; i += nthreads) sm[C::OFF_TABA + i] = fe_w2_tab[i];
     int* d = reinterpret_cast<int*>(sm + C::OFF_MDESC);
     for (int i = tid; i < 2 * NMELS; i += nthreads) d[i] = desc[i];
     for (int i = tid; i < nw; i += nthreads) sm[C::OFF_MW + i] = w[i];
@@ -234,15 +232,9 @@ template <class PreStore>
 FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2, PreStore pre_store) {
     typedef FeW2Cfg C;
     const fe2* __restrict__ s = reinterpret_cast<const fe2*>(sm) + C::LS * lane + n2;
-    float tab[40];   // this task's window and twiddles: ten 128-bit broadcast loads
-    {
-        const float4* __restrict__ t4 = reinterpret_cast<const float4*>(sm + C::OFF_TABA + 40 * n2);
-#pragma unroll
-        for (int i = 0; i < 10; ++i) {
-            const float4 v = t4[i];
-            tab[4 * i] = v.x; tab[4 * i + 1] = v.y; tab[4 * i + 2] = v.z; tab[4 * i + 3] = v.w;
-        }
-    }
+    // window and twiddles of this task: constant bank (register-indexed LDC.64; measured faster here than a
+    // shared-memory copy, which costs ~200 wavefronts of the already busy shared-memory pipe per unit)
+    const float* __restrict__ tab = fe_w2_tab + 40 * n2;
     fe2 x[C::R];
 #pragma unroll
     for (int n1 = 0; n1 < C::R; ++n1) {
