@@ -149,6 +149,11 @@ FE_HD FE_INLINE void fe_w2_load_issue(const FeWhisper2Params& p, const FeW2Unit&
 FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
     typedef FeW2Cfg C;
     fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
+#if defined(__CUDA_ARCH__)
+    // the slot offsets depend on ltid only: without this the compiler keeps all 42 of them in registers across
+    // the persistent loop, next to the 84 staging registers, and spills
+    asm volatile("" : "+r"(ltid));
+#endif
 #pragma unroll
     for (int j = 0; j < FeW2Stage::U; ++j) {
         const unsigned i = (unsigned)(ltid + j * C::NLT);
