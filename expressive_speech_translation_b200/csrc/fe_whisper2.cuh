@@ -148,16 +148,21 @@ FE_HD FE_INLINE void fe_w2_load_issue(const FeWhisper2Params& p, const FeW2Unit&
 
 FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
     typedef FeW2Cfg C;
+    // sample i = ltid + NLT * j sits in slot i + i / HOP.  NLT * 5 = 4 * HOP, so for j = 5 * m + c the slot is
+    // base_c + (4 * HOP + 4) * m with base_c = i_c + i_c / HOP, i_c = ltid + NLT * c: five bases per thread, every
+    // other offset is an immediate
+    static_assert(C::NLT * 5 == 4 * C::HOP, "slot arithmetic of the loader");
     fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
-#if defined(__CUDA_ARCH__)
-    // the slot offsets depend on ltid only: without this the compiler keeps all 42 of them in registers across
-    // the persistent loop, next to the 84 staging registers, and spills
-    asm volatile("" : "+r"(ltid));
-#endif
+    fe2* base[5];
+#pragma unroll
+    for (int c = 0; c < 5; ++c) {
+        const unsigned ic = (unsigned)(ltid + C::NLT * c);
+        base[c] = w + ic + ic / (unsigned)C::HOP;
+    }
 #pragma unroll
     for (int j = 0; j < FeW2Stage::U; ++j) {
-        const unsigned i = (unsigned)(ltid + j * C::NLT);
-        if (j + 1 < FeW2Stage::U || i < (unsigned)C::RT) w[i + i / (unsigned)C::HOP] = fe_mk2(r.a[j], r.b[j]);
+        if (j + 1 < FeW2Stage::U || ltid + j * C::NLT < C::RT)
+            base[j % 5][(4 * C::HOP + 4) * (j / 5)] = fe_mk2(r.a[j], r.b[j]);
     }
 }
 
