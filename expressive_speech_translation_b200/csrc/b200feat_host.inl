@@ -49,7 +49,8 @@ size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 int64_t host_chunk_bytes() {
     static const int64_t v = [] {
         const char* s = getenv("B200FEAT_HOST_CHUNK_MB");
-        int64_t mb = s ? atoll(s) : 16;
+        int64_t mb = s ? atoll(s) : 64;   // measured on B200 / PCIe 5 x16 (tools/e2e_sweep.py): 16 MB 46.8 ms, 64 MB 38.6 ms per
+                                          // 1024 x 30 s step; smaller chunks leave the kernels with too few units per launch
         if (mb < 1) mb = 1;
         return mb << 20;
     }();
