@@ -59,11 +59,10 @@ struct FeW2Cfg {
     static constexpr int RT = (LANES - 1) * HOP + N;     // samples per segment of a unit (5360)
     static constexpr int LS = HOP + 1;                   // lane stride in W (pairs)
     static constexpr int SW = RT + RT / HOP + 3;         // padded W (pairs)
-    static constexpr int FS = 221;                       // pairs per lane in each A plane (11*20 + 1 -> odd)
+    static constexpr int FS = 221;                       // (re pair, im pair) elements per lane in A (11*20 + 1 -> odd)
     static constexpr int PSZ = 201;                      // pairs per lane in P (200 bins + 1 -> odd)
-    static constexpr int OFF_AR = SW * 2;                // in floats: real plane
-    static constexpr int OFF_AI = OFF_AR + LANES * FS * 2;   // imaginary plane
-    static constexpr int OFF_P = OFF_AI + LANES * FS * 2;    // power spectrum P[lane][bin] (pairs); own buffer so
+    static constexpr int OFF_AR = SW * 2;                // in floats: A[lane][20*k1 + n2] = (re pair, im pair)
+    static constexpr int OFF_P = OFF_AR + LANES * FS * 4;    // power spectrum P[lane][bin] (pairs); own buffer so
                                                              // that phase A of the next unit can overlap B and M
     static constexpr int OFF_MISC = OFF_P + LANES * PSZ * 2; // ints: [0] max key [1] min key [4..7], [8..11] unit info
     static constexpr int OFF_MBAR = OFF_MISC + 12;           // two 8-byte mbarriers: [0] "B(u) has read its rows of
@@ -74,6 +73,7 @@ struct FeW2Cfg {
     static constexpr int MW_MAX = 576;
     static constexpr int SMEM_FLOATS = OFF_MW + MW_MAX;
     static_assert(OFF_MBAR % 2 == 0, "mbarriers need 8-byte alignment");
+    static_assert(OFF_AR % 4 == 0, "A is accessed with 128-bit loads and stores");
     static_assert(OFF_MDESC % 4 == 0 && OFF_MW % 4 == 0, "tables are read with 128-bit loads");
     static_assert(SMEM_FLOATS * 4 <= 232448, "more than 227 KB of shared memory");
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
@@ -236,8 +236,19 @@ FE_HD FE_INLINE int fe_w2_a_second(int warp) {
     return warp < 5 ? warp + 12 : (warp == 6 ? 17 : (warp == 7 ? 18 : (warp == 11 ? 19 : -1)));
 }
 
+// A buffer, interleaved: A[lane][20*k1 + n2] = (re pair, im pair), 16 bytes; lane stride FS elements (odd multiple
+// of 16 bytes: conflict-free 128-bit accesses).  One STS.128 / LDS.128 moves what two 64-bit accesses moved with
+// separate planes: same wavefronts, half the shared-memory instructions in the queue.
+FE_HD FE_INLINE float4* fe_w2_a_ptr(float* sm, int lane) {
+    return reinterpret_cast<float4*>(sm + FeW2Cfg::OFF_AR) + FeW2Cfg::FS * lane;
+}
+FE_HD FE_INLINE void fe_w2_a_store(float4* q, fe2 re, fe2 im) { *q = make_float4(re.x, re.y, im.x, im.y); }
+FE_HD FE_INLINE void fe_w2_a_load(const float4* q, fe2& re, fe2& im) {
+    const float4 v = *q;
+    re = fe_mk2(v.x, v.y); im = fe_mk2(v.z, v.w);
+}
+
 // ---------------------------------------------------------------- phase A
-// A planes: Ar[lane][20*k1 + n2], Ai[lane][20*k1 + n2] (pairs), lane stride FS (odd: conflict-free 64-bit)
 template <class PreStore>
 FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2, PreStore pre_store) {
     typedef FeW2Cfg C;
@@ -253,18 +264,16 @@ FE_HD FE_INLINE void fe_w2_stage_a(float* sm, int lane, int n2, PreStore pre_sto
     }
     fe2 yr[11], yi[11];
     fe_rdft20_h11(x, yr, yi);
-    fe2* __restrict__ ar = reinterpret_cast<fe2*>(sm + C::OFF_AR) + C::FS * lane + n2;
-    fe2* __restrict__ ai = reinterpret_cast<fe2*>(sm + C::OFF_AI) + C::FS * lane + n2;
-    pre_store();   // the A planes may still be read by phase B of the previous unit
-    ar[0] = yr[0];
+    float4* __restrict__ a = fe_w2_a_ptr(sm, lane) + n2;
+    pre_store();   // the A buffer may still be read by phase B of the previous unit
+    *reinterpret_cast<fe2*>(a) = yr[0];                              // k1 = 0 is real: only the first half is read
 #pragma unroll
     for (int k1 = 1; k1 < 10; ++k1) {
         const float wr = tab[18 + 2 * k1], wi = tab[19 + 2 * k1];
-        ar[C::R * k1] = fe_fnmac(wi, yi[k1], fe_mulc(wr, yr[k1]));  // wr*yr - wi*yi
-        ai[C::R * k1] = fe_fmac(wi, yr[k1], fe_mulc(wr, yi[k1]));   // wr*yi + wi*yr
+        fe_w2_a_store(a + C::R * k1, fe_fnmac(wi, yi[k1], fe_mulc(wr, yr[k1])),    // wr*yr - wi*yi
+                      fe_fmac(wi, yr[k1], fe_mulc(wr, yi[k1])));                   // wr*yi + wi*yr
     }
-    ar[C::R * 10] = fe_mulc(tab[38], yr[10]);
-    ai[C::R * 10] = fe_mulc(tab[39], yr[10]);
+    fe_w2_a_store(a + C::R * 10, fe_mulc(tab[38], yr[10]), fe_mulc(tab[39], yr[10]));
 }
 
 // all phase-A tasks of one warp, in order (prologue of the kernel; host emulation)
@@ -279,11 +288,10 @@ FE_HD FE_INLINE void fe_w2_phase_a(float* sm, int lane, int warp) {
 template <class PostLoad>
 FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1, PostLoad post_load) {
     typedef FeW2Cfg C;
-    const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * k1;
-    const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * k1;
+    const float4* __restrict__ a = fe_w2_a_ptr(sm, lane) + C::R * k1;
     fe2 xr[20], xi[20], yr[20], yi[20];
 #pragma unroll
-    for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
+    for (int n2 = 0; n2 < 20; ++n2) fe_w2_a_load(a + n2, xr[n2], xi[n2]);
     post_load();
     fe_cdft20(xr, xi, yr, yi);
     fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + k1;          // bins k1 + 20*j
@@ -298,10 +306,10 @@ FE_HD FE_INLINE void fe_w2_stage_b_heavy(float* sm, int lane, int k1, PostLoad p
 template <class PostLoad>
 FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane, PostLoad post_load) {   // k1 = 0: real input, bins 20*j, j = 0..9
     typedef FeW2Cfg C;
-    const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane;
+    const float4* __restrict__ a = fe_w2_a_ptr(sm, lane);
     fe2 xr[20], yr[10], yi[10];
 #pragma unroll
-    for (int n2 = 0; n2 < 20; ++n2) xr[n2] = ar[n2];
+    for (int n2 = 0; n2 < 20; ++n2) xr[n2] = *reinterpret_cast<const fe2*>(a + n2);
     post_load();
     yi[0] = fe_zero<fe2>();
     fe_rdft20_h10(xr, yr, yi);
@@ -313,11 +321,10 @@ FE_HD FE_INLINE void fe_w2_stage_b_k0(float* sm, int lane, PostLoad post_load) {
 template <class PostLoad>
 FE_HD FE_INLINE void fe_w2_stage_b_k10(float* sm, int lane, PostLoad post_load) {  // k1 = 10: bins 10 + 20*j, j = 0..9
     typedef FeW2Cfg C;
-    const fe2* __restrict__ ar = reinterpret_cast<const fe2*>(sm + C::OFF_AR) + C::FS * lane + C::R * 10;
-    const fe2* __restrict__ ai = reinterpret_cast<const fe2*>(sm + C::OFF_AI) + C::FS * lane + C::R * 10;
+    const float4* __restrict__ a = fe_w2_a_ptr(sm, lane) + C::R * 10;
     fe2 xr[20], xi[20], yr[10], yi[10];
 #pragma unroll
-    for (int n2 = 0; n2 < 20; ++n2) { xr[n2] = ar[n2]; xi[n2] = ai[n2]; }
+    for (int n2 = 0; n2 < 20; ++n2) fe_w2_a_load(a + n2, xr[n2], xi[n2]);
     post_load();
     fe_cdft20_h10(xr, xi, yr, yi);
     fe2* __restrict__ pa = reinterpret_cast<fe2*>(sm + C::OFF_P) + C::PSZ * lane + 10;
