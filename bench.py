@@ -2,7 +2,10 @@
 """Benchmark of the hot path: batched waveform -> Whisper large-v3 128-bin log-mel (BASELINE.json configs[1]:
 1024 synthetic 30-s 16 kHz chunks per GPU).  One step = one pass over the whole batch.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cfg2|cfg3|cfg4]
+
+--workload (default cfg2, the headline the driver runs) measures the other two featurizers of SURVEY.md section 8(a)
+with the same contract: cfg3 = CosyVoice 24 kHz mel on 256 x 10 s, cfg4 = kaldi fbank + CMN on 4096 x 5 s.
 
 N > 1 is launched by torchrun (one rank per GPU); every rank featurizes its own shard of 1024 clips (weak
 scaling, clips are independent: no data-path collective), the timed region is bracketed by barrier +
@@ -32,18 +35,85 @@ import torch  # noqa: E402
 
 METRIC = "audio_seconds_per_second_log_mel"
 UNIT = "audio-s/s"
-B_CLIPS, L_SAMPLES, N_MELS, SR = 1024, 480000, 128, 16000
-T_FRAMES = L_SAMPLES // 160
-AUDIO_S_PER_STEP = B_CLIPS * L_SAMPLES / SR                       # 30720 audio-seconds per GPU per step
-BYTES_PER_CLIP = 4 * L_SAMPLES + 4 * N_MELS * T_FRAMES            # algorithmic: 4*(in) + 4*(out) = 3 456 000 B
-CPU_SAMPLE_CLIPS = 64
 
 
-def config(n_gpus):
-    return {"workload": "BASELINE configs[1]: Whisper large-v3 128-bin log-mel, 1024 x 30 s @ 16 kHz per GPU",
-            "featurizer": "whisper_log_mel", "n_mels": N_MELS, "clips_per_gpu": B_CLIPS, "samples_per_clip": L_SAMPLES,
-            "global_clips": B_CLIPS * n_gpus, "norm": "per_clip", "parallelism": f"clip-sharded x{n_gpus}, no collective",
-            "l2_policy": "inputs (1.97 GB) and outputs (1.57 GB) per step exceed the 126 MB L2; no flush needed"}
+class Workload:
+    """one BASELINE.json config: shapes, the device / host / CPU-reference step functions and the roofline bytes.
+    The default (and the only one the driver runs) is cfg2; cfg3 / cfg4 are the other two featurizers of SURVEY.md
+    section 8(a), measured with the same contract through --workload."""
+
+    def __init__(self, key):
+        self.key = key
+        if key == "cfg2":
+            self.B, self.L, self.sr, self.n_mels = 1024, 480000, 16000, 128
+            self.T = self.L // 160
+            self.out_shape = (self.B, self.n_mels, self.T)
+            self.kernel = "fe_whisper2_kernel<128>"
+            self.cpu_clips = 64
+            self.desc = "BASELINE configs[1]: Whisper large-v3 128-bin log-mel, 1024 x 30 s @ 16 kHz per GPU"
+            self.featurizer = "whisper_log_mel"
+            self.traffic_key = "fe_whisper2_kernel_128_dram_bytes_per_1024_clips"
+            self.cpu_desc = "oracle fp32 = torch.stft + dense mel matmul + log10/max-8 (the ops whisper.audio runs)"
+        elif key == "cfg3":
+            self.B, self.L, self.sr, self.n_mels = 256, 240000, 24000, 80
+            self.T = self.L // 480
+            self.out_shape = (self.B, self.n_mels, self.T)
+            self.kernel = "fe_cosy_kernel"
+            self.cpu_clips = 64
+            self.desc = "BASELINE configs[2]: CosyVoice 24 kHz 80-bin mel_spectrogram (n_fft 1920, hop 480), 256 x 10 s per GPU"
+            self.featurizer = "cosy_mel"
+            self.traffic_key = None
+            self.cpu_desc = "oracle fp32 = reflect pad + torch.stft(1920, 480) + sqrt + dense mel matmul + ln (matcha mel_spectrogram's ops)"
+        elif key == "cfg4":
+            self.B, self.L, self.sr, self.n_mels = 4096, 80000, 16000, 80
+            self.T = 1 + (self.L - 400) // 160
+            self.out_shape = (self.B, self.T, self.n_mels)
+            self.kernel = "fe_kaldi_kernel"
+            self.cpu_clips = 256
+            self.desc = "BASELINE configs[3]: kaldi 80-dim fbank (25 ms / 10 ms, dither 0) + CMN, 4096 x 5 s @ 16 kHz per GPU"
+            self.featurizer = "kaldi_fbank"
+            self.traffic_key = None
+            self.cpu_desc = "torchaudio.compliance.kaldi.fbank per clip + mean subtraction, as the reference calls it"
+        else:
+            raise ValueError(key)
+        self.audio_s_per_step = self.B * self.L / self.sr
+        self.out_per_clip = self.out_shape[1] * self.out_shape[2]
+        self.bytes_per_clip = 4 * self.L + 4 * self.out_per_clip     # algorithmic: 4*(in) + 4*(out)
+
+    def config(self, n_gpus):
+        tot_in, tot_out = self.B * self.L * 4 / 1e9, self.B * self.out_per_clip * 4 / 1e9
+        return {"workload": self.desc, "featurizer": self.featurizer, "n_mels": self.n_mels, "clips_per_gpu": self.B,
+                "samples_per_clip": self.L, "global_clips": self.B * n_gpus,
+                "norm": "per_clip" if self.key == "cfg2" else None,
+                "parallelism": f"clip-sharded x{n_gpus}, no collective",
+                "l2_policy": f"inputs ({tot_in:.2f} GB) and outputs ({tot_out:.2f} GB) per step exceed the 126 MB L2; no flush needed"}
+
+    def device_step(self, fe, x, out):
+        if self.key == "cfg2":
+            return lambda: fe.whisper_log_mel_batch(x, n_mels=self.n_mels, norm="per_clip", out=out)
+        if self.key == "cfg3":
+            return lambda: fe.cosy_mel_batch(x, out=out)
+        return lambda: fe.kaldi_fbank_batch(x, subtract_mean=True, out=out)
+
+    def host_step(self, fe, xh, oh, dev):
+        if self.key == "cfg2":
+            return lambda: fe.whisper_log_mel_host(xh, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
+        if self.key == "cfg3":
+            return lambda: fe.cosy_mel_host(xh, out=oh, device=dev)
+        return lambda: fe.kaldi_fbank_host(xh, subtract_mean=True, out=oh, device=dev)
+
+    def cpu_step(self):
+        import oracle
+        g = torch.Generator().manual_seed(1234)
+        x = (0.1 * torch.randn(self.cpu_clips, self.L, generator=g)).clamp_(-1, 1)
+        if self.key == "cfg2":
+            return (lambda: oracle.whisper_log_mel(x, self.n_mels, norm="per_clip")), self.cpu_clips * self.L / self.sr
+        if self.key == "cfg3":
+            return (lambda: oracle.cosyvoice_mel(x)), self.cpu_clips * self.L / self.sr
+        return (lambda: [oracle.kaldi_fbank(x[b]) for b in range(self.cpu_clips)]), self.cpu_clips * self.L / self.sr
+
+
+WL = Workload("cfg2")
 
 
 # --------------------------------------------------------------------------------------------- clocks
@@ -101,15 +171,9 @@ class ClockSampler:
 
 # --------------------------------------------------------------------------------------------- reference arm
 def reference_step_fn():
-    """the reference's own CPU path for this featurizer (whisper.audio.log_mel_spectrogram's ops) on a bounded
-    sample of the workload: CPU_SAMPLE_CLIPS clips of 30 s, all host threads."""
-    import oracle
-    g = torch.Generator().manual_seed(1234)
-    x = (0.1 * torch.randn(CPU_SAMPLE_CLIPS, L_SAMPLES, generator=g)).clamp_(-1, 1)
-
-    def step():
-        return oracle.whisper_log_mel(x, N_MELS, norm="per_clip")
-    return step, CPU_SAMPLE_CLIPS * L_SAMPLES / SR
+    """the reference's own CPU path for this featurizer on a bounded sample of the workload (WL.cpu_clips clips),
+    all host threads."""
+    return WL.cpu_step()
 
 
 def time_cpu(step, reps, warm):
@@ -126,6 +190,12 @@ def time_cpu(step, reps, warm):
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 for its workers; the reference arm is one process on rank 0 and may use
+    # every host core
+    try:
+        torch.set_num_threads(len(os.sched_getaffinity(0)))
+    except Exception:
+        torch.set_num_threads(os.cpu_count() or 1)
     step, audio_s = reference_step_fn()
     ts = time_cpu(step, args.steps, args.warmup)
     total = sum(ts)
@@ -133,10 +203,9 @@ def run_reference(args, rank, world):
     cores = torch.get_num_threads()
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total / len(ts), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config(args.gpus),
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": WL.config(args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{CPU_SAMPLE_CLIPS} of the 1024 clips per step (30 s each), oracle fp32 = "
-                                       "torch.stft + dense mel matmul + log10/max-8 (the ops whisper.audio runs), "
+                             "sample": f"{WL.cpu_clips} of the {WL.B} clips per step ({WL.L / WL.sr:.0f} s each), {WL.cpu_desc}, "
                                        f"{cores} torch threads of {os.cpu_count()} host cpus"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -166,11 +235,9 @@ def run_ours(args, rank, world, local_rank):
         return float(t.item())
 
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    x = (0.1 * torch.randn(B_CLIPS, L_SAMPLES, generator=gen, device=dev)).clamp_(-1, 1)
-    out = torch.empty((B_CLIPS, N_MELS, T_FRAMES), dtype=torch.float32, device=dev)
-
-    def step():
-        fe.whisper_log_mel_batch(x, n_mels=N_MELS, norm="per_clip", out=out)
+    x = (0.1 * torch.randn(WL.B, WL.L, generator=gen, device=dev)).clamp_(-1, 1)
+    out = torch.empty(WL.out_shape, dtype=torch.float32, device=dev)
+    step = WL.device_step(fe, x, out)
 
     # ---- device-resident timing
     for _ in range(args.warmup):
@@ -189,7 +256,7 @@ def run_ours(args, rank, world, local_rank):
     clk = clocks.stop()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     ms_step = ms_total / args.steps
-    value = world * AUDIO_S_PER_STEP / (ms_step * 1e-3)
+    value = world * WL.audio_s_per_step / (ms_step * 1e-3)
 
     # ---- the featurizer kernel alone (per-launch CUDA events inside the library), rank 0 reports
     fe.profile_begin()
@@ -198,8 +265,8 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     prof = fe.profile_end()
     k_ms = prof["feature_ms"] / max(prof["feature_launches"], 1)
-    clips_per_launch = B_CLIPS * args.steps / max(prof["feature_launches"], 1)
-    achieved = clips_per_launch * BYTES_PER_CLIP / (k_ms * 1e-3) / 1e9
+    clips_per_launch = WL.B * args.steps / max(prof["feature_launches"], 1)
+    achieved = clips_per_launch * WL.bytes_per_clip / (k_ms * 1e-3) / 1e9
     peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -210,26 +277,27 @@ def run_ours(args, rank, world, local_rank):
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            traffic = json.load(f).get("fe_whisper2_kernel_128_dram_bytes_per_1024_clips")
+            traffic = json.load(f).get(WL.traffic_key) if WL.traffic_key else None
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "fe_whisper2_kernel<128>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": WL.kernel, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_per_launch": k_ms, "clips_per_launch": clips_per_launch,
-                "algorithmic_bytes_per_launch": clips_per_launch * BYTES_PER_CLIP,
+                "algorithmic_bytes_per_launch": clips_per_launch * WL.bytes_per_clip,
                 "kernel_share_of_step": prof["feature_ms"] / max(prof["feature_ms"] + prof["epilogue_ms"], 1e-9),
                 "epilogue_ms_per_step": prof["epilogue_ms"] / args.steps,
-                "step_frac": (B_CLIPS * BYTES_PER_CLIP / (ms_step / 1.0 * 1e-3) / 1e9) / peak if world == 1 else None}
+                "step_frac": (WL.B * WL.bytes_per_clip / (ms_step / 1.0 * 1e-3) / 1e9) / peak if world == 1 else None}
 
     # ---- end to end: pinned host in -> pinned host out through the host-buffer API
     del out
-    xh = torch.empty((B_CLIPS, L_SAMPLES), dtype=torch.float32, pin_memory=True)
+    xh = torch.empty((WL.B, WL.L), dtype=torch.float32, pin_memory=True)
     xh.copy_(x)
     del x
-    oh = torch.empty((B_CLIPS, N_MELS, T_FRAMES), dtype=torch.float32, pin_memory=True)
+    oh = torch.empty(WL.out_shape, dtype=torch.float32, pin_memory=True)
+    host_step = WL.host_step(fe, xh, oh, dev)
 
     def e2e_step():
-        fe.whisper_log_mel_host(xh, n_mels=N_MELS, norm="per_clip", out=oh, device=dev)
+        host_step()
         return float(oh[0, 0, 0])                                  # read the step's result on the host
 
     e2e_steps = max(2, min(args.steps, 5))
@@ -240,8 +308,8 @@ def run_ours(args, rank, world, local_rank):
         e2e_step()
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
-    e2e = {"value": world * AUDIO_S_PER_STEP / (e2e_ms * 1e-3), "unit": UNIT,
-           "h2d_bytes_per_step": B_CLIPS * L_SAMPLES * 4, "d2h_bytes_per_step": B_CLIPS * N_MELS * T_FRAMES * 4,
+    e2e = {"value": world * WL.audio_s_per_step / (e2e_ms * 1e-3), "unit": UNIT,
+           "h2d_bytes_per_step": WL.B * WL.L * 4, "d2h_bytes_per_step": WL.B * WL.out_per_clip * 4,
            "ms_per_step": e2e_ms, "steps": e2e_steps, "api": "whisper_log_mel_host -> b200feat_whisper_logmel_host "
            "(pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"}
 
@@ -252,19 +320,19 @@ def run_ours(args, rank, world, local_rank):
         ts = time_cpu(stepc, 3, 1)
         cores = torch.get_num_threads()
         cpu = {"value": audio_s / min(ts), "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{CPU_SAMPLE_CLIPS} of the 1024 clips (30 s each), best of 3 after 1 warm-up, oracle fp32 "
-                         f"(torch.stft + dense mel matmul + log10/max-8), {cores} torch threads of {os.cpu_count()} host cpus"}
+               "sample": f"{WL.cpu_clips} of the {WL.B} clips ({WL.L / WL.sr:.0f} s each), best of 3 after 1 warm-up, {WL.cpu_desc}, "
+                         f"{cores} torch threads of {os.cpu_count()} host cpus"}
 
     if world > 1:
         counts = [None] * world
-        dist.all_gather_object(counts, {"rank": rank, "clips": B_CLIPS * args.steps})
+        dist.all_gather_object(counts, {"rank": rank, "clips": WL.B * args.steps})
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic (0.1*N(0,1) clipped to [-1,1], seed 1234+rank, generated on device)",
-                "config": config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+                "config": WL.config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": launches, "clocks": clk}
         print(json.dumps(line), flush=True)
 
@@ -275,7 +343,11 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4"],
+                    help="BASELINE.json config: cfg2 = Whisper 128-bin (the headline; default), cfg3 = CosyVoice mel, cfg4 = kaldi fbank")
     args = ap.parse_args()
+    global WL
+    WL = Workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -288,7 +360,8 @@ def main():
             # convenience: re-launch under torchrun
             cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                    "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29531"),
-                   os.path.abspath(__file__), "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+                   os.path.abspath(__file__), "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
+                   "--workload", args.workload]
             sys.exit(subprocess.call(cmd))
     run_ours(args, rank, world, local_rank)
 
