@@ -83,6 +83,30 @@ FE_HD FE_INLINE fe2 fe_fma(fe2 a, fe2 b, fe2 c) { return fe_mk2(fmaf(a.x, b.x, c
 #endif
 
 
+// Rolled sparse mel projection of the one-frame-per-lane kernels (tables: generated/fe_tables.h, fe_melroll_*):
+// filters m0, m0 + mstep, ... < m1; ld(k) returns this lane's power at bin k, emit(m, value) is called once per
+// filter.  Four partial sums per filter, taps zero-padded to a multiple of four.  (The fully unrolled form with
+// immediate weights is thousands of instructions of which every warp runs a different part: the kernels then
+// starve on instruction fetch.)
+template <class Load, class Emit>
+FE_HD FE_INLINE void fe_mel_rolled(const int* __restrict__ desc, const float* __restrict__ w, int m0, int m1, int mstep,
+                                   Load ld, Emit emit) {
+#pragma unroll 1
+    for (int m = m0; m < m1; m += mstep) {
+        const int k0 = desc[3 * m], n4 = desc[3 * m + 1];
+        const float* __restrict__ wm = w + desc[3 * m + 2];
+        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+#pragma unroll 2
+        for (int j = 0; j < n4; j += 4) {
+            a0 = fmaf(wm[j], ld(k0 + j), a0);
+            a1 = fmaf(wm[j + 1], ld(k0 + j + 1), a1);
+            a2 = fmaf(wm[j + 2], ld(k0 + j + 2), a2);
+            a3 = fmaf(wm[j + 3], ld(k0 + j + 3), a3);
+        }
+        emit(m, (a0 + a1) + (a2 + a3));
+    }
+}
+
 // order-preserving float <-> int key (signed compare of keys == float compare)
 FE_HD FE_INLINE int fe_float_key(float f) {
     union { float f; int i; } u;

@@ -186,5 +186,5 @@ FE_HD FE_INLINE void fe_c_phase_mel(const FeCosyParams& p, float* sm, int tid, i
         const float lg = FE_LOG2(fmaxf(v, 1e-5f)) * 0.69314718055994531f;  // ln
         if (frame < p.T_out) o[(int64_t)m * rs] = live ? lg : 0.0f;  // ragged batches: zeros past T_b
     };
-    for (int c = warp; c < FE_MELPROJ_COSY_NCHUNK; c += C::NW) fe_melproj_cosy<float>(c, [&](int k) { return sm[k * C::PS + lane]; }, emit);
+    fe_mel_rolled(fe_melroll_cosy_desc, fe_melroll_cosy_w, warp, C::NMEL, C::NW, [&](int k) { return sm[k * C::PS + lane]; }, emit);
 }

@@ -201,6 +201,8 @@ FE_HD FE_INLINE void fe_k_phase_mel(const FeKaldiParams&, float* sm, int tid, in
     auto emit = [&](int m, float v) {
         st[m] = FE_LOG2(fmaxf(v, C::EPS)) * 0.69314718055994531f;  // ln
     };
+    // unrolled (immediate weights): the rolled form (fe_mel_rolled) was measured 11 % slower here -- six taps per
+    // filter on average do not amortise the loop overhead
     for (int c = warp; c < FE_MELPROJ_KALDI_NCHUNK; c += C::NW) fe_melproj_kaldi<float>(c, [&](int k) { return sm[k * C::PS + lane]; }, emit);
 }
 

@@ -279,6 +279,29 @@ def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=No
     return "\n".join(out) + "\n"
 
 
+def gen_melrolled(name, filt, n_bins):
+    """tables for the rolled mel projection of the one-frame-per-lane kernels (kaldi, CosyVoice): per filter
+    name_desc[3*m] = first tap k0, [3*m+1] = taps padded to a multiple of 4, [3*m+2] = offset of its weights in
+    name_w (zero-padded; the padded taps stay inside [0, n_bins))."""
+    desc, wts = [], []
+    for m in range(filt.shape[0]):
+        nz = np.nonzero(filt[m])[0]
+        if len(nz) == 0:
+            k0, n = 0, 0
+        else:
+            k0, n = int(nz[0]), int(nz[-1] - nz[0] + 1)
+            assert np.all(filt[m, k0:k0 + n] != 0), "taps of a filter must be contiguous"
+        n4 = max(4, (n + 3) // 4 * 4)
+        k0 = min(k0, n_bins - n4)
+        assert k0 >= 0 and np.count_nonzero(filt[m, :k0]) == 0 and np.count_nonzero(filt[m, k0 + n4:]) == 0
+        desc += [k0, n4, len(wts)]
+        wts += [float(v) for v in filt[m, k0:k0 + n4]]
+    out = [f"// rolled mel projection tables, {filt.shape[0]} filters, {int(np.count_nonzero(filt))} taps ({len(wts)} padded)",
+           emit_array(name + "_desc", np.array(desc, dtype=np.int64), per_line=9, ctype="int"),
+           emit_array(name + "_w", np.array(wts, dtype=np.float64))]
+    return "\n".join(out) + "\n"
+
+
 def twiddle_table(N, rows, cols):
     """float2 table T[row][col] = exp(-2*pi*i*row*col/N), rows x cols."""
     t = np.zeros((rows, cols, 2), dtype=np.float64)
@@ -351,8 +374,8 @@ def main():
         mel_share[w_] = 1.8
     tb.append(gen_melloop("fe_melloop_w80", w80, 12, (2, 3, 4, 6, 8, 11, 14), chunk_weight=mel_share))
     tb.append(gen_melloop("fe_melloop_w128", w128, 12, (1, 2, 3, 4, 6, 7, 9), chunk_weight=mel_share))
+    tb.append(gen_melrolled("fe_melroll_cosy", cz, 640))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
-    tb.append(gen_melproj("fe_melproj_cosy", cz, 16, 639))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
         f.write("\n".join(tb))
     # the float32 tables the kernels bake, for the parity tests (tests/ compares them to the oracle's)
