@@ -109,28 +109,9 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
         const int ltid = tid - C::NCT;
         int par = 0;
         int it = 0;
-#ifdef FE_W2_LOADER_ASYNC
-        for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1, ++it) {
-            const FeW2Unit t = fe_w2_unit(p, u);
-            FE_TR(it, 0);
-            if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
-            FE_TR(it, 1);
-            if (t.t0 < t.T) {
-                if (fe_w2_interior(p, t)) fe_w2_load_async(p, t, sm, ltid);
-                else fe_w2_load_edge(p, t, sm, ltid);
-            }
-            if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
-            FE_TR(it, 2);
-            fe_bar_arrive(FE_BAR_W_FULL, C::NT);
-            FE_TR(it, 3);
-        }
-#else
         FeW2Stage stage;
         FeW2Unit t = fe_w2_unit(p, blockIdx.x);
         bool live = t.t0 < t.T, fast = live && fe_w2_interior(p, t);
-#ifdef FE_W2_EXP_NOLOAD
-        live = false;
-#endif
         if (fast) fe_w2_load_issue(p, t, ltid, stage);
         for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1, ++it) {
             FE_TR(it, 0);
@@ -146,14 +127,10 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
                 t = fe_w2_unit(p, un);
                 live = t.t0 < t.T;
                 fast = live && fe_w2_interior(p, t);
-#ifdef FE_W2_EXP_NOLOAD
-                fast = false; live = false;
-#endif
                 if (fast) fe_w2_load_issue(p, t, ltid, stage);
             }
             FE_TR(it, 3);
         }
-#endif
         return;
     }
     // ---- compute warps

@@ -101,36 +101,16 @@ FE_HD FE_INLINE FeW2Unit fe_w2_unit(const FeWhisper2Params& p, int u) {
 }
 
 // ---------------------------------------------------------------- loader
-// ltid in [0, NLT).  Interior units (fully inside the clip) are copied with 4-byte cp.async, one sample of each
-// segment per step: a warp reads two coalesced 128-byte rows and scatters them into 32 consecutive pairs.  No
-// staging registers, a rolled loop (small code), the copies of a whole unit in flight at once.  W is released
-// by the compute warps right after their last phase-A loads, most of a unit period before it is needed again.
+// ltid in [0, NLT).  One sample of both segments per step: a warp reads two coalesced 128-byte rows and writes
+// 32 consecutive pairs (conflict-free 64-bit stores; 128-bit loads would make the interleaving stores 4-way
+// conflicted).
 FE_HD FE_INLINE bool fe_w2_interior(const FeWhisper2Params& p, const FeW2Unit& t) {
     typedef FeW2Cfg C;
     const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
     return g0 >= 0 && g0 + C::SEG + C::RT <= t.len;
 }
 
-FE_HD FE_INLINE void fe_w2_load_async(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
-    typedef FeW2Cfg C;
-    const float* __restrict__ xa = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL);
-    const float* __restrict__ xb = xa + C::SEG;
-    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
-#if defined(__CUDA_ARCH__)
-    const unsigned w0 = (unsigned)__cvta_generic_to_shared(w);
-#pragma unroll 2
-    for (unsigned i = (unsigned)ltid; i < (unsigned)C::RT; i += (unsigned)C::NLT) {
-        const unsigned d = w0 + 8u * (i + i / (unsigned)C::HOP);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(xa + i) : "memory");
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u), "l"(xb + i) : "memory");
-    }
-    asm volatile("cp.async.wait_all;" ::: "memory");
-#else
-    for (int i = ltid; i < C::RT; i += C::NLT) w[i + i / C::HOP] = fe_mk2(xa[i], xb[i]);
-#endif
-}
-
-// register-staged variant: fe_w2_load_issue puts every load of the unit in flight (it runs BEFORE the loader
+// Interior units (fully inside the clip) are register-staged: fe_w2_load_issue puts every load of the unit in flight (it runs BEFORE the loader
 // waits for W to be released); fe_w2_load_store writes the pairs once W is free (conflict-free 64-bit stores)
 struct FeW2Stage {
     static constexpr int U = (FeW2Cfg::RT + FeW2Cfg::NLT - 1) / FeW2Cfg::NLT;  // samples per loader thread and segment
@@ -442,10 +422,8 @@ FE_HD FE_INLINE void fe_w2_mel_class(FeW2MelCtx& c, int i0, int i1) {
         }
         const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(acc.x), fe_w2_lg2(acc.y)), c.one);   // (log10(v) + 4) / 4
         float* o = fe_row_ptr(c.obase, c.rs4, (unsigned)d.x >> 16);
-#ifndef FE_W2_EXP_NOSTG
         if (c.la) fe_stg<0>(o, y.x);
         if (c.lb) fe_stg<4 * C::LANES>(o, y.y);
-#endif
         c.mx = fe_max3(c.mx, y.x, y.y);
         c.mn = fe_min3(c.mn, y.x, y.y);
     }
@@ -473,36 +451,6 @@ struct FeW2MelRun<NMELS, K, true> {
     static FE_HD FE_INLINE void run(FeW2MelCtx&, const int*) {}
 };
 
-#ifdef FE_W2_MEL_UNROLLED
-template <int NMELS>
-FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
-    typedef FeW2Cfg C;
-    const int fa = t.t0 + lane, fb = fa + C::LANES;
-    const bool la = fa < t.T, lb = fb < t.T;
-    float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + fa;
-    const unsigned rs4 = (unsigned)p.T_out * 4u;
-    const fe2* __restrict__ P = reinterpret_cast<const fe2*>(sm + C::OFF_P) + C::PSZ * lane;
-    union { unsigned u; float f; } qnan;
-    qnan.u = 0x7fc00000u;
-    const fe2 one = fe_mk2(la ? 1.0f : qnan.f, lb ? 1.0f : qnan.f);
-    float mn = 3.0e38f, mx = -3.0e38f;
-    float* q = o;
-    int qm = 0;
-    auto ld = [&](int k) -> fe2 { return P[k]; };
-    auto emit = [&](int m, fe2 v) {
-        const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(v.x), fe_w2_lg2(v.y)), one);
-        q = reinterpret_cast<float*>(reinterpret_cast<char*>(q) + (size_t)rs4 * (unsigned)(m - qm));
-        qm = m;
-        if (la) q[0] = y.x;
-        if (lb) q[C::LANES] = y.y;
-        mx = fe_max3(mx, y.x, y.y);
-        mn = fe_min3(mn, y.x, y.y);
-    };
-    if (NMELS == 80) fe_melproj_w80<fe2>(warp, ld, emit);
-    else fe_melproj_w128<fe2>(warp, ld, emit);
-    return fe_mk2(mn, mx);
-}
-#else
 template <int NMELS>
 FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
     typedef FeW2Cfg C;
@@ -526,7 +474,6 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     FeW2MelRun<NMELS, 0>::run(c, r);
     return fe_mk2(c.mn, c.mx);
 }
-#endif
 
 // ---------------------------------------------------------------- fix-up (second kernel)
 // Floor and clamp in the y = (x + 4) / 4 domain, with x = log10(mel) un-floored:

@@ -365,8 +365,6 @@ def main():
     w128 = slaney(16000, 400, 128, 0.0, 8000.0)
     cz = slaney(24000, 1920, 80, 0.0, 8000.0)
     kb = kaldi_banks()
-    tb.append(gen_melproj("fe_melproj_w80", w80, 12, 199, epi_cost=8))
-    tb.append(gen_melproj("fe_melproj_w128", w128, 12, 199, epi_cost=8))
     # compute warps 5, 8, 9, 10 run one phase-A task per unit, the others two (fe_w2_a_second): they take
     # a larger share of the mel projection so that all warps reach the unit's barrier together
     mel_share = [1.0] * 12
