@@ -240,14 +240,28 @@ __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2
             const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
             const bool clampu = n_live > 0 && mm.x < thr;
             float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + t.t0;
-            for (int i = threadIdx.x; i < NMELS * C::FT; i += blockDim.x) {
-                const int m = i / C::FT, c = i % C::FT;
-                if (c >= n_in) continue;
-                float* q = o + (int64_t)m * p.T_out + c;
-                if (c >= n_live) *q = 0.0f;
-                else if (clampu) {
-                    const float v = *q;
-                    if (v < thr) *q = thr;
+            // a thread's column c is fixed (blockDim.x is a multiple of FT); its rows are m = m0, m0 + RSTEP, ...
+            // Batches of eight independent loads: one HBM round trip per batch instead of one per element.
+            constexpr int RSTEP = 256 / C::FT;
+            const int c = threadIdx.x % C::FT, m0 = threadIdx.x / C::FT;
+            if (c < n_in) {
+                float* __restrict__ q0 = o + c;
+                if (c >= n_live) {
+                    for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = 0.0f;
+                } else if (clampu) {
+                    for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
+                        float v[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int m = mb + j * RSTEP;
+                            v[j] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const int m = mb + j * RSTEP;
+                            if (m < NMELS && v[j] < thr) q0[(int64_t)m * p.T_out] = thr;
+                        }
+                    }
                 }
             }
         }
