@@ -269,20 +269,40 @@ __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2
     }
 }
 
-__global__ void __launch_bounds__(FeKCfg::NT, 2) fe_kaldi_kernel(const FeKaldiParams p) {
+static int kaldi_tiles_per_cta() {
+    static const int v = [] {
+        const char* s = getenv("B200FEAT_KALDI_TPC");
+        int t = s ? atoi(s) : 2;   // B200, 4096 x 5 s: 1 -> 2.45 ms, 2 -> 2.42, 4 -> 2.45, 8 -> 2.76 (tail of the L2-sized waves)
+        return t < 1 ? 1 : t;
+    }();
+    return v;
+}
+
+// One CTA runs `tiles_per_cta` consecutive tiles (32 frames each) of the launch; the global loads of the next tile
+// are in flight while the phases of the current one run.
+__global__ void __launch_bounds__(FeKCfg::NT, 2) fe_kaldi_kernel(const FeKaldiParams p, int total_tiles, int tiles_per_cta) {
     extern __shared__ __align__(16) float sm[];
-    const int tid = threadIdx.x, cta = blockIdx.x;
-    fe_k_phase_load(p, sm, tid, cta);
-    __syncthreads();
-    fe_k_phase_sum(p, sm, tid, cta);
-    __syncthreads();
-    fe_k_phase_a(p, sm, tid, cta);
-    __syncthreads();
-    fe_k_phase_b(p, sm, tid, cta);
-    __syncthreads();
-    fe_k_phase_mel(p, sm, tid, cta);
-    __syncthreads();
-    fe_k_phase_store(p, sm, tid, cta);
+    const int tid = threadIdx.x;
+    const int first = blockIdx.x * tiles_per_cta;
+    const int last = first + tiles_per_cta < total_tiles ? first + tiles_per_cta : total_tiles;
+    FeKStage st;
+    if (first < last) fe_k_load_issue(p, tid, first, st);
+    for (int cta = first; cta < last; ++cta) {
+        fe_k_load_store(sm, tid, st);
+        if (cta + 1 < last) fe_k_load_issue(p, tid, cta + 1, st);
+        __syncthreads();
+        fe_k_phase_sum(p, sm, tid, cta);
+        __syncthreads();
+        fe_k_phase_a(p, sm, tid, cta);
+        __syncthreads();
+        fe_k_phase_b(p, sm, tid, cta);
+        __syncthreads();
+        fe_k_phase_mel(p, sm, tid, cta);
+        __syncthreads();
+        fe_k_phase_store(p, sm, tid, cta);
+        // no barrier needed here: the next pass writes W (the region the dead P occupied) and every thread meets two
+        // barriers before anything writes the staging tile that phase O is still reading
+    }
 }
 
 // CMN: one CTA per (clip, slab of 64 frames); 80 threads rebuild the clip mean from the per-tile sums
@@ -621,7 +641,9 @@ int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, i
         p.clip0 = (int32_t)c0; p.nclips = (int32_t)nc;
         {
             ProfScope ps(st, 0);
-            fe_kaldi_kernel<<<(unsigned)(nc * tiles), FeKCfg::NT, FeKCfg::SMEM_BYTES, st>>>(p);
+            const int total_tiles = (int)(nc * tiles);
+            const int tpc = kaldi_tiles_per_cta();
+            fe_kaldi_kernel<<<(unsigned)((total_tiles + tpc - 1) / tpc), FeKCfg::NT, FeKCfg::SMEM_BYTES, st>>>(p, total_tiles, tpc);
             g_launches++;
         }
         if (subtract_mean) {

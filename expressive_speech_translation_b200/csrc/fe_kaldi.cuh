@@ -55,26 +55,50 @@ FE_HD FE_INLINE FeKTile fe_k_tile(const FeKaldiParams& p, int cta) {
 }
 
 // ---------------------------------------------------------------- phase L
-FE_HD FE_INLINE void fe_k_phase_load(const FeKaldiParams& p, float* sm, int tid, int cta) {
+// Coalesced tile load in two halves: fe_k_load_issue puts the (at most six) 128-bit loads of a thread in flight,
+// fe_k_load_store writes them to W.  The kernel issues the loads of the CTA's next tile before it starts the
+// phases of the current one, so the HBM latency is off the critical path (it was 41 % of the stall samples).
+struct FeKStage {
+    static constexpr int U = (FeKCfg::RT + FeKCfg::NT * 4 - 1) / (FeKCfg::NT * 4);
+    float4 v[U];
+};
+
+FE_HD FE_INLINE void fe_k_load_issue(const FeKaldiParams& p, int tid, int cta, FeKStage& st) {
     typedef FeKCfg C;
     const FeKTile t = fe_k_tile(p, cta);
     const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
     const int64_t g0 = (int64_t)t.t0 * C::HOP;
-    for (int r4 = tid * 4; r4 < C::RT; r4 += C::NT * 4) {
+#pragma unroll
+    for (int j = 0; j < FeKStage::U; ++j) {
+        const int r4 = tid * 4 + j * C::NT * 4;
+        if (r4 >= C::RT) continue;
         const int64_t g = g0 + r4;
-        float v0, v1, v2, v3;
         if ((p.vec_ok & 1) && g + 3 < t.len) {
-            const float4 q = *reinterpret_cast<const float4*>(x + g);
-            v0 = q.x; v1 = q.y; v2 = q.z; v3 = q.w;
+            st.v[j] = *reinterpret_cast<const float4*>(x + g);
         } else {
-            v0 = (g + 0 < t.len) ? x[g + 0] : 0.0f;
-            v1 = (g + 1 < t.len) ? x[g + 1] : 0.0f;
-            v2 = (g + 2 < t.len) ? x[g + 2] : 0.0f;
-            v3 = (g + 3 < t.len) ? x[g + 3] : 0.0f;
+            st.v[j].x = (g + 0 < t.len) ? x[g + 0] : 0.0f;
+            st.v[j].y = (g + 1 < t.len) ? x[g + 1] : 0.0f;
+            st.v[j].z = (g + 2 < t.len) ? x[g + 2] : 0.0f;
+            st.v[j].w = (g + 3 < t.len) ? x[g + 3] : 0.0f;
         }
-        float* d = sm + r4 + r4 / C::HOP;
-        d[0] = v0; d[1] = v1; d[2] = v2; d[3] = v3;
     }
+}
+
+FE_HD FE_INLINE void fe_k_load_store(float* sm, int tid, const FeKStage& st) {
+    typedef FeKCfg C;
+#pragma unroll
+    for (int j = 0; j < FeKStage::U; ++j) {
+        const int r4 = tid * 4 + j * C::NT * 4;
+        if (r4 >= C::RT) continue;
+        float* d = sm + r4 + r4 / C::HOP;
+        d[0] = st.v[j].x; d[1] = st.v[j].y; d[2] = st.v[j].z; d[3] = st.v[j].w;
+    }
+}
+
+FE_HD FE_INLINE void fe_k_phase_load(const FeKaldiParams& p, float* sm, int tid, int cta) {
+    FeKStage st;
+    fe_k_load_issue(p, tid, cta, st);
+    fe_k_load_store(sm, tid, st);
 }
 
 // ---------------------------------------------------------------- phase S (frame sums for DC removal)
