@@ -33,6 +33,18 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
+def _load_manifest_helpers():
+    """expressive_speech_translation_b200/manifest.py loaded by path: pure shard arithmetic, usable by the reference arm
+    without importing the package (and with it the CUDA library)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_b200_manifest", os.path.join(ROOT, "expressive_speech_translation_b200", "manifest.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+manifest = _load_manifest_helpers()
+
 METRIC = "audio_seconds_per_second_log_mel"
 UNIT = "audio-s/s"
 
@@ -42,8 +54,9 @@ class Workload:
     The default (and the only one the driver runs) is cfg2; cfg3 / cfg4 are the other two featurizers of SURVEY.md
     section 8(a), measured with the same contract through --workload."""
 
-    def __init__(self, key):
+    def __init__(self, key, rank=0, world=1):
         self.key = key
+        self.world = world
         if key == "cfg2":
             self.B, self.L, self.sr, self.n_mels = 1024, 480000, 16000, 128
             self.T = self.L // 160
@@ -74,29 +87,55 @@ class Workload:
             self.featurizer = "kaldi_fbank"
             self.traffic_key = None
             self.cpu_desc = "torchaudio.compliance.kaldi.fbank per clip + mean subtraction, as the reference calls it"
+        elif key == "cfg5":
+            # the manifest sweep: a FIXED total of 10 000 clips, contiguous shards per rank (strong scaling), each shard
+            # featurized in sub-batches of <= 512 clips like the manifest runner does
+            self.total_clips, self.sub = 10000, 512
+            lo, hi = manifest.shard_rows(self.total_clips, rank, world)
+            self.B, self.L, self.sr, self.n_mels = hi - lo, 960000, 16000, 80
+            self.T = self.L // 160
+            self.out_shape = (self.B, self.n_mels, self.T)
+            self.kernel = "fe_whisper2_kernel<80>"
+            self.cpu_clips = 32
+            self.desc = ("BASELINE configs[4]: Batch-Processing manifest sweep, 10 000 x 60 s @ 16 kHz, Whisper 80-bin log-mel, "
+                         "contiguous clip shards per GPU, sub-batches of 512 clips")
+            self.featurizer = "whisper_log_mel"
+            self.traffic_key = None
+            self.cpu_desc = "oracle fp32 = torch.stft + dense mel matmul + log10/max-8 (the ops whisper.audio runs)"
         else:
             raise ValueError(key)
-        self.audio_s_per_step = self.B * self.L / self.sr
+        self.audio_s_per_step = self.B * self.L / self.sr              # this rank's share
+        self.scaling = "strong" if key == "cfg5" else "weak"
+        # whole-job audio per step: fixed total for the sweep, per-GPU work x N otherwise
+        self.global_audio_s = (self.total_clips if key == "cfg5" else self.B * world) * self.L / self.sr
+        self.e2e_clips = min(self.B, 1024)                              # clips of the shard the host-buffer leg streams per step
         self.out_per_clip = self.out_shape[1] * self.out_shape[2]
         self.bytes_per_clip = 4 * self.L + 4 * self.out_per_clip     # algorithmic: 4*(in) + 4*(out)
 
     def config(self, n_gpus):
         tot_in, tot_out = self.B * self.L * 4 / 1e9, self.B * self.out_per_clip * 4 / 1e9
         return {"workload": self.desc, "featurizer": self.featurizer, "n_mels": self.n_mels, "clips_per_gpu": self.B,
-                "samples_per_clip": self.L, "global_clips": self.B * n_gpus,
-                "norm": "per_clip" if self.key == "cfg2" else None,
+                "samples_per_clip": self.L, "global_clips": self.total_clips if self.key == "cfg5" else self.B * n_gpus,
+                "norm": "per_clip" if self.key in ("cfg2", "cfg5") else None,
                 "parallelism": f"clip-sharded x{n_gpus}, no collective",
                 "l2_policy": f"inputs ({tot_in:.2f} GB) and outputs ({tot_out:.2f} GB) per step exceed the 126 MB L2; no flush needed"}
 
     def device_step(self, fe, x, out):
         if self.key == "cfg2":
             return lambda: fe.whisper_log_mel_batch(x, n_mels=self.n_mels, norm="per_clip", out=out)
+        if self.key == "cfg5":
+            spans = manifest.sub_batches(0, self.B, self.sub)
+
+            def sweep():
+                for lo, hi in spans:
+                    fe.whisper_log_mel_batch(x[lo:hi], n_mels=self.n_mels, norm="per_clip", out=out[lo:hi])
+            return sweep
         if self.key == "cfg3":
             return lambda: fe.cosy_mel_batch(x, out=out)
         return lambda: fe.kaldi_fbank_batch(x, subtract_mean=True, out=out)
 
     def host_step(self, fe, xh, oh, dev):
-        if self.key == "cfg2":
+        if self.key in ("cfg2", "cfg5"):
             return lambda: fe.whisper_log_mel_host(xh, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
         if self.key == "cfg3":
             return lambda: fe.cosy_mel_host(xh, out=oh, device=dev)
@@ -106,7 +145,7 @@ class Workload:
         import oracle
         g = torch.Generator().manual_seed(1234)
         x = (0.1 * torch.randn(self.cpu_clips, self.L, generator=g)).clamp_(-1, 1)
-        if self.key == "cfg2":
+        if self.key in ("cfg2", "cfg5"):
             return (lambda: oracle.whisper_log_mel(x, self.n_mels, norm="per_clip")), self.cpu_clips * self.L / self.sr
         if self.key == "cfg3":
             return (lambda: oracle.cosyvoice_mel(x)), self.cpu_clips * self.L / self.sr
@@ -202,7 +241,7 @@ def run_reference(args, rank, world):
     value = audio_s * len(ts) / total
     cores = torch.get_num_threads()
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(ts), "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": 1e3 * total / len(ts), "higher_is_better": True, "scaling": WL.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": WL.config(args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{WL.cpu_clips} of the {WL.B} clips per step ({WL.L / WL.sr:.0f} s each), {WL.cpu_desc}, "
@@ -235,7 +274,12 @@ def run_ours(args, rank, world, local_rank):
         return float(t.item())
 
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    x = (0.1 * torch.randn(WL.B, WL.L, generator=gen, device=dev)).clamp_(-1, 1)
+    if WL.key == "cfg5":
+        x = torch.empty(WL.B, WL.L, dtype=torch.float32, device=dev)    # 38.4 GB at N = 1: filled in place, 256 clips at a time
+        for lo, hi in manifest.sub_batches(0, WL.B, 256):
+            x[lo:hi].normal_(generator=gen).mul_(0.1).clamp_(-1, 1)
+    else:
+        x = (0.1 * torch.randn(WL.B, WL.L, generator=gen, device=dev)).clamp_(-1, 1)
     out = torch.empty(WL.out_shape, dtype=torch.float32, device=dev)
     step = WL.device_step(fe, x, out)
 
@@ -256,7 +300,7 @@ def run_ours(args, rank, world, local_rank):
     clk = clocks.stop()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     ms_step = ms_total / args.steps
-    value = world * WL.audio_s_per_step / (ms_step * 1e-3)
+    value = WL.global_audio_s / (ms_step * 1e-3)
 
     # ---- the featurizer kernel alone (per-launch CUDA events inside the library), rank 0 reports
     fe.profile_begin()
@@ -290,10 +334,11 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- end to end: pinned host in -> pinned host out through the host-buffer API
     del out
-    xh = torch.empty((WL.B, WL.L), dtype=torch.float32, pin_memory=True)
-    xh.copy_(x)
+    ne = WL.e2e_clips
+    xh = torch.empty((ne, WL.L), dtype=torch.float32, pin_memory=True)
+    xh.copy_(x[:ne])
     del x
-    oh = torch.empty(WL.out_shape, dtype=torch.float32, pin_memory=True)
+    oh = torch.empty((ne,) + tuple(WL.out_shape[1:]), dtype=torch.float32, pin_memory=True)
     host_step = WL.host_step(fe, xh, oh, dev)
 
     def e2e_step():
@@ -308,10 +353,10 @@ def run_ours(args, rank, world, local_rank):
         e2e_step()
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
-    e2e = {"value": world * WL.audio_s_per_step / (e2e_ms * 1e-3), "unit": UNIT,
-           "h2d_bytes_per_step": WL.B * WL.L * 4, "d2h_bytes_per_step": WL.B * WL.out_per_clip * 4,
-           "ms_per_step": e2e_ms, "steps": e2e_steps, "api": "whisper_log_mel_host -> b200feat_whisper_logmel_host "
-           "(pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"}
+    e2e = {"value": world * ne * WL.L / WL.sr / (e2e_ms * 1e-3), "unit": UNIT,
+           "h2d_bytes_per_step": ne * WL.L * 4, "d2h_bytes_per_step": ne * WL.out_per_clip * 4,
+           "ms_per_step": e2e_ms, "steps": e2e_steps, "clips_per_step_per_gpu": ne,
+           "api": f"{WL.featurizer}_host -> b200feat_*_host (pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"}
 
     # ---- CPU baseline beside it (rank 0, N = 1 only)
     cpu = None
@@ -325,15 +370,17 @@ def run_ours(args, rank, world, local_rank):
 
     if world > 1:
         counts = [None] * world
-        dist.all_gather_object(counts, {"rank": rank, "clips": WL.B * args.steps})
+        dist.all_gather_object(counts, {"rank": rank, "clips": WL.B})
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": WL.scaling, "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic (0.1*N(0,1) clipped to [-1,1], seed 1234+rank, generated on device)",
                 "config": WL.config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": launches, "clocks": clk}
+        if world > 1:
+            line["config"]["clips_per_rank"] = [c["clips"] for c in sorted(counts, key=lambda c: c["rank"])]
         print(json.dumps(line), flush=True)
 
 
@@ -343,15 +390,16 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4"],
-                    help="BASELINE.json config: cfg2 = Whisper 128-bin (the headline; default), cfg3 = CosyVoice mel, cfg4 = kaldi fbank")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4", "cfg5"],
+                    help="BASELINE.json config: cfg2 = Whisper 128-bin (the headline; default), cfg3 = CosyVoice mel, cfg4 = kaldi fbank, "
+                         "cfg5 = manifest sweep (10 000 x 60 s, Whisper 80-bin, strong scaling)")
     args = ap.parse_args()
     global WL
-    WL = Workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    WL = Workload(args.workload, rank if world == args.gpus else 0, world if world == args.gpus else 1)
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
