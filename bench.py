@@ -333,6 +333,8 @@ def run_ours(args, rank, world, local_rank):
                 "step_frac": (WL.B * WL.bytes_per_clip / (ms_step / 1.0 * 1e-3) / 1e9) / peak if world == 1 else None}
 
     # ---- end to end: pinned host in -> pinned host out through the host-buffer API
+    # (one process per GPU: keep this rank's host buffers on the NUMA node next to its GPU)
+    bound = None if os.environ.get("B200FEAT_NO_NUMA_BIND") else manifest.bind_host_to_gpu(local_rank)
     del out
     ne = WL.e2e_clips
     xh = torch.empty((ne, WL.L), dtype=torch.float32, pin_memory=True)
@@ -355,7 +357,7 @@ def run_ours(args, rank, world, local_rank):
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
     e2e = {"value": world * ne * WL.L / WL.sr / (e2e_ms * 1e-3), "unit": UNIT,
            "h2d_bytes_per_step": ne * WL.L * 4, "d2h_bytes_per_step": ne * WL.out_per_clip * 4,
-           "ms_per_step": e2e_ms, "steps": e2e_steps, "clips_per_step_per_gpu": ne,
+           "ms_per_step": e2e_ms, "steps": e2e_steps, "clips_per_step_per_gpu": ne, "host_cpus_bound": len(bound) if bound else None,
            "api": f"{WL.featurizer}_host -> b200feat_*_host (pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"}
 
     # ---- CPU baseline beside it (rank 0, N = 1 only)

@@ -47,3 +47,27 @@ def gather_counts(clips, frames, samples, device=None, group=None):
     out = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(out, mine, group=group)
     return torch.stack(out)
+
+
+def bind_host_to_gpu(device_index):
+    """Pins the calling process to the CPUs NVML lists as local to CUDA device `device_index`, so that host buffers
+    it allocates afterwards (first touch) live on the NUMA node next to that GPU's PCIe root.  With one process per
+    GPU (the sweep's launch model) this keeps every rank's H2D/D2H traffic off the socket interconnect.
+    -> the cpu list it bound to, or None when NVML / the affinity call is unavailable (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        props = torch.cuda.get_device_properties(device_index)
+        bus_id = f"{props.pci_domain_id:08x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0"
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id)
+        n_words = (os.cpu_count() + 63) // 64
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
