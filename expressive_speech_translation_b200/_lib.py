@@ -23,6 +23,9 @@ SYMBOLS = {
     "b200feat_whisper_logmel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                            _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int64,
                                            _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
+    "b200feat_whisper_logmel_f16": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
+                                               _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int64,
+                                               _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
     "b200feat_cosy_mel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                      _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64,
                                      _c.c_void_p]),
@@ -31,6 +34,8 @@ SYMBOLS = {
                                         _c.c_int64, _c.c_void_p]),
     "b200feat_whisper_logmel_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,
                                                 _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32]),
+    "b200feat_whisper_logmel_f16_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,
+                                                    _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32]),
     "b200feat_cosy_mel_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_void_p,
                                           _c.c_int32]),
     "b200feat_kaldi_fbank_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,

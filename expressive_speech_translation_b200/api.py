@@ -116,26 +116,36 @@ def _stream(device):
 
 
 # ----------------------------------------------------------------------------------------- batched device API
-def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_clip", out=None):
+def _out_dtype(out_dtype):
+    if out_dtype not in (torch.float32, torch.float16):
+        raise ValueError(f"out_dtype must be torch.float32 or torch.float16, got {out_dtype}")
+    return out_dtype
+
+
+def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_clip", out=None, out_dtype=torch.float32):
     """(B, L) waveform batch on a CUDA device -> (B, n_mels, (L + padding) // 160) log-mel, async on the
-    current stream.  `lengths` (B,) marks ragged clips (frames past a clip's own count are 0)."""
+    current stream.  `lengths` (B,) marks ragged clips (frames past a clip's own count are 0).
+    out_dtype=torch.float16 writes the encoder-ready half tensor directly: bit-identical to `.to(torch.float16)` of
+    the float32 result (the cast whisper.transcribe(fp16=True) applies, whisper/transcribe.py `mel_segment.to(dtype)`)."""
     assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
     wave = _as_float_tensor(wave, "wave")
     device = _cuda_device(wave.device if wave.is_cuda else None)
     w, stride = _prep_wave(wave, device)
     B, L = w.shape
     T = (L + padding) // WHISPER_HOP
     if out is None:
-        out = torch.empty((B, n_mels, T), dtype=torch.float32, device=device)
-    elif out.shape != (B, n_mels, T) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
-        raise ValueError("out must be a contiguous float32 (B, n_mels, T) tensor on the wave's device")
+        out = torch.empty((B, n_mels, T), dtype=out_dtype, device=device)
+    elif out.shape != (B, n_mels, T) or not out.is_contiguous() or out.device != device:
+        raise ValueError("out must be a contiguous float32 / float16 (B, n_mels, T) tensor on the wave's device")
     if B == 0 or T == 0:
         return out
     ln = _lengths_dev(lengths, B, device)
     ws, nws = _workspace(KIND_WHISPER, B, L + int(padding), device)
+    fn = lib.b200feat_whisper_logmel if out_dtype == torch.float32 else lib.b200feat_whisper_logmel_f16
     with torch.cuda.device(device):
-        rc = lib.b200feat_whisper_logmel(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
-                                         _ptr(out), n_mels * T, T, _ptr(ws), nws, _stream(device))
+        rc = fn(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
+                _ptr(out), n_mels * T, T, _ptr(ws), nws, _stream(device))
     check(rc, "b200feat_whisper_logmel")
     return out
 
@@ -204,28 +214,30 @@ def _host_lengths(lengths, B):
     return ln
 
 
-def _host_out(shape, out, pin):
+def _host_out(shape, out, pin, dtype=torch.float32):
     if out is not None:
-        if tuple(out.shape) != tuple(shape) or out.dtype != torch.float32 or out.is_cuda or not out.is_contiguous():
-            raise ValueError(f"out must be a contiguous float32 host tensor of shape {tuple(shape)}")
+        if tuple(out.shape) != tuple(shape) or out.dtype != dtype or out.is_cuda or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous {dtype} host tensor of shape {tuple(shape)}")
         return out
-    return torch.empty(shape, dtype=torch.float32, pin_memory=pin)
+    return torch.empty(shape, dtype=dtype, pin_memory=pin)
 
 
 def whisper_log_mel_host(wave, lengths=None, n_mels=80, padding=0, norm="per_clip", out=None, device=None,
-                         pin_output=True):
+                         pin_output=True, out_dtype=torch.float32):
     """Host (ideally pinned) (B, L) waveform -> host (B, n_mels, T) log-mel through the chunked
-    H2D / kernel / D2H pipeline inside the library.  Blocks until the result is complete."""
+    H2D / kernel / D2H pipeline inside the library.  Blocks until the result is complete.
+    out_dtype=torch.float16: half features (see whisper_log_mel_batch), half the D2H bytes."""
     assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
     w = _host_2d(wave, "wave")
     B, L = w.shape
     T = (L + padding) // WHISPER_HOP
     dev = _cuda_device(device)
-    out = _host_out((B, n_mels, T), out, pin_output)
+    out = _host_out((B, n_mels, T), out, pin_output, out_dtype)
     ln = _host_lengths(lengths, B)
     if B and T:
-        rc = lib.b200feat_whisper_logmel_host(_ptr(w), _ptr(ln), B, L, n_mels, int(padding), _NORMS[norm],
-                                              _ptr(out), dev.index)
+        fn = lib.b200feat_whisper_logmel_host if out_dtype == torch.float32 else lib.b200feat_whisper_logmel_f16_host
+        rc = fn(_ptr(w), _ptr(ln), B, L, n_mels, int(padding), _NORMS[norm], _ptr(out), dev.index)
         check(rc, "b200feat_whisper_logmel_host")
     return out
 

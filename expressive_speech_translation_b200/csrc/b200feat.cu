@@ -2,6 +2,7 @@
 // Build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC -shared
 // (see expressive_speech_translation_b200/build.py).  sm_100a only; no other architecture, no CPU path.
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
@@ -87,7 +88,7 @@ struct FeMbarWait {
 //            dependencies inside the interval ("B(u) has read the A planes" before A(u+1) stores into them,
 //            "P(u) complete" before M(u) reads it).  Warps of one SM sub-partition are in different phases at any
 //            time, so the shared-memory bursts of one overlap the FP32 work of another.
-template <int NMELS>
+template <int NMELS, bool OUT16>
 __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhisper2Params p) {
     typedef FeW2Cfg C;
     extern __shared__ __align__(16) float sm[];
@@ -185,7 +186,7 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
             }
             if (k == 0 && !first) {
                 fe_mbar_wait(mb_pb, parity);
-                if (live) mm = fe_w2_phase_mel<NMELS>(p, cur, sm, lane, warp);
+                if (live) mm = fe_w2_phase_mel<NMELS, OUT16>(p, cur, sm, lane, warp);
             }
             FE_TR(it, 3 + k);
         }
@@ -211,7 +212,7 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
 // frames past a ragged clip's own end.  Everything else is left untouched (one trip to HBM).
 // One thread checks one unit (coalesced read of its (min, max)); the units that need work -- few or none for
 // noise-like audio of full length -- are then rewritten by the whole CTA, one after the other.
-template <int NMELS>
+template <int NMELS, bool OUT16>
 __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2Params p) {
     typedef FeW2Cfg C;
     __shared__ int list[256];
@@ -239,27 +240,50 @@ __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2
             const float2 mm = p.unit_minmax[uu];
             const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
             const bool clampu = n_live > 0 && mm.x < thr;
-            float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + t.t0;
             // a thread's column c is fixed (blockDim.x is a multiple of FT); its rows are m = m0, m0 + RSTEP, ...
             // Batches of eight independent loads: one HBM round trip per batch instead of one per element.
+            // float16 output: rounding is monotone, so clamping the rounded values against the rounded threshold
+            // equals rounding the clamped float32 values.
             constexpr int RSTEP = 256 / C::FT;
             const int c = threadIdx.x % C::FT, m0 = threadIdx.x / C::FT;
             if (c < n_in) {
-                float* __restrict__ q0 = o + c;
-                if (c >= n_live) {
-                    for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = 0.0f;
-                } else if (clampu) {
-                    for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
-                        float v[8];
+                if (OUT16) {
+                    __half* __restrict__ q0 = reinterpret_cast<__half*>(p.out) + (int64_t)t.b * p.out_batch_stride + t.t0 + c;
+                    const __half thr_h = __ushort_as_half(fe_f2h_rn(thr));
+                    if (c >= n_live) {
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = __ushort_as_half(0);
+                    } else if (clampu) {
+                        for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
+                            __half v[8];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int m = mb + j * RSTEP;
-                            v[j] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr;
+                            for (int j = 0; j < 8; ++j) {
+                                const int m = mb + j * RSTEP;
+                                v[j] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr_h;
+                            }
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const int m = mb + j * RSTEP;
+                                if (m < NMELS && __half2float(v[j]) < __half2float(thr_h)) q0[(int64_t)m * p.T_out] = thr_h;
+                            }
                         }
+                    }
+                } else {
+                    float* __restrict__ q0 = reinterpret_cast<float*>(p.out) + (int64_t)t.b * p.out_batch_stride + t.t0 + c;
+                    if (c >= n_live) {
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = 0.0f;
+                    } else if (clampu) {
+                        for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
+                            float v[8];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const int m = mb + j * RSTEP;
-                            if (m < NMELS && v[j] < thr) q0[(int64_t)m * p.T_out] = thr;
+                            for (int j = 0; j < 8; ++j) {
+                                const int m = mb + j * RSTEP;
+                                v[j] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr;
+                            }
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const int m = mb + j * RSTEP;
+                                if (m < NMELS && v[j] < thr) q0[(int64_t)m * p.T_out] = thr;
+                            }
                         }
                     }
                 }
@@ -426,8 +450,10 @@ int check_device_arch() {
         FE_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
         state[dev] = (major == 10) ? 1 : -1;
         if (state[dev] == 1) {
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<80>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<80, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<80, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
             FE_CUDA(cudaDeviceGetAttribute(&g_num_sms[dev < 64 ? dev : 0], cudaDevAttrMultiProcessorCount, dev));
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeKCfg::SMEM_BYTES));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
@@ -519,10 +545,10 @@ int64_t b200feat_workspace_bytes(int32_t kind, int32_t B, int64_t L) {
 }
 
 // ------------------------------------------------------------------------------------------ Whisper
-int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
-                            int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
-                            float* out, int64_t out_batch_stride, int64_t T_out,
-                            void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+static int whisper_logmel_impl(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                               int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                               void* out, bool out16, int64_t out_batch_stride, int64_t T_out,
+                               void* workspace, int64_t workspace_bytes, void* cuda_stream) {
     if (int rc = common_checks("whisper_logmel", wave, out, B, L, wave_stride)) return rc;
     if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "whisper_logmel: Unsupported n_mels: %d", n_mels);
     if (padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel: padding %d < 0", padding);
@@ -560,8 +586,10 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
     {
         const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
         ProfScope ps(st, 0);
-        if (n_mels == 80) fe_whisper2_kernel<80><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
-        else fe_whisper2_kernel<128><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        if (n_mels == 80 && !out16) fe_whisper2_kernel<80, false><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        else if (n_mels == 80) fe_whisper2_kernel<80, true><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        else if (!out16) fe_whisper2_kernel<128, false><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        else fe_whisper2_kernel<128, true><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
         g_launches++;
     }
     {
@@ -569,12 +597,30 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
         const int need = (p.total_units + 255) / 256;
         const unsigned grid = (unsigned)(need < sms * 8 ? need : sms * 8);
         ProfScope ps(st, 1);
-        if (n_mels == 80) fe_whisper2_fixup_kernel<80><<<grid, 256, 0, st>>>(p);
-        else fe_whisper2_fixup_kernel<128><<<grid, 256, 0, st>>>(p);
+        if (n_mels == 80 && !out16) fe_whisper2_fixup_kernel<80, false><<<grid, 256, 0, st>>>(p);
+        else if (n_mels == 80) fe_whisper2_fixup_kernel<80, true><<<grid, 256, 0, st>>>(p);
+        else if (!out16) fe_whisper2_fixup_kernel<128, false><<<grid, 256, 0, st>>>(p);
+        else fe_whisper2_fixup_kernel<128, true><<<grid, 256, 0, st>>>(p);
         g_launches++;
     }
     FE_CUDA(cudaGetLastError());
     return 0;
+}
+
+int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                            int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                            float* out, int64_t out_batch_stride, int64_t T_out,
+                            void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    return whisper_logmel_impl(wave, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out, false, out_batch_stride, T_out,
+                               workspace, workspace_bytes, cuda_stream);
+}
+
+int b200feat_whisper_logmel_f16(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                                int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                                void* out_f16, int64_t out_batch_stride, int64_t T_out,
+                                void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    return whisper_logmel_impl(wave, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out_f16, true, out_batch_stride, T_out,
+                               workspace, workspace_bytes, cuda_stream);
 }
 
 // ------------------------------------------------------------------------------------------ CosyVoice

@@ -39,8 +39,8 @@ struct FeWhisper2Params {
     int32_t padding;           // zeros appended to every clip before framing
     int32_t n_mels;            // 80 | 128
     int32_t norm_mode;         // FE_NORM_*
-    float* out;                // (B, n_mels, T_out)
-    int64_t out_batch_stride;  // floats between clips in `out`
+    void* out;                 // (B, n_mels, T_out), float32 or float16 (the kernel's OUT16 template argument)
+    int64_t out_batch_stride;  // elements between clips in `out`
     int64_t T_out;             // frames per output row (row stride)
     int32_t units_per_clip;    // ceil(T_out / 64)
     int32_t total_units;       // B * units_per_clip
@@ -343,23 +343,59 @@ FE_HD FE_INLINE float fe_min3(float a, float b, float c) {
 #endif
 }
 // base + m * row_bytes in ONE instruction (IMAD.WIDE.U32 with the immediate m); row_bytes < 2^26
-FE_HD FE_INLINE float* fe_row_ptr(float* base, unsigned row_bytes, unsigned m) {
+FE_HD FE_INLINE char* fe_row_ptr(char* base, unsigned row_bytes, unsigned m) {
 #if defined(__CUDA_ARCH__)
-    float* r;
+    char* r;
     asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(row_bytes), "r"(m), "l"(base));
     return r;
 #else
-    return reinterpret_cast<float*>(reinterpret_cast<char*>(base) + (size_t)row_bytes * m);
+    return base + (size_t)row_bytes * m;
 #endif
 }
 // global stores through a pointer built by fe_row_ptr: STG instead of a generic ST, and no "memory" clobber --
 // the output is write-only for this kernel, so shared-memory loads of the next filter may move above the store
 template <int BYTE_OFF>
-FE_HD FE_INLINE void fe_stg(float* q, float v) {
+FE_HD FE_INLINE void fe_stg(char* q, float v) {
 #if defined(__CUDA_ARCH__)
     asm volatile("st.global.f32 [%0+%1], %2;" ::"l"(q), "n"(BYTE_OFF), "f"(v));
 #else
-    *reinterpret_cast<float*>(reinterpret_cast<char*>(q) + BYTE_OFF) = v;
+    *reinterpret_cast<float*>(q + BYTE_OFF) = v;
+#endif
+}
+// float32 -> IEEE binary16 bits, round to nearest even (what torch's .to(float16) does); the host form is the plain
+// bit manipulation so that the g++ emulation needs no CUDA header
+FE_HD FE_INLINE unsigned short fe_f2h_rn(float v) {
+#if defined(__CUDA_ARCH__)
+    unsigned short h;
+    asm("cvt.rn.f16.f32 %0, %1;" : "=h"(h) : "f"(v));
+    return h;
+#else
+    union { float f; unsigned u; } c; c.f = v;
+    const unsigned sign = (c.u >> 16) & 0x8000u, a = c.u & 0x7fffffffu;
+    if (a > 0x7f800000u) return (unsigned short)(sign | 0x7e00u);            // NaN
+    if (a >= 0x477ff000u) return (unsigned short)(sign | 0x7c00u);           // >= 65520 (and inf) -> inf
+    if (a < 0x33000001u) return (unsigned short)sign;                        // <= 2^-25 -> 0
+    if (a < 0x38800000u) {                                                   // subnormal half
+        const int shift = 126 - (int)(a >> 23);                             // 14..24
+        const unsigned m = (a & 0x7fffffu) | 0x800000u;
+        unsigned r = m >> shift;
+        const unsigned rem = m & ((1u << shift) - 1u), half = 1u << (shift - 1);
+        if (rem > half || (rem == half && (r & 1u))) ++r;
+        return (unsigned short)(sign | r);
+    }
+    unsigned r = ((a - 0x38000000u) >> 13);
+    const unsigned rem = a & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (r & 1u))) ++r;
+    return (unsigned short)(sign | r);
+#endif
+}
+template <int BYTE_OFF>
+FE_HD FE_INLINE void fe_stg_h(char* q, float v) {
+    const unsigned short h = fe_f2h_rn(v);
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.b16 [%0+%1], %2;" ::"l"(q), "n"(BYTE_OFF), "h"(h));
+#else
+    *reinterpret_cast<unsigned short*>(q + BYTE_OFF) = h;
 #endif
 }
 // log2 without the 1e-10 floor: 0 (and flushed subnormals) -> -inf; the floor is applied with the clamp
@@ -382,14 +418,14 @@ struct FeW2MelCtx {
     const char* Pl;      // this lane's row of power pairs
     const char* wtab;    // padded weights (shared memory)
     const int2* desc;    // descriptors (shared memory)
-    float* obase;        // out + clip offset + first frame of the pair
+    char* obase;         // out + clip offset + first frame of the pair
     unsigned rs4;        // output row pitch in bytes
     fe2 one;             // 1 for live frames, NaN for dead ones
     bool la, lb;
     float mn, mx;
 };
 
-template <int CAP>
+template <int CAP, bool OUT16>
 FE_HD FE_INLINE void fe_w2_mel_class(FeW2MelCtx& c, int i0, int i1) {
     typedef FeW2Cfg C;
 #pragma unroll(CAP <= 2 ? 4 : 2)
@@ -421,9 +457,14 @@ FE_HD FE_INLINE void fe_w2_mel_class(FeW2MelCtx& c, int i0, int i1) {
             acc = fe_add(acc, acc2);
         }
         const fe2 y = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(acc.x), fe_w2_lg2(acc.y)), c.one);   // (log10(v) + 4) / 4
-        float* o = fe_row_ptr(c.obase, c.rs4, (unsigned)d.x >> 16);
-        if (c.la) fe_stg<0>(o, y.x);
-        if (c.lb) fe_stg<4 * C::LANES>(o, y.y);
+        char* o = fe_row_ptr(c.obase, c.rs4, (unsigned)d.x >> 16);
+        if (OUT16) {   // min/max below stay on the unrounded values: the fix-up decides in float32 like the reference
+            if (c.la) fe_stg_h<0>(o, y.x);
+            if (c.lb) fe_stg_h<2 * C::LANES>(o, y.y);
+        } else {
+            if (c.la) fe_stg<0>(o, y.x);
+            if (c.lb) fe_stg<4 * C::LANES>(o, y.y);
+        }
         c.mx = fe_max3(c.mx, y.x, y.y);
         c.mn = fe_min3(c.mn, y.x, y.y);
     }
@@ -439,19 +480,19 @@ template <> struct FeW2MelCaps<128> {
     static constexpr int N = FE_MELLOOP_W128_NCLS;
     static FE_HD constexpr int cap(int k) { constexpr int c[N] = {FE_MELLOOP_W128_CAPS}; return c[k]; }
 };
-template <int NMELS, int K, bool END = (K == FeW2MelCaps<NMELS>::N)>
+template <int NMELS, bool OUT16, int K, bool END = (K == FeW2MelCaps<NMELS>::N)>
 struct FeW2MelRun {
     static FE_HD FE_INLINE void run(FeW2MelCtx& c, const int* r) {
-        fe_w2_mel_class<FeW2MelCaps<NMELS>::cap(K)>(c, r[K], r[K + 1]);
-        FeW2MelRun<NMELS, K + 1>::run(c, r);
+        fe_w2_mel_class<FeW2MelCaps<NMELS>::cap(K), OUT16>(c, r[K], r[K + 1]);
+        FeW2MelRun<NMELS, OUT16, K + 1>::run(c, r);
     }
 };
-template <int NMELS, int K>
-struct FeW2MelRun<NMELS, K, true> {
+template <int NMELS, bool OUT16, int K>
+struct FeW2MelRun<NMELS, OUT16, K, true> {
     static FE_HD FE_INLINE void run(FeW2MelCtx&, const int*) {}
 };
 
-template <int NMELS>
+template <int NMELS, bool OUT16 = false>
 FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int lane, int warp) {
     typedef FeW2Cfg C;
     constexpr int NCLS = FeW2MelCaps<NMELS>::N;
@@ -462,8 +503,9 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     c.Pl = reinterpret_cast<const char*>(reinterpret_cast<const fe2*>(sm + C::OFF_P) + C::PSZ * lane);
     c.wtab = reinterpret_cast<const char*>(sm + C::OFF_MW);
     c.desc = reinterpret_cast<const int2*>(sm + C::OFF_MDESC);
-    c.obase = p.out + (int64_t)t.b * p.out_batch_stride + fa;
-    c.rs4 = (unsigned)p.T_out * 4u;                // row pitch in bytes; the host guarantees T_out < 2^24
+    constexpr int ESZ = OUT16 ? 2 : 4;
+    c.obase = reinterpret_cast<char*>(p.out) + ((int64_t)t.b * p.out_batch_stride + fa) * ESZ;
+    c.rs4 = (unsigned)p.T_out * (unsigned)ESZ;     // row pitch in bytes; the host guarantees T_out < 2^24
     union { unsigned u; float f; } qnan;
     qnan.u = 0x7fc00000u;
     c.one = fe_mk2(c.la ? 1.0f : qnan.f, c.lb ? 1.0f : qnan.f);
@@ -471,7 +513,7 @@ FE_HD FE_INLINE fe2 fe_w2_phase_mel(const FeWhisper2Params& p, const FeW2Unit& t
     int r[NCLS + 1];
 #pragma unroll
     for (int k = 0; k <= NCLS; ++k) r[k] = ranges[k];
-    FeW2MelRun<NMELS, 0>::run(c, r);
+    FeW2MelRun<NMELS, OUT16, 0>::run(c, r);
     return fe_mk2(c.mn, c.mx);
 }
 

@@ -10,7 +10,7 @@
 #include "fe_whisper2.cuh"
 
 // one unit at a time: loader threads, then the compute warps phase by phase (what the named barriers order on the GPU)
-template <int NMELS>
+template <int NMELS, bool OUT16>
 static void run_whisper(const FeWhisper2Params& p) {
     typedef FeW2Cfg C;
     std::vector<float> sm(C::SMEM_FLOATS);
@@ -31,7 +31,7 @@ static void run_whisper(const FeWhisper2Params& p) {
             for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_a(sm.data(), l, w);
             for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_b(sm.data(), l, w);
             for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) {
-                const fe2 mm = fe_w2_phase_mel<NMELS>(p, t, sm.data(), l, w);
+                const fe2 mm = fe_w2_phase_mel<NMELS, OUT16>(p, t, sm.data(), l, w);
                 mn = std::min(mn, mm.x); mx = std::max(mx, mm.y);
             }
         }
@@ -41,8 +41,27 @@ static void run_whisper(const FeWhisper2Params& p) {
     }
 }
 
-extern "C" int emu_whisper(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
-                           int n_mels, int padding, int norm_mode, float* out, int64_t T_out) {
+// float32 -> binary16 -> float32 (host form of fe_f2h_rn; the inverse is exact)
+static float half_bits_to_float(unsigned short h) {
+    const unsigned sign = (unsigned)(h & 0x8000u) << 16, e = (h >> 10) & 31u, m = h & 1023u;
+    union { unsigned u; float f; } c;
+    if (e == 0) {
+        c.f = (float)m * 5.9604644775390625e-08f;            // m * 2^-24
+        c.u |= sign;
+    } else if (e == 31) {
+        c.u = sign | 0x7f800000u | (m << 13);
+    } else {
+        c.u = sign | ((e + 112u) << 23) | (m << 13);
+    }
+    return c.f;
+}
+
+extern "C" void emu_f2h(const float* in, unsigned short* out, int64_t n) {
+    for (int64_t i = 0; i < n; ++i) out[i] = fe_f2h_rn(in[i]);
+}
+
+static int emu_whisper_any(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                           int n_mels, int padding, int norm_mode, void* out, bool out16, int64_t T_out) {
     typedef FeW2Cfg C;
     std::vector<int> keys(B > 0 ? B : 1, FE_KEY_INIT);
     FeWhisper2Params p;
@@ -53,19 +72,41 @@ extern "C" int emu_whisper(const float* wave, const int64_t* lengths, int B, int
     p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
     std::vector<float2> mm((size_t)std::max(p.total_units, 1));
     p.max_keys = keys.data(); p.unit_minmax = mm.data();
-    if (n_mels == 80) run_whisper<80>(p); else if (n_mels == 128) run_whisper<128>(p); else return -1;
-    // the fix-up kernel's arithmetic, applied to every element
+    if (n_mels == 80 && !out16) run_whisper<80, false>(p);
+    else if (n_mels == 80) run_whisper<80, true>(p);
+    else if (n_mels == 128 && !out16) run_whisper<128, false>(p);
+    else if (n_mels == 128) run_whisper<128, true>(p);
+    else return -1;
+    // the fix-up kernel's arithmetic, applied to every element (float16: on the rounded values, against the
+    // rounded threshold, as the kernel does)
     for (int b = 0; b < B; ++b) {
         const float thr = fe_w2_threshold(fe_key_float(keys[norm_mode == FE_NORM_PER_CALL ? 0 : b]));
         const int64_t len = fe_clip_len(lengths, b, L);
         const int64_t Tb = std::min<int64_t>((len + padding) / 160, T_out);
         for (int m = 0; m < n_mels; ++m)
             for (int64_t t = 0; t < T_out; ++t) {
-                float& v = out[(int64_t)b * p.out_batch_stride + m * T_out + t];
-                v = t < Tb ? (v < thr ? thr : v) : 0.0f;
+                const int64_t i = (int64_t)b * p.out_batch_stride + m * T_out + t;
+                if (out16) {
+                    unsigned short& h = static_cast<unsigned short*>(out)[i];
+                    const unsigned short th = fe_f2h_rn(thr);
+                    h = t < Tb ? (half_bits_to_float(h) < half_bits_to_float(th) ? th : h) : (unsigned short)0;
+                } else {
+                    float& v = static_cast<float*>(out)[i];
+                    v = t < Tb ? (v < thr ? thr : v) : 0.0f;
+                }
             }
     }
     return 0;
+}
+
+extern "C" int emu_whisper(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                           int n_mels, int padding, int norm_mode, float* out, int64_t T_out) {
+    return emu_whisper_any(wave, lengths, B, L, stride, n_mels, padding, norm_mode, out, false, T_out);
+}
+
+extern "C" int emu_whisper_f16(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                               int n_mels, int padding, int norm_mode, unsigned short* out, int64_t T_out) {
+    return emu_whisper_any(wave, lengths, B, L, stride, n_mels, padding, norm_mode, out, true, T_out);
 }
 
 // ------------------------------------------------------------------------------------------ kaldi

@@ -36,6 +36,16 @@ def emu_whisper(emu, x, n_mels=80, padding=0, norm=0, lengths=None):
     return out
 
 
+def emu_whisper_f16(emu, x, n_mels=80, padding=0, norm=0, lengths=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    T = (L + padding) // 160
+    out = np.full((B, n_mels, T), 7.0, dtype=np.float16)
+    keep, lp = _lens(lengths)
+    assert emu.emu_whisper_f16(x.ctypes.data_as(vp), lp, B, L, L, n_mels, padding, norm, out.ctypes.data_as(vp), T) == 0
+    return out
+
+
 def emu_kaldi(emu, x, cmn=1, lengths=None):
     x = np.ascontiguousarray(x, dtype=np.float32)
     B, L = x.shape
@@ -82,6 +92,37 @@ def test_whisper_speech_sine_zeros_percall_ragged(emu):
     ref = oracle.whisper_log_mel(x[1, :5003], 80, dtype=torch.float64).numpy()
     assert np.abs(got[1, :, :ref.shape[1]] - ref).max() <= 1e-4
     assert not got[1, :, ref.shape[1]:].any()
+
+
+def test_float_to_half_converter(emu):
+    """fe_f2h_rn's host form (the device form is cvt.rn.f16.f32) against torch's float32 -> float16 cast."""
+    g = torch.Generator().manual_seed(3)
+    v = torch.cat([torch.randn(200000, generator=g) * 2.0, torch.randn(50000, generator=g) * 1e-5,
+                   torch.randn(50000, generator=g) * 7e4,
+                   torch.tensor([0.0, -0.0, 1.0, -1.5, 65504.0, 65519.9, 65520.0, 1e9, float("inf"), -float("inf"),
+                                 2.0 ** -24, 2.0 ** -25, 2.0 ** -25 * 1.0001, 6.1e-5, 6.097e-5, 1.00048828125, 1.0009765625])])
+    # every half value and the midpoints between neighbours (ties to even)
+    h = torch.arange(0, 0x7c00, dtype=torch.int16).view(torch.float16).float()
+    v = torch.cat([v, h, -h, (h[:-1] + h[1:]) / 2]).contiguous()
+    out = np.zeros(v.numel(), dtype=np.uint16)
+    emu.emu_f2h(v.numpy().ctypes.data_as(vp), out.ctypes.data_as(vp), v.numel())
+    ref = v.to(torch.float16).view(torch.int16).numpy().view(np.uint16)
+    assert np.array_equal(out, ref)
+
+
+def test_whisper_f16_output_is_the_rounded_f32_output(emu):
+    """float16 store path of phase M + the fix-up in the half domain == float32 result cast to half, bit for bit:
+    noise (no clamp), speech-like (clamp active), per-call norm, ragged with zero fill."""
+    gen = torch.Generator().manual_seed(11)
+    cases = [((0.1 * torch.randn(2, 12000, generator=gen)).clamp(-1, 1), dict(n_mels=128)),
+             (speech_like(gen, 2, 16000, 16000), dict(n_mels=80)),
+             (speech_like(gen, 2, 16000, 16000), dict(n_mels=128, norm=1)),
+             (speech_like(gen, 2, 16000, 16000), dict(n_mels=80, lengths=[16000, 5003], padding=320))]
+    for x, kw in cases:
+        f32 = emu_whisper(emu, x.numpy(), **kw)
+        f16 = emu_whisper_f16(emu, x.numpy(), **kw)
+        assert f16.dtype == np.float16 and f16.shape == f32.shape
+        assert np.array_equal(f16.view(np.uint16), torch.from_numpy(f32).to(torch.float16).numpy().view(np.uint16))
 
 
 @pytest.mark.parametrize("B,L", [(2, 16000), (1, 80000), (3, 999), (1, 400)])

@@ -113,6 +113,48 @@ def test_whisper_host_path_equals_device_path(fe):
     assert torch.equal(dev, host)
 
 
+def _same_half_bits(a16, b32):
+    return torch.equal(a16.view(torch.int16), b32.to(torch.float16).view(torch.int16))
+
+
+def test_whisper_f16_output_is_the_rounded_f32_output(fe):
+    """b200feat_whisper_logmel_f16: the half tensor whisper.transcribe(fp16=True) feeds the
+    encoder == our float32 result cast with .to(float16), bit for bit; and within float16 resolution of the oracle."""
+    gen = torch.Generator().manual_seed(21)
+    sp = speech_like(gen, 5, 48000, 16000)
+    lens = [48000, 31999, 5003, 777, 48000]
+    cases = [(noise(9, 30011, 4), dict(n_mels=128)),
+             (sp, dict(n_mels=80)),                                   # clamp active
+             (sp, dict(n_mels=128, norm="per_call")),
+             (sp, dict(n_mels=80, lengths=lens, padding=4800)),        # ragged: zero fill in the half domain
+             (torch.zeros(2, 16000), dict(n_mels=80))]
+    for x, kw in cases:
+        f32 = fe.whisper_log_mel_batch(x.cuda(), **kw)
+        f16 = fe.whisper_log_mel_batch(x.cuda(), out_dtype=torch.float16, **kw)
+        assert f16.dtype == torch.float16 and f16.shape == f32.shape
+        assert _same_half_bits(f16, f32)
+        host = fe.whisper_log_mel_host(x.pin_memory(), out_dtype=torch.float16, **kw)
+        assert host.dtype == torch.float16 and torch.equal(host.view(torch.int16), f16.cpu().view(torch.int16))
+    ref = oracle.whisper_log_mel(sp, 80, dtype=torch.float64, norm="per_clip")
+    f16 = fe.whisper_log_mel_batch(sp.cuda(), n_mels=80, out_dtype=torch.float16).cpu()
+    assert (f16.double() - ref).abs().max() <= TOL + 2.0 ** -11 * 1.5   # half an ulp of float16 at |y| <= 1.5, on top of TOL
+    # preallocated out selects the dtype; a wrong dtype is refused
+    out = torch.empty((5, 80, 300), dtype=torch.float16, device="cuda")
+    assert fe.whisper_log_mel_batch(sp.cuda(), n_mels=80, out=out) is out and torch.equal(out.cpu().view(torch.int16), f16.view(torch.int16))
+    with pytest.raises(ValueError):
+        fe.whisper_log_mel_batch(sp.cuda(), out_dtype=torch.bfloat16)
+
+
+def test_whisper_f16_full_size(fe):
+    """BASELINE config 2 shape with the half epilogue: equal to the rounded float32 result on all 393 M values."""
+    g = torch.Generator(device="cuda").manual_seed(77)
+    x = (0.1 * torch.randn(1024, 480000, generator=g, device="cuda")).clamp_(-1, 1)
+    x[3, 100000:].zero_()                                              # a clip whose tail needs the clamp
+    f32 = fe.whisper_log_mel_batch(x, n_mels=128)
+    f16 = fe.whisper_log_mel_batch(x, n_mels=128, out_dtype=torch.float16)
+    assert _same_half_bits(f16, f32)
+
+
 def test_whisper_full_size_properties(fe):
     """BASELINE config 2: 1024 x 30 s, 128 bins."""
     B, L = 1024, 480000
