@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libb200feat.so")
 
 KIND_WHISPER, KIND_COSY, KIND_KALDI = 0, 1, 2
 NORM_PER_CLIP, NORM_PER_CALL = 0, 1
+DT_F32, DT_F16, DT_S16 = 0, 1, 2
 
 # every symbol include/b200feat.h declares: (restype, argtypes)
 _c = ctypes
@@ -23,9 +24,9 @@ SYMBOLS = {
     "b200feat_whisper_logmel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                            _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int64,
                                            _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
-    "b200feat_whisper_logmel_f16": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
-                                               _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int64,
-                                               _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
+    "b200feat_whisper_logmel_ex": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
+                                              _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32, _c.c_int64,
+                                              _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
     "b200feat_cosy_mel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                      _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64,
                                      _c.c_void_p]),
@@ -34,8 +35,9 @@ SYMBOLS = {
                                         _c.c_int64, _c.c_void_p]),
     "b200feat_whisper_logmel_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,
                                                 _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32]),
-    "b200feat_whisper_logmel_f16_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,
-                                                    _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32]),
+    "b200feat_whisper_logmel_ex_host": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_void_p, _c.c_int32, _c.c_int64,
+                                                   _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32,
+                                                   _c.c_int32]),
     "b200feat_cosy_mel_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_void_p,
                                           _c.c_int32]),
     "b200feat_kaldi_fbank_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,

@@ -30,6 +30,7 @@ from ._lib import lib, check, KIND_WHISPER, KIND_COSY, KIND_KALDI, NORM_PER_CLIP
 WHISPER_SR, WHISPER_N_FFT, WHISPER_HOP = 16000, 400, 160
 COSY_PARAMS = dict(n_fft=1920, num_mels=80, sampling_rate=24000, hop_size=480, win_size=1920, fmin=0, fmax=8000)
 _NORMS = {"per_clip": NORM_PER_CLIP, "per_call": NORM_PER_CALL}
+_DTYPES = {torch.float32: _lib.DT_F32, torch.float16: _lib.DT_F16, torch.int16: _lib.DT_S16}
 
 
 def num_frames(kind, n_samples, padding=0):
@@ -70,11 +71,13 @@ def _cuda_device(device=None):
     return device
 
 
-def _as_float_tensor(x, what):
+def _as_float_tensor(x, what, allow_pcm16=False):
     if isinstance(x, np.ndarray):
         x = torch.from_numpy(x)
     if not torch.is_tensor(x):
         raise TypeError(f"{what} must be a torch.Tensor or numpy.ndarray, got {type(x).__name__}")
+    if allow_pcm16 and x.dtype == torch.int16:
+        return x
     if not x.is_floating_point():
         raise TypeError(f"{what} must be floating point (the reference's torch.stft rejects {x.dtype})")
     return x
@@ -96,8 +99,8 @@ def _lengths_dev(lengths, B, device):
 
 
 def _prep_wave(wave, device):
-    """(B, L) float32 on `device` with a usable row stride; returns (tensor, stride)."""
-    w = wave.to(device=device, dtype=torch.float32)
+    """(B, L) float32 (int16 PCM stays int16) on `device` with a usable row stride; returns (tensor, stride)."""
+    w = wave.to(device=device, dtype=torch.int16 if wave.dtype == torch.int16 else torch.float32)
     if w.dim() != 2:
         raise ValueError(f"expected a (B, L) waveform batch, got shape {tuple(w.shape)}")
     if w.stride(1) != 1 or (w.shape[0] > 1 and w.stride(0) < w.shape[1]):
@@ -126,10 +129,11 @@ def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_cl
     """(B, L) waveform batch on a CUDA device -> (B, n_mels, (L + padding) // 160) log-mel, async on the
     current stream.  `lengths` (B,) marks ragged clips (frames past a clip's own count are 0).
     out_dtype=torch.float16 writes the encoder-ready half tensor directly: bit-identical to `.to(torch.float16)` of
-    the float32 result (the cast whisper.transcribe(fp16=True) applies, whisper/transcribe.py `mel_segment.to(dtype)`)."""
+    the float32 result (the cast whisper.transcribe(fp16=True) applies, whisper/transcribe.py `mel_segment.to(dtype)`).
+    An int16 `wave` is taken as PCM and scaled by 1/32768 inside the loader (whisper.audio.load_audio's conversion)."""
     assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
     out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
-    wave = _as_float_tensor(wave, "wave")
+    wave = _as_float_tensor(wave, "wave", allow_pcm16=True)
     device = _cuda_device(wave.device if wave.is_cuda else None)
     w, stride = _prep_wave(wave, device)
     B, L = w.shape
@@ -142,10 +146,14 @@ def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_cl
         return out
     ln = _lengths_dev(lengths, B, device)
     ws, nws = _workspace(KIND_WHISPER, B, L + int(padding), device)
-    fn = lib.b200feat_whisper_logmel if out_dtype == torch.float32 else lib.b200feat_whisper_logmel_f16
     with torch.cuda.device(device):
-        rc = fn(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
-                _ptr(out), n_mels * T, T, _ptr(ws), nws, _stream(device))
+        if w.dtype == torch.float32 and out_dtype == torch.float32:
+            rc = lib.b200feat_whisper_logmel(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
+                                             _ptr(out), n_mels * T, T, _ptr(ws), nws, _stream(device))
+        else:
+            rc = lib.b200feat_whisper_logmel_ex(_ptr(w), _DTYPES[w.dtype], _ptr(ln), B, L, stride, n_mels, int(padding),
+                                                _NORMS[norm], _ptr(out), _DTYPES[out_dtype], n_mels * T, T, _ptr(ws), nws,
+                                                _stream(device))
     check(rc, "b200feat_whisper_logmel")
     return out
 
@@ -195,11 +203,12 @@ def kaldi_fbank_batch(wave, lengths=None, subtract_mean=True, out=None):
 
 
 # ----------------------------------------------------------------------------------------- host-buffer (end-to-end) API
-def _host_2d(x, what):
-    x = _as_float_tensor(x, what)
+def _host_2d(x, what, allow_pcm16=False):
+    x = _as_float_tensor(x, what, allow_pcm16)
     if x.is_cuda:
         raise ValueError(f"{what}: the *_host entry points take host memory")
-    x = x.to(torch.float32)
+    if x.dtype != torch.int16:
+        x = x.to(torch.float32)
     if x.dim() != 2:
         raise ValueError(f"expected a (B, L) waveform batch, got shape {tuple(x.shape)}")
     return x.contiguous()
@@ -229,15 +238,18 @@ def whisper_log_mel_host(wave, lengths=None, n_mels=80, padding=0, norm="per_cli
     out_dtype=torch.float16: half features (see whisper_log_mel_batch), half the D2H bytes."""
     assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
     out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
-    w = _host_2d(wave, "wave")
+    w = _host_2d(wave, "wave", allow_pcm16=True)
     B, L = w.shape
     T = (L + padding) // WHISPER_HOP
     dev = _cuda_device(device)
     out = _host_out((B, n_mels, T), out, pin_output, out_dtype)
     ln = _host_lengths(lengths, B)
     if B and T:
-        fn = lib.b200feat_whisper_logmel_host if out_dtype == torch.float32 else lib.b200feat_whisper_logmel_f16_host
-        rc = fn(_ptr(w), _ptr(ln), B, L, n_mels, int(padding), _NORMS[norm], _ptr(out), dev.index)
+        if w.dtype == torch.float32 and out_dtype == torch.float32:
+            rc = lib.b200feat_whisper_logmel_host(_ptr(w), _ptr(ln), B, L, n_mels, int(padding), _NORMS[norm], _ptr(out), dev.index)
+        else:
+            rc = lib.b200feat_whisper_logmel_ex_host(_ptr(w), _DTYPES[w.dtype], _ptr(ln), B, L, n_mels, int(padding),
+                                                     _NORMS[norm], _ptr(out), _DTYPES[out_dtype], dev.index)
         check(rc, "b200feat_whisper_logmel_host")
     return out
 

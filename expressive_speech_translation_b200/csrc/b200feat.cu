@@ -88,7 +88,7 @@ struct FeMbarWait {
 //            dependencies inside the interval ("B(u) has read the A planes" before A(u+1) stores into them,
 //            "P(u) complete" before M(u) reads it).  Warps of one SM sub-partition are in different phases at any
 //            time, so the shared-memory bursts of one overlap the FP32 work of another.
-template <int NMELS, bool OUT16>
+template <int NMELS, bool OUT16, bool IN16>
 __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhisper2Params p) {
     typedef FeW2Cfg C;
     extern __shared__ __align__(16) float sm[];
@@ -113,13 +113,13 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
         FeW2Stage stage;
         FeW2Unit t = fe_w2_unit(p, blockIdx.x);
         bool live = t.t0 < t.T, fast = live && fe_w2_interior(p, t);
-        if (fast) fe_w2_load_issue(p, t, ltid, stage);
+        if (fast) fe_w2_load_issue<IN16>(p, t, ltid, stage);
         for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1, ++it) {
             FE_TR(it, 0);
             if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
             FE_TR(it, 1);
-            if (fast) fe_w2_load_store(sm, ltid, stage);
-            else if (live) fe_w2_load_edge(p, t, sm, ltid);
+            if (fast) fe_w2_load_store<IN16>(sm, ltid, stage);
+            else if (live) fe_w2_load_edge<IN16>(p, t, sm, ltid);
             if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
             FE_TR(it, 2);
             fe_bar_arrive(FE_BAR_W_FULL, C::NT);
@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
                 t = fe_w2_unit(p, un);
                 live = t.t0 < t.T;
                 fast = live && fe_w2_interior(p, t);
-                if (fast) fe_w2_load_issue(p, t, ltid, stage);
+                if (fast) fe_w2_load_issue<IN16>(p, t, ltid, stage);
             }
             FE_TR(it, 3);
         }
@@ -376,6 +376,32 @@ __global__ void __launch_bounds__(FeCCfg::NT, 1) fe_cosy_kernel(const FeCosyPara
     fe_c_phase_mel(p, sm, tid, cta);
 }
 
+// the eight instantiations (mel bins x output dtype x input dtype) behind one switch
+template <class F>
+static int whisper2_for_each(F f) {
+    if (int rc = f(fe_whisper2_kernel<80, false, false>, 0)) return rc;
+    if (int rc = f(fe_whisper2_kernel<80, false, true>, 1)) return rc;
+    if (int rc = f(fe_whisper2_kernel<80, true, false>, 2)) return rc;
+    if (int rc = f(fe_whisper2_kernel<80, true, true>, 3)) return rc;
+    if (int rc = f(fe_whisper2_kernel<128, false, false>, 4)) return rc;
+    if (int rc = f(fe_whisper2_kernel<128, false, true>, 5)) return rc;
+    if (int rc = f(fe_whisper2_kernel<128, true, false>, 6)) return rc;
+    if (int rc = f(fe_whisper2_kernel<128, true, true>, 7)) return rc;
+    return 0;
+}
+static int whisper2_smem_attr() {
+    return whisper2_for_each([](void (*k)(const FeWhisper2Params), int) {
+        return cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES) == cudaSuccess ? 0 : 1;
+    });
+}
+static void launch_whisper2(int n_mels, bool out16, bool in16, unsigned grid, cudaStream_t st, const FeWhisper2Params& p) {
+    const int want = (n_mels == 128 ? 4 : 0) + (out16 ? 2 : 0) + (in16 ? 1 : 0);
+    whisper2_for_each([&](void (*k)(const FeWhisper2Params), int id) {
+        if (id == want) k<<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        return 0;
+    });
+}
+
 // =====================================================================================================
 // host side
 // =====================================================================================================
@@ -450,10 +476,7 @@ int check_device_arch() {
         FE_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
         state[dev] = (major == 10) ? 1 : -1;
         if (state[dev] == 1) {
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<80, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<128, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<80, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
-            FE_CUDA(cudaFuncSetAttribute(fe_whisper2_kernel<128, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW2Cfg::SMEM_BYTES));
+            if (whisper2_smem_attr()) return fail(B200FEAT_ECUDA, "cudaFuncSetAttribute(fe_whisper2_kernel, max dynamic shared memory) failed");
             FE_CUDA(cudaDeviceGetAttribute(&g_num_sms[dev < 64 ? dev : 0], cudaDevAttrMultiProcessorCount, dev));
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeKCfg::SMEM_BYTES));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
@@ -545,7 +568,7 @@ int64_t b200feat_workspace_bytes(int32_t kind, int32_t B, int64_t L) {
 }
 
 // ------------------------------------------------------------------------------------------ Whisper
-static int whisper_logmel_impl(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* lengths, int32_t B, int64_t L,
                                int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
                                void* out, bool out16, int64_t out_batch_stride, int64_t T_out,
                                void* workspace, int64_t workspace_bytes, void* cuda_stream) {
@@ -573,7 +596,8 @@ static int whisper_logmel_impl(const float* wave, const int64_t* lengths, int32_
 
     FeWhisper2Params p;
     memset(&p, 0, sizeof(p));
-    p.wave = wave; p.lengths = lengths; p.wave_stride = wave_stride; p.L = L; p.B = B;
+    p.wave = static_cast<const float*>(wave); p.in_s16 = in_s16 ? 1 : 0;
+    p.lengths = lengths; p.wave_stride = wave_stride; p.L = L; p.B = B;
     p.padding = padding; p.n_mels = n_mels; p.norm_mode = norm_mode;
     p.out = out; p.out_batch_stride = out_batch_stride; p.T_out = T_out;
     p.units_per_clip = (int32_t)units;
@@ -586,10 +610,7 @@ static int whisper_logmel_impl(const float* wave, const int64_t* lengths, int32_
     {
         const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
         ProfScope ps(st, 0);
-        if (n_mels == 80 && !out16) fe_whisper2_kernel<80, false><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
-        else if (n_mels == 80) fe_whisper2_kernel<80, true><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
-        else if (!out16) fe_whisper2_kernel<128, false><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
-        else fe_whisper2_kernel<128, true><<<grid, FeW2Cfg::NT, FeW2Cfg::SMEM_BYTES, st>>>(p);
+        launch_whisper2(n_mels, out16, in_s16, grid, st, p);
         g_launches++;
     }
     {
@@ -611,16 +632,25 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
                             int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
                             float* out, int64_t out_batch_stride, int64_t T_out,
                             void* workspace, int64_t workspace_bytes, void* cuda_stream) {
-    return whisper_logmel_impl(wave, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out, false, out_batch_stride, T_out,
-                               workspace, workspace_bytes, cuda_stream);
+    return whisper_logmel_impl(wave, false, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out, false,
+                               out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
 }
 
-int b200feat_whisper_logmel_f16(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
-                                int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
-                                void* out_f16, int64_t out_batch_stride, int64_t T_out,
-                                void* workspace, int64_t workspace_bytes, void* cuda_stream) {
-    return whisper_logmel_impl(wave, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out_f16, true, out_batch_stride, T_out,
-                               workspace, workspace_bytes, cuda_stream);
+static int whisper_ex_dtypes(const char* who, int32_t wave_dtype, int32_t out_dtype) {
+    if (wave_dtype != B200FEAT_F32 && wave_dtype != B200FEAT_S16)
+        return fail(B200FEAT_EINVAL, "%s: wave_dtype %d (B200FEAT_F32 or B200FEAT_S16)", who, wave_dtype);
+    if (out_dtype != B200FEAT_F32 && out_dtype != B200FEAT_F16)
+        return fail(B200FEAT_EINVAL, "%s: out_dtype %d (B200FEAT_F32 or B200FEAT_F16)", who, out_dtype);
+    return 0;
+}
+
+int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64_t* lengths, int32_t B, int64_t L,
+                               int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                               void* out, int32_t out_dtype, int64_t out_batch_stride, int64_t T_out,
+                               void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    if (int rc = whisper_ex_dtypes("whisper_logmel_ex", wave_dtype, out_dtype)) return rc;
+    return whisper_logmel_impl(wave, wave_dtype == B200FEAT_S16, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out,
+                               out_dtype == B200FEAT_F16, out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
 }
 
 // ------------------------------------------------------------------------------------------ CosyVoice

@@ -57,10 +57,11 @@ int64_t host_chunk_bytes() {
     return v;
 }
 
-// launch(d_wave, d_len_or_null, nclips, d_out (void*), d_ws, ws_bytes, stream) -> rc
+// launch(d_wave (void*), d_len_or_null, nclips, d_out (void*), d_ws, ws_bytes, stream) -> rc
 template <class Launch>
-int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L, int64_t ws_L,
+int host_pipeline(int kind, const void* wave_host_v, int64_t in_esz, const int64_t* lengths_host, int32_t B, int64_t L, int64_t ws_L,
                   int64_t out_per_clip, void* out_host_v, int64_t out_esz, int device, bool single_chunk, Launch launch) {
+    const char* wave_host = static_cast<const char*>(wave_host_v);
     char* out_host = static_cast<char*>(out_host_v);
     if (B < 0 || L < 0) return fail(B200FEAT_EINVAL, "host call: negative B or L");
     if (B == 0 || out_per_clip == 0) return 0;
@@ -72,7 +73,7 @@ int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host,
     Arena* a = arena_for(device);
     std::lock_guard<std::mutex> lk(a->mu);
 
-    const int64_t in_bytes = L * 4, out_bytes = out_per_clip * out_esz;
+    const int64_t in_bytes = L * in_esz, out_bytes = out_per_clip * out_esz;
     int64_t chunk = host_chunk_bytes() / (in_bytes + out_bytes);
     if (chunk < 1) chunk = 1;
     if (chunk > B || single_chunk) chunk = B;
@@ -91,11 +92,11 @@ int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host,
         const int slot = (int)(i % nslot);
         cudaStream_t st = a->streams[slot];
         char* sb = a->base + slot_bytes * slot;
-        float* d_wave = reinterpret_cast<float*>(sb);
+        void* d_wave = sb;
         void* d_out = sb + s_wave;
         int64_t* d_len = reinterpret_cast<int64_t*>(sb + s_wave + s_out);
         void* d_ws = sb + s_wave + s_out + s_len;
-        cudaError_t e = cudaMemcpyAsync(d_wave, wave_host + c0 * L, (size_t)nc * in_bytes, cudaMemcpyHostToDevice, st);
+        cudaError_t e = cudaMemcpyAsync(d_wave, wave_host + c0 * in_bytes, (size_t)nc * in_bytes, cudaMemcpyHostToDevice, st);
         if (e == cudaSuccess && lengths_host)
             e = cudaMemcpyAsync(d_len, lengths_host + c0, (size_t)nc * 8, cudaMemcpyHostToDevice, st);
         if (e != cudaSuccess) { rc = fail(B200FEAT_ECUDA, "host call: H2D copy failed: %s", cudaGetErrorString(e)); break; }
@@ -116,16 +117,16 @@ int host_pipeline(int kind, const float* wave_host, const int64_t* lengths_host,
 
 extern "C" {
 
-static int whisper_logmel_host_impl(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
+static int whisper_logmel_host_impl(const void* wave_host, bool in_s16, const int64_t* lengths_host, int32_t B, int64_t L,
                                     int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host, bool out16,
                                     int32_t device) {
     if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "whisper_logmel_host: Unsupported n_mels: %d", n_mels);
     if (padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel_host: padding < 0");
     const int64_t T = (L + padding) / FeW2Cfg::HOP;
-    return host_pipeline(B200FEAT_KIND_WHISPER, wave_host, lengths_host, B, L, L + padding, (int64_t)n_mels * T, out_host,
-                         out16 ? 2 : 4, device, norm_mode == FE_NORM_PER_CALL,
-                         [=](const float* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
-                             return whisper_logmel_impl(dw, dl, nc, L, L, n_mels, padding, norm_mode, dout, out16,
+    return host_pipeline(B200FEAT_KIND_WHISPER, wave_host, in_s16 ? 2 : 4, lengths_host, B, L, L + padding, (int64_t)n_mels * T,
+                         out_host, out16 ? 2 : 4, device, norm_mode == FE_NORM_PER_CALL,
+                         [=](const void* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return whisper_logmel_impl(dw, in_s16, dl, nc, L, L, n_mels, padding, norm_mode, dout, out16,
                                                         (int64_t)n_mels * T, T, ws, wsb, st);
                          });
 }
@@ -133,30 +134,32 @@ static int whisper_logmel_host_impl(const float* wave_host, const int64_t* lengt
 int b200feat_whisper_logmel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                                  int32_t n_mels, int32_t padding, int32_t norm_mode, float* out_host,
                                  int32_t device) {
-    return whisper_logmel_host_impl(wave_host, lengths_host, B, L, n_mels, padding, norm_mode, out_host, false, device);
+    return whisper_logmel_host_impl(wave_host, false, lengths_host, B, L, n_mels, padding, norm_mode, out_host, false, device);
 }
 
-int b200feat_whisper_logmel_f16_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
-                                     int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host_f16,
-                                     int32_t device) {
-    return whisper_logmel_host_impl(wave_host, lengths_host, B, L, n_mels, padding, norm_mode, out_host_f16, true, device);
+int b200feat_whisper_logmel_ex_host(const void* wave_host, int32_t wave_dtype, const int64_t* lengths_host, int32_t B,
+                                    int64_t L, int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host,
+                                    int32_t out_dtype, int32_t device) {
+    if (int rc = whisper_ex_dtypes("whisper_logmel_ex_host", wave_dtype, out_dtype)) return rc;
+    return whisper_logmel_host_impl(wave_host, wave_dtype == B200FEAT_S16, lengths_host, B, L, n_mels, padding, norm_mode,
+                                    out_host, out_dtype == B200FEAT_F16, device);
 }
 
 int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                            float* out_host, int32_t device) {
     const int64_t T = b200feat_num_frames(B200FEAT_KIND_COSY, L, 0);
-    return host_pipeline(B200FEAT_KIND_COSY, wave_host, lengths_host, B, L, L, (int64_t)FeCCfg::NMEL * T, out_host, 4, device, false,
-                         [=](const float* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
-                             return b200feat_cosy_mel(dw, dl, nc, L, L, static_cast<float*>(dout), (int64_t)FeCCfg::NMEL * T, T, ws, wsb, st);
+    return host_pipeline(B200FEAT_KIND_COSY, wave_host, 4, lengths_host, B, L, L, (int64_t)FeCCfg::NMEL * T, out_host, 4, device, false,
+                         [=](const void* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return b200feat_cosy_mel(static_cast<const float*>(dw), dl, nc, L, L, static_cast<float*>(dout), (int64_t)FeCCfg::NMEL * T, T, ws, wsb, st);
                          });
 }
 
 int b200feat_kaldi_fbank_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                               int32_t subtract_mean, float* out_host, int32_t device) {
     const int64_t T = b200feat_num_frames(B200FEAT_KIND_KALDI, L, 0);
-    return host_pipeline(B200FEAT_KIND_KALDI, wave_host, lengths_host, B, L, L, (int64_t)FeKCfg::NMEL * T, out_host, 4, device, false,
-                         [=](const float* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
-                             return b200feat_kaldi_fbank(dw, dl, nc, L, L, subtract_mean, static_cast<float*>(dout), (int64_t)FeKCfg::NMEL * T, T, ws, wsb, st);
+    return host_pipeline(B200FEAT_KIND_KALDI, wave_host, 4, lengths_host, B, L, L, (int64_t)FeKCfg::NMEL * T, out_host, 4, device, false,
+                         [=](const void* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return b200feat_kaldi_fbank(static_cast<const float*>(dw), dl, nc, L, L, subtract_mean, static_cast<float*>(dout), (int64_t)FeKCfg::NMEL * T, T, ws, wsb, st);
                          });
 }
 

@@ -31,7 +31,7 @@
 #include "fe_common.h"
 
 struct FeWhisper2Params {
-    const float* wave;         // (B, wave_stride) fp32
+    const float* wave;         // (B, wave_stride) fp32 -- or int16 PCM when in_s16 (then a `const short*` in disguise)
     const int64_t* lengths;    // nullable, device: valid samples per clip
     int64_t wave_stride;
     int64_t L;                 // samples per clip when lengths == nullptr (also the clamp for lengths)
@@ -45,6 +45,7 @@ struct FeWhisper2Params {
     int32_t units_per_clip;    // ceil(T_out / 64)
     int32_t total_units;       // B * units_per_clip
     int32_t vec_ok;            // wave base 16B-aligned and wave_stride % 4 == 0
+    int32_t in_s16;            // 1: wave holds int16 PCM, the loader scales by 1/32768 (whisper.audio.load_audio's cast)
     int32_t* max_keys;         // (B) or (1): order-preserving keys of the running max of (x + 4) / 4
     float2* unit_minmax;       // (total_units): (min, max) of the unit's live outputs
 };
@@ -117,15 +118,49 @@ struct FeW2Stage {
     float a[U], b[U];
 };
 
+// bit moves between int and float registers (host: memcpy)
+FE_HD FE_INLINE float fe_int_bits_as_float(int v) {
+#if defined(__CUDA_ARCH__)
+    return __int_as_float(v);
+#else
+    float f; memcpy(&f, &v, 4); return f;
+#endif
+}
+FE_HD FE_INLINE int fe_float_bits_as_int(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_int(f);
+#else
+    int v; memcpy(&v, &f, 4); return v;
+#endif
+}
+// int16 PCM -> float exactly as whisper.audio.load_audio does it: astype(float32) / 32768.0 (a power of two: exact)
+FE_HD FE_INLINE float fe_pcm16_to_float(int v) { return (float)v * (1.0f / 32768.0f); }
+
+// int16 input (IN16, a template argument of the kernel so that the float32 kernel carries none of this code): the
+// staged registers carry the raw sample as integer bits, the conversion happens at the store
+template <bool IN16 = false>
 FE_HD FE_INLINE void fe_w2_load_issue(const FeWhisper2Params& p, const FeW2Unit& t, int ltid, FeW2Stage& r) {
     typedef FeW2Cfg C;
-    const float* __restrict__ xa = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL) + ltid;
+    const int64_t off = (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 * C::HOP - C::PADL) + ltid;
+    if (IN16) {
+        const short* __restrict__ xs = reinterpret_cast<const short*>(p.wave) + off;
+#pragma unroll
+        for (int j = 0; j < FeW2Stage::U; ++j) {
+            if (j + 1 < FeW2Stage::U || ltid + j * C::NLT < C::RT) {
+                r.a[j] = fe_int_bits_as_float((int)xs[j * C::NLT]);
+                r.b[j] = fe_int_bits_as_float((int)xs[j * C::NLT + C::SEG]);
+            }
+        }
+        return;
+    }
+    const float* __restrict__ xa = p.wave + off;
 #pragma unroll
     for (int j = 0; j < FeW2Stage::U; ++j) {
         if (j + 1 < FeW2Stage::U || ltid + j * C::NLT < C::RT) { r.a[j] = xa[j * C::NLT]; r.b[j] = xa[j * C::NLT + C::SEG]; }
     }
 }
 
+template <bool IN16 = false>
 FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
     typedef FeW2Cfg C;
     // sample i = ltid + NLT * j sits in slot i + i / HOP.  NLT * 5 = 4 * HOP, so for j = 5 * m + c the slot is
@@ -138,6 +173,15 @@ FE_HD FE_INLINE void fe_w2_load_store(float* sm, int ltid, const FeW2Stage& r) {
     for (int c = 0; c < 5; ++c) {
         const unsigned ic = (unsigned)(ltid + C::NLT * c);
         base[c] = w + ic + ic / (unsigned)C::HOP;
+    }
+    if (IN16) {
+#pragma unroll
+        for (int j = 0; j < FeW2Stage::U; ++j) {
+            if (j + 1 < FeW2Stage::U || ltid + j * C::NLT < C::RT)
+                base[j % 5][(4 * C::HOP + 4) * (j / 5)] =
+                    fe_mk2(fe_pcm16_to_float(fe_float_bits_as_int(r.a[j])), fe_pcm16_to_float(fe_float_bits_as_int(r.b[j])));
+        }
+        return;
     }
 #pragma unroll
     for (int j = 0; j < FeW2Stage::U; ++j) {
@@ -182,10 +226,46 @@ FE_HD FE_INLINE void fe_w2_load_edge_t(const float* __restrict__ x, I g0, I len,
 #endif
 }
 
+// int16 edge units: cp.async cannot convert, so plain loads in batches of four independent pairs per thread
+template <class I>
+FE_HD FE_INLINE void fe_w2_load_edge_s16_t(const short* __restrict__ x, I g0, I len, I lp, float* sm, int ltid) {
+    typedef FeW2Cfg C;
+    fe2* __restrict__ w = reinterpret_cast<fe2*>(sm);
+    constexpr int NB = 4;
+#pragma unroll 1
+    for (int i0 = ltid; i0 < C::RT; i0 += NB * C::NLT) {
+        int va[NB], vb[NB];
+#pragma unroll
+        for (int k = 0; k < NB; ++k) {
+            const int i = i0 + k * C::NLT;
+            va[k] = 0; vb[k] = 0;
+            if (i < C::RT) {
+                const I ga = fe_w2_reflect<I>(g0 + i, lp), gb = fe_w2_reflect<I>(g0 + C::SEG + i, lp);
+                if (ga < len) va[k] = x[ga];
+                if (gb < len) vb[k] = x[gb];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NB; ++k) {
+            const int i = i0 + k * C::NLT;
+            if (i < C::RT) w[i + i / C::HOP] = fe_mk2(fe_pcm16_to_float(va[k]), fe_pcm16_to_float(vb[k]));
+        }
+    }
+}
+
+template <bool IN16 = false>
 FE_HD FE_INLINE void fe_w2_load_edge(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
     typedef FeW2Cfg C;
-    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
     const int64_t g0 = (int64_t)t.t0 * C::HOP - C::PADL;
+    if (IN16) {
+        const short* __restrict__ xs = reinterpret_cast<const short*>(p.wave) + (int64_t)t.b * p.wave_stride;
+        if (t.lp < ((int64_t)1 << 30) && g0 < ((int64_t)1 << 30))
+            fe_w2_load_edge_s16_t<int>(xs, (int)g0, (int)t.len, (int)t.lp, sm, ltid);
+        else
+            fe_w2_load_edge_s16_t<int64_t>(xs, g0, t.len, t.lp, sm, ltid);
+        return;
+    }
+    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
     if (t.lp < ((int64_t)1 << 30) && g0 < ((int64_t)1 << 30))
         fe_w2_load_edge_t<int>(x, (int)g0, (int)t.len, (int)t.lp, sm, ltid);
     else

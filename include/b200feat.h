@@ -71,14 +71,21 @@ int b200feat_whisper_logmel(const float* wave, const int64_t* lengths, int32_t B
                             float* out, int64_t out_batch_stride, int64_t T_out,
                             void* workspace, int64_t workspace_bytes, void* cuda_stream);
 
-/* The same featurizer writing IEEE binary16: out_f16 is (B, n_mels, T_out) float16, strides in elements.  Every value
- * is the float32 result rounded to nearest even, i.e. bit-identical to `mel.to(torch.float16)` -- the cast
- * whisper.transcribe applies to each segment when fp16=True, which is how the reference calls it
- * (/root/reference/Backend/services/cascaded_backend.py:158).  Halves the output bytes. */
-int b200feat_whisper_logmel_f16(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
-                                int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
-                                void* out_f16, int64_t out_batch_stride, int64_t T_out,
-                                void* workspace, int64_t workspace_bytes, void* cuda_stream);
+/* Extended Whisper entry point (the bytes either side of the path).
+ *   wave_dtype B200FEAT_S16: `wave` is int16 PCM as ffmpeg hands it to whisper.audio.load_audio; the loader scales by
+ *     1/32768 exactly like load_audio's `.astype(np.float32) / 32768.0` (UPSTREAM openai-whisper audio.py, reached from
+ *     /root/reference/Backend/services/cascaded_backend.py:158) -- half the input bytes.
+ *   out_dtype B200FEAT_F16: `out` is (B, n_mels, T_out) IEEE binary16; every value is the float32 result rounded to
+ *     nearest even, i.e. bit-identical to `mel.to(torch.float16)`, the cast whisper.transcribe applies to each segment
+ *     with fp16=True (how cascaded_backend.py:158 calls it) -- half the output bytes.
+ * Strides are in elements of the respective dtype.  B200FEAT_F32 / B200FEAT_F32 is b200feat_whisper_logmel. */
+#define B200FEAT_F32 0
+#define B200FEAT_F16 1
+#define B200FEAT_S16 2
+int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64_t* lengths, int32_t B, int64_t L,
+                               int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                               void* out, int32_t out_dtype, int64_t out_batch_stride, int64_t T_out,
+                               void* workspace, int64_t workspace_bytes, void* cuda_stream);
 
 /* CosyVoice 24 kHz mel (n_fft 1920, hop 480, 80 mels, ln, no normalisation).
  * out: (B, 80, T_out) fp32. */
@@ -100,9 +107,9 @@ int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, i
 int b200feat_whisper_logmel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                                  int32_t n_mels, int32_t padding, int32_t norm_mode, float* out_host,
                                  int32_t device);
-int b200feat_whisper_logmel_f16_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
-                                     int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host_f16,
-                                     int32_t device);
+int b200feat_whisper_logmel_ex_host(const void* wave_host, int32_t wave_dtype, const int64_t* lengths_host, int32_t B,
+                                    int64_t L, int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host,
+                                    int32_t out_dtype, int32_t device);
 int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                            float* out_host, int32_t device);
 int b200feat_kaldi_fbank_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,

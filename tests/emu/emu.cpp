@@ -22,11 +22,14 @@ static void run_whisper(const FeWhisper2Params& p) {
             if (fe_w2_interior(p, t)) {
                 for (int l = 0; l < C::NLT; ++l) {
                     FeW2Stage st;
-                    fe_w2_load_issue(p, t, l, st);
-                    fe_w2_load_store(sm.data(), l, st);
+                    if (p.in_s16) { fe_w2_load_issue<true>(p, t, l, st); fe_w2_load_store<true>(sm.data(), l, st); }
+                    else { fe_w2_load_issue<false>(p, t, l, st); fe_w2_load_store<false>(sm.data(), l, st); }
                 }
             } else {
-                for (int l = 0; l < C::NLT; ++l) fe_w2_load_edge(p, t, sm.data(), l);
+                for (int l = 0; l < C::NLT; ++l) {
+                    if (p.in_s16) fe_w2_load_edge<true>(p, t, sm.data(), l);
+                    else fe_w2_load_edge<false>(p, t, sm.data(), l);
+                }
             }
             for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_a(sm.data(), l, w);
             for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_b(sm.data(), l, w);
@@ -60,13 +63,14 @@ extern "C" void emu_f2h(const float* in, unsigned short* out, int64_t n) {
     for (int64_t i = 0; i < n; ++i) out[i] = fe_f2h_rn(in[i]);
 }
 
-static int emu_whisper_any(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+static int emu_whisper_any(const void* wave, bool in_s16, const int64_t* lengths, int B, int64_t L, int64_t stride,
                            int n_mels, int padding, int norm_mode, void* out, bool out16, int64_t T_out) {
     typedef FeW2Cfg C;
     std::vector<int> keys(B > 0 ? B : 1, FE_KEY_INIT);
     FeWhisper2Params p;
     memset(&p, 0, sizeof(p));
-    p.wave = wave; p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B; p.padding = padding;
+    p.wave = static_cast<const float*>(wave); p.in_s16 = in_s16 ? 1 : 0;
+    p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B; p.padding = padding;
     p.n_mels = n_mels; p.norm_mode = norm_mode; p.out = out; p.out_batch_stride = (int64_t)n_mels * T_out;
     p.T_out = T_out; p.units_per_clip = (int)((T_out + C::FT - 1) / C::FT); p.total_units = B * p.units_per_clip;
     p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
@@ -101,12 +105,17 @@ static int emu_whisper_any(const float* wave, const int64_t* lengths, int B, int
 
 extern "C" int emu_whisper(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
                            int n_mels, int padding, int norm_mode, float* out, int64_t T_out) {
-    return emu_whisper_any(wave, lengths, B, L, stride, n_mels, padding, norm_mode, out, false, T_out);
+    return emu_whisper_any(wave, false, lengths, B, L, stride, n_mels, padding, norm_mode, out, false, T_out);
 }
 
 extern "C" int emu_whisper_f16(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
                                int n_mels, int padding, int norm_mode, unsigned short* out, int64_t T_out) {
-    return emu_whisper_any(wave, lengths, B, L, stride, n_mels, padding, norm_mode, out, true, T_out);
+    return emu_whisper_any(wave, false, lengths, B, L, stride, n_mels, padding, norm_mode, out, true, T_out);
+}
+
+extern "C" int emu_whisper_s16(const short* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                               int n_mels, int padding, int norm_mode, float* out, int64_t T_out) {
+    return emu_whisper_any(wave, true, lengths, B, L, stride, n_mels, padding, norm_mode, out, false, T_out);
 }
 
 // ------------------------------------------------------------------------------------------ kaldi

@@ -125,6 +125,26 @@ def test_whisper_f16_output_is_the_rounded_f32_output(emu):
         assert np.array_equal(f16.view(np.uint16), torch.from_numpy(f32).to(torch.float16).numpy().view(np.uint16))
 
 
+def test_whisper_int16_pcm_input(emu):
+    """int16 PCM in (scaled by 1/32768 in the loader, interior and edge units) == the float32 path on pcm / 32768,
+    bit for bit, and within tolerance of the oracle on the same converted samples."""
+    gen = torch.Generator().manual_seed(13)
+    x = speech_like(gen, 2, 24000, 16000)
+    pcm = (x * 32767.0).round().clamp(-32768, 32767).to(torch.int16)
+    xf = pcm.to(torch.float32) / 32768.0
+    for kw in (dict(n_mels=80), dict(n_mels=128, padding=1600, lengths=[24000, 7001])):
+        n_mels, padding, lengths = kw.get("n_mels"), kw.get("padding", 0), kw.get("lengths")
+        B, L = pcm.shape
+        T = (L + padding) // 160
+        out = np.full((B, n_mels, T), 7.0, dtype=np.float32)
+        keep, lp = _lens(lengths)
+        a = np.ascontiguousarray(pcm.numpy())
+        assert emu.emu_whisper_s16(a.ctypes.data_as(vp), lp, B, L, L, n_mels, padding, 0, out.ctypes.data_as(vp), T) == 0
+        assert np.array_equal(out, emu_whisper(emu, xf.numpy(), n_mels, padding, 0, lengths))
+    ref = oracle.whisper_log_mel(xf, 80, dtype=torch.float64, norm="per_clip").numpy()
+    assert np.abs(emu_whisper(emu, xf.numpy(), 80) - ref).max() <= 1e-4
+
+
 @pytest.mark.parametrize("B,L", [(2, 16000), (1, 80000), (3, 999), (1, 400)])
 def test_kaldi(emu, B, L):
     x = (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(L))).clamp(-1, 1)

@@ -145,6 +145,30 @@ def test_whisper_f16_output_is_the_rounded_f32_output(fe):
         fe.whisper_log_mel_batch(sp.cuda(), out_dtype=torch.bfloat16)
 
 
+def test_whisper_int16_pcm_input(fe):
+    """wave_dtype B200FEAT_S16 (the load_audio cast folded into the loader): identical to
+    the float32 path fed pcm / 32768 -- device and host entry points, ragged, padded, unaligned rows, with float16 out."""
+    gen = torch.Generator().manual_seed(31)
+    x = speech_like(gen, 6, 40001, 16000)                              # odd L: rows of the int16 batch are 2-byte aligned only
+    pcm = (x * 32767.0).round().clamp(-32768, 32767).to(torch.int16)
+    xf = pcm.to(torch.float32) / 32768.0
+    lens = [40001, 40000, 12345, 801, 40001, 160]
+    for kw in (dict(n_mels=80), dict(n_mels=128, norm="per_call"), dict(n_mels=128, lengths=lens, padding=3200)):
+        ref = fe.whisper_log_mel_batch(xf.cuda(), **kw)
+        got = fe.whisper_log_mel_batch(pcm.cuda(), **kw)
+        assert got.dtype == torch.float32 and torch.equal(got, ref)
+        host = fe.whisper_log_mel_host(pcm.pin_memory(), **kw)
+        assert torch.equal(host, ref.cpu())
+        both = fe.whisper_log_mel_host(pcm, out_dtype=torch.float16, **kw)
+        assert _same_half_bits(both, ref.cpu())
+    o = oracle.whisper_log_mel(xf, 80, dtype=torch.float64, norm="per_clip")
+    assert (fe.whisper_log_mel_batch(pcm.cuda(), n_mels=80).cpu().double() - o).abs().max() <= TOL
+    with pytest.raises(TypeError):
+        fe.whisper_log_mel_batch(pcm.to(torch.int32).cuda())
+    with pytest.raises(TypeError):
+        fe.cosy_mel_batch(pcm.cuda())                                   # int16 is a Whisper-path feature only
+
+
 def test_whisper_f16_full_size(fe):
     """BASELINE config 2 shape with the half epilogue: equal to the rounded float32 result on all 393 M values."""
     g = torch.Generator(device="cuda").manual_seed(77)
