@@ -332,6 +332,23 @@ def run_ours(args, rank, world, local_rank):
                 "epilogue_ms_per_step": prof["epilogue_ms"] / args.steps,
                 "step_frac": (WL.B * WL.bytes_per_clip / (ms_step / 1.0 * 1e-3) / 1e9) / peak if world == 1 else None}
 
+    # ---- device-resident step with the narrow dtypes (int16 PCM in, float16 out), Whisper workloads only
+    narrow_dev_ms = None
+    if WL.featurizer == "whisper_log_mel":
+        nb = min(WL.B, 1024)
+        x16 = (x[:nb] * 32767.0).round_().to(torch.int16)
+        o16 = torch.empty((nb,) + tuple(WL.out_shape[1:]), dtype=torch.float16, device=dev)
+        for _ in range(3):
+            fe.whisper_log_mel_batch(x16, n_mels=WL.n_mels, norm="per_clip", out=o16)
+        e0.record()
+        for _ in range(args.steps):
+            fe.whisper_log_mel_batch(x16, n_mels=WL.n_mels, norm="per_clip", out=o16)
+        e1.record()
+        torch.cuda.synchronize()
+        narrow_dev_ms = e0.elapsed_time(e1) / args.steps
+        narrow_dev_clips = nb
+        del x16, o16
+
     # ---- end to end: pinned host in -> pinned host out through the host-buffer API
     # (one process per GPU: keep this rank's host buffers on the NUMA node next to its GPU)
     bound = None if os.environ.get("B200FEAT_NO_NUMA_BIND") else manifest.bind_host_to_gpu(local_rank)
@@ -381,7 +398,8 @@ def run_ours(args, rank, world, local_rank):
         n_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
         e2e["pcm16_in_f16_out"] = {"value": world * ne * WL.L / WL.sr / (n_ms * 1e-3), "unit": UNIT, "ms_per_step": n_ms,
                                    "h2d_bytes_per_step": ne * WL.L * 2, "d2h_bytes_per_step": ne * WL.out_per_clip * 2,
-                                   "api": "whisper_log_mel_host(int16 wave, out float16) -> b200feat_whisper_logmel_ex_host"}
+                                   "api": "whisper_log_mel_host(int16 wave, out float16) -> b200feat_whisper_logmel_ex_host",
+                                   "device_resident_ms_per_step": narrow_dev_ms, "device_resident_clips": narrow_dev_clips}
         del xs, oh16
 
     # ---- CPU baseline beside it (rank 0, N = 1 only)
