@@ -112,23 +112,21 @@ __global__ void __launch_bounds__(FeW2Cfg::NT, 1) fe_whisper2_kernel(const FeWhi
         int it = 0;
         FeW2Stage stage;
         FeW2Unit t = fe_w2_unit(p, blockIdx.x);
-        bool live = t.t0 < t.T, fast = live && fe_w2_interior(p, t);
-        if (fast) fe_w2_load_issue<IN16>(p, t, ltid, stage);
+        int mode = fe_w2_load_mode<IN16>(p, t);
+        fe_w2_load_ahead<IN16>(p, t, ltid, mode, stage);
         for (int u = blockIdx.x; u < p.total_units; u += gridDim.x, par ^= 1, ++it) {
             FE_TR(it, 0);
             if (u != (int)blockIdx.x) fe_bar_sync(FE_BAR_W_FREE, C::NT);
             FE_TR(it, 1);
-            if (fast) fe_w2_load_store<IN16>(sm, ltid, stage);
-            else if (live) fe_w2_load_edge<IN16>(p, t, sm, ltid);
+            fe_w2_load_finish<IN16>(p, t, sm, ltid, mode, stage);
             if (ltid == 0) { misc[4 + 4 * par] = t.b; misc[5 + 4 * par] = t.t0; misc[6 + 4 * par] = t.T; }
             FE_TR(it, 2);
             fe_bar_arrive(FE_BAR_W_FULL, C::NT);
             const int un = u + (int)gridDim.x;
             if (un < p.total_units) {   // next unit: loads go in flight now, stores wait for W_FREE
                 t = fe_w2_unit(p, un);
-                live = t.t0 < t.T;
-                fast = live && fe_w2_interior(p, t);
-                if (fast) fe_w2_load_issue<IN16>(p, t, ltid, stage);
+                mode = fe_w2_load_mode<IN16>(p, t);
+                fe_w2_load_ahead<IN16>(p, t, ltid, mode, stage);
             }
             FE_TR(it, 3);
         }

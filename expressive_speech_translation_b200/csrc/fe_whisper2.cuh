@@ -134,7 +134,11 @@ FE_HD FE_INLINE int fe_float_bits_as_int(float f) {
 #endif
 }
 // int16 PCM -> float exactly as whisper.audio.load_audio does it: astype(float32) / 32768.0 (a power of two: exact)
-FE_HD FE_INLINE float fe_pcm16_to_float(int v) { return (float)v * (1.0f / 32768.0f); }
+// Without I2F (quarter-rate conversion pipe, on the loader's critical path: measured +16 % kernel time): the bits
+// 0x4B400000 + v are the float 1.5 * 2^23 + v, and one FMA maps that to v / 32768 exactly (12582912 / 32768 = 384).
+FE_HD FE_INLINE float fe_pcm16_to_float(int v) {
+    return fmaf(fe_int_bits_as_float(0x4B400000 + v), 1.0f / 32768.0f, -384.0f);
+}
 
 // int16 input (IN16, a template argument of the kernel so that the float32 kernel carries none of this code): the
 // staged registers carry the raw sample as integer bits, the conversion happens at the store
@@ -253,6 +257,51 @@ FE_HD FE_INLINE void fe_w2_load_edge_s16_t(const short* __restrict__ x, I g0, I 
     }
 }
 
+// Edge units, register-staged like interior ones: every (reflected, bounds-checked) load of the unit goes in flight
+// before the loader waits for W; fe_w2_load_store then writes them.  (The cp.async form below starts its copies only
+// once W is free: 1.51 -> 1.47 ms for 1024 x 30 s, two edge units per 47-unit clip.)  32-bit index arithmetic: the
+// caller checks that the clip is shorter than 2^30 samples (longer clips take fe_w2_load_edge).
+FE_HD FE_INLINE bool fe_w2_edge_fits_int(const FeW2Unit& t) {
+    return t.lp < ((int64_t)1 << 30) && (int64_t)t.t0 * FeW2Cfg::HOP < ((int64_t)1 << 30);
+}
+template <bool IN16>
+FE_HD FE_INLINE void fe_w2_load_issue_edge(const FeWhisper2Params& p, const FeW2Unit& t, int ltid, FeW2Stage& r) {
+    typedef FeW2Cfg C;
+    const short* __restrict__ xs = reinterpret_cast<const short*>(p.wave) + (int64_t)t.b * p.wave_stride;
+    const float* __restrict__ xf = p.wave + (int64_t)t.b * p.wave_stride;
+    const int g0 = t.t0 * C::HOP - C::PADL + ltid, len = (int)t.len, lp = (int)t.lp;
+#pragma unroll
+    for (int j = 0; j < FeW2Stage::U; ++j) {
+        if (j + 1 < FeW2Stage::U || ltid + j * C::NLT < C::RT) {
+            const int ga = fe_w2_reflect<int>(g0 + j * C::NLT, lp), gb = fe_w2_reflect<int>(g0 + j * C::NLT + C::SEG, lp);
+            if (IN16) {
+                r.a[j] = fe_int_bits_as_float(ga < len ? (int)xs[ga] : 0);
+                r.b[j] = fe_int_bits_as_float(gb < len ? (int)xs[gb] : 0);
+            } else {
+                r.a[j] = ga < len ? xf[ga] : 0.0f;
+                r.b[j] = gb < len ? xf[gb] : 0.0f;
+            }
+        }
+    }
+}
+
+// how the loader fills W for a unit: 0 nothing (no live frame), 1 interior + register-staged, 2 edge + register-staged,
+// 3 edge of a clip of 2^30 samples or more, element-wise after W is free
+template <bool IN16>
+FE_HD FE_INLINE int fe_w2_load_mode(const FeWhisper2Params& p, const FeW2Unit& t) {
+    if (!(t.t0 < t.T)) return 0;
+    if (fe_w2_interior(p, t)) return 1;
+    return fe_w2_edge_fits_int(t) ? 2 : 3;
+}
+template <bool IN16>
+FE_HD FE_INLINE void fe_w2_load_ahead(const FeWhisper2Params& p, const FeW2Unit& t, int ltid, int mode, FeW2Stage& r) {
+    if (mode == 1) fe_w2_load_issue<IN16>(p, t, ltid, r);
+    else if (mode == 2) fe_w2_load_issue_edge<IN16>(p, t, ltid, r);
+}
+template <bool IN16>
+FE_HD FE_INLINE void fe_w2_load_finish(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid, int mode,
+                                       const FeW2Stage& r);
+
 template <bool IN16 = false>
 FE_HD FE_INLINE void fe_w2_load_edge(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid) {
     typedef FeW2Cfg C;
@@ -270,6 +319,13 @@ FE_HD FE_INLINE void fe_w2_load_edge(const FeWhisper2Params& p, const FeW2Unit& 
         fe_w2_load_edge_t<int>(x, (int)g0, (int)t.len, (int)t.lp, sm, ltid);
     else
         fe_w2_load_edge_t<int64_t>(x, g0, t.len, t.lp, sm, ltid);
+}
+
+template <bool IN16>
+FE_HD FE_INLINE void fe_w2_load_finish(const FeWhisper2Params& p, const FeW2Unit& t, float* sm, int ltid, int mode,
+                                       const FeW2Stage& r) {
+    if (mode == 1 || mode == 2) fe_w2_load_store<IN16>(sm, ltid, r);
+    else if (mode == 3) fe_w2_load_edge<IN16>(p, t, sm, ltid);
 }
 
 // copies the constant tables into shared memory; every thread of the CTA calls it, a barrier must follow

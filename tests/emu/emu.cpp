@@ -19,16 +19,16 @@ static void run_whisper(const FeWhisper2Params& p) {
         const FeW2Unit t = fe_w2_unit(p, u);
         float mn = 3.0e38f, mx = -3.0e38f;
         if (t.t0 < t.T) {
-            if (fe_w2_interior(p, t)) {
-                for (int l = 0; l < C::NLT; ++l) {
-                    FeW2Stage st;
-                    if (p.in_s16) { fe_w2_load_issue<true>(p, t, l, st); fe_w2_load_store<true>(sm.data(), l, st); }
-                    else { fe_w2_load_issue<false>(p, t, l, st); fe_w2_load_store<false>(sm.data(), l, st); }
-                }
-            } else {
-                for (int l = 0; l < C::NLT; ++l) {
-                    if (p.in_s16) fe_w2_load_edge<true>(p, t, sm.data(), l);
-                    else fe_w2_load_edge<false>(p, t, sm.data(), l);
+            for (int l = 0; l < C::NLT; ++l) {   // the loader's three paths, as the kernel picks them
+                FeW2Stage st;
+                if (p.in_s16) {
+                    const int mode = fe_w2_load_mode<true>(p, t);
+                    fe_w2_load_ahead<true>(p, t, l, mode, st);
+                    fe_w2_load_finish<true>(p, t, sm.data(), l, mode, st);
+                } else {
+                    const int mode = fe_w2_load_mode<false>(p, t);
+                    fe_w2_load_ahead<false>(p, t, l, mode, st);
+                    fe_w2_load_finish<false>(p, t, sm.data(), l, mode, st);
                 }
             }
             for (int w = 0; w < C::NCW; ++w) for (int l = 0; l < 32; ++l) fe_w2_phase_a(sm.data(), l, w);
