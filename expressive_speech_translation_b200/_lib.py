@@ -30,6 +30,9 @@ SYMBOLS = {
     "b200feat_cosy_mel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                      _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64,
                                      _c.c_void_p]),
+    "b200feat_cosy_mel_frames": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
+                                            _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64,
+                                            _c.c_void_p]),
     "b200feat_kaldi_fbank": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                         _c.c_int32, _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p,
                                         _c.c_int64, _c.c_void_p]),

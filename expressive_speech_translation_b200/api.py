@@ -158,24 +158,26 @@ def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_cl
     return out
 
 
-def cosy_mel_batch(wave, lengths=None, out=None):
-    """(B, L) 24 kHz batch on a CUDA device -> (B, 80, T) ln-mel (n_fft 1920, hop 480)."""
+def cosy_mel_batch(wave, lengths=None, out=None, frame_major=False):
+    """(B, L) 24 kHz batch on a CUDA device -> (B, 80, T) ln-mel (n_fft 1920, hop 480); frame_major=True writes
+    (B, T, 80), the layout the CosyVoice frontend's `_extract_speech_feat` produces with `.transpose(0, 1)`."""
     wave = _as_float_tensor(wave, "y")
     device = _cuda_device(wave.device if wave.is_cuda else None)
     w, stride = _prep_wave(wave, device)
     B, L = w.shape
     T = num_frames("cosy", L)
+    shape = (B, T, 80) if frame_major else (B, 80, T)
     if out is None:
-        out = torch.empty((B, 80, T), dtype=torch.float32, device=device)
-    elif out.shape != (B, 80, T) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
-        raise ValueError("out must be a contiguous float32 (B, 80, T) tensor on the wave's device")
+        out = torch.empty(shape, dtype=torch.float32, device=device)
+    elif out.shape != shape or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError(f"out must be a contiguous float32 {shape} tensor on the wave's device")
     if B == 0 or T == 0:
         return out
     ln = _lengths_dev(lengths, B, device)
     ws, nws = _workspace(KIND_COSY, B, L, device)
     with torch.cuda.device(device):
-        rc = lib.b200feat_cosy_mel(_ptr(w), _ptr(ln), B, L, stride, _ptr(out), 80 * T, T, _ptr(ws), nws,
-                                   _stream(device))
+        fn = lib.b200feat_cosy_mel_frames if frame_major else lib.b200feat_cosy_mel
+        rc = fn(_ptr(w), _ptr(ln), B, L, stride, _ptr(out), 80 * T, T, _ptr(ws), nws, _stream(device))
     check(rc, "b200feat_cosy_mel")
     return out
 

@@ -652,9 +652,9 @@ int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64
 }
 
 // ------------------------------------------------------------------------------------------ CosyVoice
-int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
-                      int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
-                      void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+static int cosy_mel_impl(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                         int64_t wave_stride, float* out, bool frame_major, int64_t out_batch_stride, int64_t T_out,
+                         void* workspace, int64_t workspace_bytes, void* cuda_stream) {
     (void)workspace; (void)workspace_bytes;
     if (int rc = common_checks("cosy_mel", wave, out, B, L, wave_stride)) return rc;
     const int64_t T_full = b200feat_num_frames(B200FEAT_KIND_COSY, L, 0);
@@ -668,7 +668,7 @@ int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int6
     FeCosyParams p;
     memset(&p, 0, sizeof(p));
     p.wave = wave; p.lengths = lengths; p.wave_stride = wave_stride; p.L = L; p.B = B;
-    p.out = out; p.out_batch_stride = out_batch_stride; p.T_out = T_out;
+    p.out = out; p.out_batch_stride = out_batch_stride; p.T_out = T_out; p.frame_major = frame_major ? 1 : 0;
     const int64_t tiles = (T_out + FeCCfg::FT - 1) / FeCCfg::FT;
     p.tiles_per_clip = (int32_t)tiles;
     p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
@@ -683,6 +683,18 @@ int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int6
     }
     FE_CUDA(cudaGetLastError());
     return 0;
+}
+
+int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                      int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
+                      void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    return cosy_mel_impl(wave, lengths, B, L, wave_stride, out, false, out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
+}
+
+int b200feat_cosy_mel_frames(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                             int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
+                             void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    return cosy_mel_impl(wave, lengths, B, L, wave_stride, out, true, out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
 }
 
 // ------------------------------------------------------------------------------------------ kaldi

@@ -160,9 +160,10 @@ struct FeCosyParams {
     int64_t wave_stride;
     int64_t L;
     int32_t B;
-    float* out;                // (B, 80, T_out)
+    float* out;                // (B, 80, T_out), or (B, T_out, 80) when frame_major
     int64_t out_batch_stride;
     int64_t T_out;
+    int32_t frame_major;       // 1: the CosyVoice frontend's layout (speech_feat.transpose(0, 1)): frames outermost
     int32_t tiles_per_clip;    // ceil(T_out / 16)
     int32_t vec_ok;
     int32_t clip0, nclips;     // clips [clip0, clip0 + nclips) are processed by this launch

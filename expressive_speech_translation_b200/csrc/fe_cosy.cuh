@@ -180,8 +180,10 @@ FE_HD FE_INLINE void fe_c_phase_mel(const FeCosyParams& p, float* sm, int tid, i
     const FeCTile t = fe_c_tile(p, cta);
     const int frame = t.t0 + lane;
     const bool live = frame < t.T;
-    float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + frame;
-    const int64_t rs = p.T_out;
+    // mel-major: out[b][m][frame]; frame-major: out[b][frame][m] (16 frames x 320 B apart per store -- the output is
+    // 14 % of this kernel's bytes and the kernel is nowhere near HBM-bound)
+    float* __restrict__ o = p.out + (int64_t)t.b * p.out_batch_stride + (p.frame_major ? (int64_t)frame * C::NMEL : (int64_t)frame);
+    const int64_t rs = p.frame_major ? 1 : p.T_out;
     auto emit = [&](int m, float v) {
         const float lg = FE_LOG2(fmaxf(v, 1e-5f)) * 0.69314718055994531f;  // ln
         if (frame < p.T_out) o[(int64_t)m * rs] = live ? lg : 0.0f;  // ragged batches: zeros past T_b

@@ -93,6 +93,14 @@ int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int6
                       int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
                       void* workspace, int64_t workspace_bytes, void* cuda_stream);
 
+/* The same mel written frame-major, out: (B, T_out, 80): the layout the CosyVoice frontend builds with
+ * `feat_extractor(speech).squeeze(0).transpose(0, 1)` before it hands the prompt features to the flow model (UPSTREAM
+ * cosyvoice/cli/frontend.py `_extract_speech_feat`, reached from /root/reference/Docker/cosyvoice_api.py:128;
+ * SURVEY.md section 8(f) item 2).  Rows past a ragged clip's own frame count are zero. */
+int b200feat_cosy_mel_frames(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                             int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
+                             void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
 /* kaldi fbank (80 bins, 25 ms / 10 ms, povey, dither 0, snip_edges), optional per-clip mean
  * subtraction over frames.  out: (B, T_out, 80) fp32 frame-major. */
 int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, int64_t L,

@@ -169,6 +169,18 @@ def test_whisper_int16_pcm_input(fe):
         fe.cosy_mel_batch(pcm.cuda())                                   # int16 is a Whisper-path feature only
 
 
+def test_cosy_frame_major_layout(fe):
+    """b200feat_cosy_mel_frames == the mel-major result transposed (what frontend._extract_speech_feat builds), ragged too."""
+    x = speech_like(torch.Generator().manual_seed(41), 4, 36000, 24000)
+    lens = [36000, 24001, 2000, 36000]
+    for kw in (dict(), dict(lengths=lens)):
+        a = fe.cosy_mel_batch(x.cuda(), **kw)
+        b = fe.cosy_mel_batch(x.cuda(), frame_major=True, **kw)
+        assert b.shape == (4, a.shape[2], 80) and torch.equal(b, a.transpose(1, 2).contiguous())
+    out = torch.full((4, 75, 80), 7.0, device="cuda")
+    assert fe.cosy_mel_batch(x.cuda(), out=out, frame_major=True) is out and not (out == 7.0).any()
+
+
 def test_whisper_f16_full_size(fe):
     """BASELINE config 2 shape with the half epilogue: equal to the rounded float32 result on all 393 M values."""
     g = torch.Generator(device="cuda").manual_seed(77)
