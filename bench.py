@@ -61,8 +61,8 @@ class Workload:
             self.B, self.L, self.sr, self.n_mels = 1024, 480000, 16000, 128
             self.T = self.L // 160
             self.out_shape = (self.B, self.n_mels, self.T)
-            self.kernel = "fe_whisper2_kernel<128>"
-            self.cpu_clips = 64
+            self.kernel = "fe_whisper2_kernel<128, 0, 0>"
+            self.cpu_clips = 256
             self.desc = "BASELINE configs[1]: Whisper large-v3 128-bin log-mel, 1024 x 30 s @ 16 kHz per GPU"
             self.featurizer = "whisper_log_mel"
             self.traffic_key = "fe_whisper2_kernel_128_dram_bytes_per_1024_clips"
@@ -95,7 +95,7 @@ class Workload:
             self.B, self.L, self.sr, self.n_mels = hi - lo, 960000, 16000, 80
             self.T = self.L // 160
             self.out_shape = (self.B, self.n_mels, self.T)
-            self.kernel = "fe_whisper2_kernel<80>"
+            self.kernel = "fe_whisper2_kernel<80, 0, 0>"
             self.cpu_clips = 32
             self.desc = ("BASELINE configs[4]: Batch-Processing manifest sweep, 10 000 x 60 s @ 16 kHz, Whisper 80-bin log-mel, "
                          "contiguous clip shards per GPU, sub-batches of 512 clips")
