@@ -24,5 +24,6 @@ from .api import (  # noqa: F401
     install,
     uninstall,
 )
+from .hf import WhisperFeatureExtractor  # noqa: F401
 
 __version__ = "0.1.0"

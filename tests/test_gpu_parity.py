@@ -181,6 +181,38 @@ def test_cosy_frame_major_layout(fe):
     assert fe.cosy_mel_batch(x.cuda(), out=out, frame_major=True) is out and not (out == 7.0).any()
 
 
+def test_hf_whisper_feature_extractor_mirror(fe, tmp_path):
+    """fe.WhisperFeatureExtractor against the installed transformers class on the same clips: the MuseTalk call
+    (`feature_extractor(segment, return_tensors="pt", sampling_rate=16000).input_features`), batches of ragged clips,
+    128 bins, attention mask, a custom max_length, from_pretrained of a local preprocessor_config.json."""
+    transformers = pytest.importorskip("transformers")
+    gen = torch.Generator().manual_seed(51)
+    clips = [speech_like(gen, 1, n, 16000)[0].numpy() for n in (480000, 123457, 16000)]
+    long_clip = speech_like(gen, 1, 500000, 16000)[0].numpy()           # longer than 30 s: truncated
+    for nm in (80, 128):
+        ref_fx = transformers.WhisperFeatureExtractor(feature_size=nm)
+        fx = fe.WhisperFeatureExtractor(feature_size=nm)
+        ref = ref_fx(clips[1], return_tensors="pt", sampling_rate=16000).input_features
+        got = fx(clips[1], return_tensors="pt", sampling_rate=16000).input_features
+        assert got.shape == ref.shape == (1, nm, 3000) and got.dtype == torch.float32
+        assert (got - ref).abs().max() <= TOL
+        ref = ref_fx(clips + [long_clip], return_tensors="pt", sampling_rate=16000, return_attention_mask=True)
+        got = fx(clips + [long_clip], return_tensors="pt", sampling_rate=16000, return_attention_mask=True)
+        assert (got["input_features"] - ref["input_features"]).abs().max() <= TOL
+        assert torch.equal(got["attention_mask"].long(), ref["attention_mask"].long())
+    ref = ref_fx(clips[2], return_tensors="np", sampling_rate=16000, max_length=32000).input_features
+    got = fx(clips[2], return_tensors="np", sampling_rate=16000, max_length=32000).input_features
+    assert isinstance(got, np.ndarray) and got.shape == ref.shape == (1, 128, 200) and np.abs(got - ref).max() <= TOL
+    with pytest.raises(ValueError):
+        fx(clips[0], sampling_rate=44100)
+    with pytest.raises(NotImplementedError):
+        fx(clips[0], sampling_rate=16000, do_normalize=True)
+    (tmp_path / "preprocessor_config.json").write_text('{"feature_size": 80, "chunk_length": 30, "n_fft": 400, "hop_length": 160, '
+                                                       '"sampling_rate": 16000, "padding_value": 0.0, "feature_extractor_type": "WhisperFeatureExtractor"}')
+    fx2 = fe.WhisperFeatureExtractor.from_pretrained(str(tmp_path))
+    assert fx2.feature_size == 80 and fx2.n_samples == 480000 and fx2.nb_max_frames == 3000
+
+
 def test_whisper_f16_full_size(fe):
     """BASELINE config 2 shape with the half epilogue: equal to the rounded float32 result on all 393 M values."""
     g = torch.Generator(device="cuda").manual_seed(77)
