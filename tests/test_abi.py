@@ -112,3 +112,32 @@ def test_python_rejects_unsupported_configs_loudly():
     if not torch.cuda.is_available():
         with pytest.raises(RuntimeError, match="no CPU path"):
             m.log_mel_spectrogram(torch.zeros(16000))
+
+
+def test_hf_feature_extractor_mirror_argument_handling(tmp_path):
+    """the transformers.WhisperFeatureExtractor mirror: constructor / from_pretrained / the errors raised before any
+    device work (the numerics are a -m gpu test against the installed transformers class)."""
+    import numpy as np
+    import torch
+    import expressive_speech_translation_b200 as m
+    fx = m.WhisperFeatureExtractor()
+    assert (fx.feature_size, fx.sampling_rate, fx.hop_length, fx.n_fft, fx.n_samples, fx.nb_max_frames) == (80, 16000, 160, 400, 480000, 3000)
+    x = np.zeros(16000, dtype=np.float32)
+    with pytest.raises(ValueError, match="sampling rate of 16000"):
+        fx(x, sampling_rate=44100)
+    for kw in (dict(do_normalize=True), dict(pad_to_multiple_of=8), dict(padding="do_not_pad"), dict(return_tensors="tf")):
+        with pytest.raises(NotImplementedError):
+            fx(x, sampling_rate=16000, **kw)
+    with pytest.raises(ValueError, match="mono-channel"):
+        fx(np.zeros((2, 2, 100), dtype=np.float32), sampling_rate=16000)
+    with pytest.raises(NotImplementedError):
+        m.WhisperFeatureExtractor(feature_size=64)
+    with pytest.raises(NotImplementedError):
+        m.WhisperFeatureExtractor(sampling_rate=22050)
+    (tmp_path / "preprocessor_config.json").write_text('{"feature_size": 128, "chunk_length": 30, "hop_length": 160, "n_fft": 400, '
+                                                       '"sampling_rate": 16000, "processor_class": "WhisperProcessor"}')
+    fx = m.WhisperFeatureExtractor.from_pretrained(str(tmp_path))
+    assert fx.feature_size == 128
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CPU path"):
+            fx(x, sampling_rate=16000)
