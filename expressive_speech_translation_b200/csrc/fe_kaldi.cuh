@@ -117,7 +117,9 @@ FE_HD FE_INLINE void fe_k_phase_sum(const FeKaldiParams&, float* sm, int tid, in
 }
 
 // ---------------------------------------------------------------- phase A
-template <bool N2_IS_ZERO>
+// One instantiation for every n2 (this codelet is a seventh of the kernel's code, and the kernel is fetch-bound):
+// n2 == 0 differs only in where the sample before 16*n1 sits -- one pad slot lower when n1 is a multiple of 10,
+// and x[-1] := x[0] for the very first sample.
 FE_HD FE_INLINE void fe_k_stage_a(float* sm, int lane, int n2) {
     typedef FeKCfg C;
     float mu = 0.0f;
@@ -125,15 +127,17 @@ FE_HD FE_INLINE void fe_k_stage_a(float* sm, int lane, int n2) {
     for (int w = 0; w < C::NW; ++w) mu += sm[C::OFF_PART + w * C::FT + lane];
     mu *= (1.0f / C::WIN);
     const float* __restrict__ s = sm + (C::HOP + 1) * lane + n2;
+    const int z = n2 == 0 ? 1 : 0;
     float x[C::NZ1];
 #pragma unroll
     for (int n1 = 0; n1 < C::NZ1; ++n1) {
         // sample n = 16*n1 + n2; (16*n1 + n2) / 160 == n1 / 10 for every n2 < 16
         const float cur = s[C::R2 * n1 + n1 / (C::HOP / C::R2)];
         float prev;
-        if (N2_IS_ZERO) {
-            // n - 1 = 16*n1 - 1 sits in the previous 160-block when n1 % 10 == 0; n = 0 replicates x[0]
-            prev = (n1 == 0) ? cur : s[C::R2 * n1 - 1 + (n1 - 1) / (C::HOP / C::R2)];
+        if (n1 == 0) {
+            prev = s[z - 1];                             // n = 0 replicates x[0] (n2 == 0 reads s[0] again)
+        } else if (n1 % (C::HOP / C::R2) == 0) {
+            prev = s[C::R2 * n1 + n1 / (C::HOP / C::R2) - 1 - z];   // 16*n1 - 1 sits in the previous 160-block
         } else {
             prev = s[C::R2 * n1 + n1 / (C::HOP / C::R2) - 1];
         }
@@ -156,10 +160,8 @@ FE_HD FE_INLINE void fe_k_stage_a(float* sm, int lane, int n2) {
 FE_HD FE_INLINE void fe_k_phase_a(const FeKaldiParams&, float* sm, int tid, int) {
     typedef FeKCfg C;
     const int lane = tid & 31, warp = tid >> 5;
-    for (int n2 = warp; n2 < C::R2; n2 += C::NW) {
-        if (n2 == 0) fe_k_stage_a<true>(sm, lane, 0);
-        else fe_k_stage_a<false>(sm, lane, n2);
-    }
+#pragma unroll 1
+    for (int n2 = warp; n2 < C::R2; n2 += C::NW) fe_k_stage_a(sm, lane, n2);
 }
 
 // ---------------------------------------------------------------- phase B
@@ -211,6 +213,7 @@ FE_HD FE_INLINE void fe_k_stage_b_light(float* sm, int lane) {
 FE_HD FE_INLINE void fe_k_phase_b(const FeKaldiParams&, float* sm, int tid, int) {
     typedef FeKCfg C;
     const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll 1
     for (int j = warp; j < C::R1 / 2; j += C::NW) {
         if (j == 0) fe_k_stage_b_light(sm, lane);
         else fe_k_stage_b_heavy(sm, lane, j);
