@@ -17,6 +17,10 @@ from .api import (  # noqa: F401
     whisper_log_mel_host,
     cosy_mel_host,
     kaldi_fbank_host,
+    condition_pcm,
+    resample,
+    resample_out_len,
+    Resample,
     num_frames,
     launch_count,
     profile_begin,

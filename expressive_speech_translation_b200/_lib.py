@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libb200feat.so")
 KIND_WHISPER, KIND_COSY, KIND_KALDI = 0, 1, 2
 NORM_PER_CLIP, NORM_PER_CALL = 0, 1
 DT_F32, DT_F16, DT_S16 = 0, 1, 2
+RESAMPLE_HANN, RESAMPLE_KAISER = 0, 1
 
 # every symbol include/b200feat.h declares: (restype, argtypes)
 _c = ctypes
@@ -45,6 +46,10 @@ SYMBOLS = {
                                           _c.c_int32]),
     "b200feat_kaldi_fbank_host": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int32,
                                              _c.c_void_p, _c.c_int32]),
+    "b200feat_resample_out_len": (_c.c_int64, [_c.c_int64, _c.c_int32, _c.c_int32]),
+    "b200feat_resample": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_void_p, _c.c_int32,
+                                     _c.c_int64, _c.c_int64, _c.c_int32, _c.c_int32, _c.c_int32, _c.c_double,
+                                     _c.c_int32, _c.c_double, _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p]),
     "b200feat_release": (None, []),
     "b200feat_launch_count": (_c.c_int64, []),
     "b200feat_profile_begin": (_c.c_int, []),

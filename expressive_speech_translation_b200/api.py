@@ -382,6 +382,101 @@ def fbank(waveform, blackman_coeff: float = 0.42, channel: int = -1, dither: flo
     return kaldi_fbank_host(x, subtract_mean=subtract_mean, pin_output=False)[0]
 
 
+# ----------------------------------------------------------------------------------------- waveform conditioning
+_RS_METHODS = {"sinc_interp_hann": _lib.RESAMPLE_HANN, "sinc_interpolation": _lib.RESAMPLE_HANN,
+               "sinc_interp_kaiser": _lib.RESAMPLE_KAISER, "kaiser_window": _lib.RESAMPLE_KAISER}
+
+
+def resample_out_len(n_frames, orig_freq, new_freq):
+    """ceil(new * n / orig) with the ratio reduced by its gcd (torchaudio's target_length)."""
+    return int(lib.b200feat_resample_out_len(int(n_frames), int(orig_freq), int(new_freq)))
+
+
+def condition_pcm(pcm, orig_freq, new_freq, lengths=None, mix=None, lowpass_filter_width=6, rolloff=0.99,
+                  resampling_method="sinc_interp_hann", beta=None, out=None):
+    """Interleaved PCM -> mono -> resampled float32 waveform batch in ONE kernel (b200feat_resample), the row in
+    front of the featurizers: `pcm` is (B, L) mono or (B, L, C) with C in {1, 2}, int16 (scaled by 1/32768 like
+    whisper.audio.load_audio) or float32, on a CUDA device (a host tensor is copied over).  `mix` = per-channel
+    weights (None: mean of the channels, audio_processor.py:314; (0.65, 0.35) is its mid + 0.3 * side branch, :316-318).
+    Filter arguments are torchaudio.functional.resample's.  Returns (B, ceil(new * L / orig)) float32; with
+    `lengths` (input frames per clip) every row is zero past its own ceil(new * len / orig).  Async on the current stream."""
+    if isinstance(pcm, np.ndarray):
+        pcm = torch.from_numpy(pcm)
+    if not torch.is_tensor(pcm):
+        raise TypeError(f"pcm must be a torch.Tensor or numpy.ndarray, got {type(pcm).__name__}")
+    if pcm.dtype != torch.int16:
+        if not pcm.is_floating_point():
+            raise TypeError(f"Expected floating point type for waveform tensor, but received {pcm.dtype}.")
+        pcm = pcm if pcm.dtype == torch.float32 else pcm.to(torch.float32)
+    if not (int(orig_freq) == orig_freq and int(new_freq) == new_freq):
+        raise Exception("Frequencies must be of integer type to ensure quality resampling computation.")
+    if orig_freq <= 0.0 or new_freq <= 0.0:
+        raise ValueError("Original frequency and desired frequecy should be positive")
+    if resampling_method not in _RS_METHODS:
+        raise ValueError("Invalid resampling method: {}".format(resampling_method))
+    if lowpass_filter_width <= 0:
+        raise ValueError("Low pass filter width should be positive.")
+    if pcm.dim() == 2:
+        pcm = pcm.unsqueeze(-1)
+    if pcm.dim() != 3 or pcm.shape[2] not in (1, 2):
+        raise ValueError(f"expected (B, L) or (B, L, C) PCM with C in (1, 2), got shape {tuple(pcm.shape)}")
+    device = _cuda_device(pcm.device if pcm.is_cuda else None)
+    x = pcm.to(device).contiguous()
+    B, L, C = x.shape
+    L_out = resample_out_len(L, orig_freq, new_freq)
+    if out is None:
+        out = torch.empty((B, L_out), dtype=torch.float32, device=device)
+    elif out.shape != (B, L_out) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError(f"out must be a contiguous float32 ({B}, {L_out}) tensor on {device}")
+    mix_arr = None
+    if mix is not None:
+        if len(mix) != C:
+            raise ValueError(f"mix has {len(mix)} weights for {C} channel(s)")
+        mix_arr = (ctypes.c_float * C)(*[float(v) for v in mix])
+    ld = _lengths_dev(lengths, B, device)
+    with torch.cuda.device(device):
+        check(lib.b200feat_resample(_ptr(x), _DTYPES[x.dtype], C, mix_arr, _ptr(ld), B, L, L * C,
+                                    int(orig_freq), int(new_freq), int(lowpass_filter_width), float(rolloff),
+                                    _RS_METHODS[resampling_method], 14.769656459379492 if beta is None else float(beta),
+                                    _ptr(out), L_out, L_out, _stream(device)), "b200feat_resample")
+    return out
+
+
+def resample(waveform, orig_freq: int, new_freq: int, lowpass_filter_width: int = 6, rolloff: float = 0.99,
+             resampling_method: str = "sinc_interp_hann", beta=None):
+    """torchaudio.functional.resample (functional.py:1435): `(..., time)` -> `(..., ceil(new * time / orig))`, same
+    arguments, defaults and errors; returns the input itself when the rates are equal.  The result lives on the
+    input's device (a CPU tensor makes the round trip to the current CUDA device: there is no CPU path)."""
+    if orig_freq <= 0.0 or new_freq <= 0.0:
+        raise ValueError("Original frequency and desired frequecy should be positive")
+    if orig_freq == new_freq:
+        return waveform
+    if not torch.is_tensor(waveform):
+        raise TypeError(f"waveform must be a torch.Tensor, got {type(waveform).__name__}")
+    if not waveform.is_floating_point():
+        raise TypeError(f"Expected floating point type for waveform tensor, but received {waveform.dtype}.")
+    shape = waveform.shape
+    y = condition_pcm(waveform.reshape(-1, shape[-1]), orig_freq, new_freq, None, None, lowpass_filter_width, rolloff,
+                      resampling_method, beta)
+    return y.reshape(shape[:-1] + y.shape[-1:]).to(device=waveform.device, dtype=waveform.dtype)
+
+
+class Resample:
+    """torchaudio.transforms.Resample as /root/reference/Backend/services/audio_processor.py:296-303 builds it
+    (orig_freq, new_freq, resampling_method, lowpass_filter_width, rolloff, beta); calling it resamples `(..., time)`."""
+
+    def __init__(self, orig_freq: int = 16000, new_freq: int = 16000, resampling_method: str = "sinc_interp_hann",
+                 lowpass_filter_width: int = 6, rolloff: float = 0.99, beta=None, *, dtype=None):
+        self.orig_freq, self.new_freq, self.resampling_method = orig_freq, new_freq, resampling_method
+        self.lowpass_filter_width, self.rolloff, self.beta = lowpass_filter_width, rolloff, beta
+
+    def __call__(self, waveform):
+        return resample(waveform, self.orig_freq, self.new_freq, self.lowpass_filter_width, self.rolloff,
+                        self.resampling_method, self.beta)
+
+    forward = __call__
+
+
 # ----------------------------------------------------------------------------------------- install / uninstall
 _PATCHED = []
 
@@ -394,7 +489,9 @@ def install(verbose=False):
                ("whisper.transcribe", "log_mel_spectrogram", log_mel_spectrogram),
                ("whisper", "log_mel_spectrogram", log_mel_spectrogram),
                ("matcha.utils.audio", "mel_spectrogram", mel_spectrogram),
-               ("torchaudio.compliance.kaldi", "fbank", fbank)]
+               ("torchaudio.compliance.kaldi", "fbank", fbank),
+               ("torchaudio.functional", "resample", resample),
+               ("torchaudio.transforms", "Resample", Resample)]
     done = []
     for mod_name, attr, fn in targets:
         try:

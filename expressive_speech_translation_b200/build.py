@@ -14,6 +14,8 @@ DEPS = [
     os.path.join(HERE, "csrc", "fe_whisper2.cuh"),
     os.path.join(HERE, "csrc", "fe_kaldi.cuh"),
     os.path.join(HERE, "csrc", "fe_cosy.cuh"),
+    os.path.join(HERE, "csrc", "fe_resample.cuh"),
+    os.path.join(HERE, "csrc", "fe_resample_plan.h"),
     os.path.join(HERE, "csrc", "generated", "fe_codelets.h"),
     os.path.join(HERE, "csrc", "generated", "fe_tables.h"),
     os.path.join(os.path.dirname(HERE), "include", "b200feat.h"),

@@ -19,6 +19,11 @@
 #include "fe_whisper2.cuh"
 #include "fe_kaldi.cuh"
 #include "fe_cosy.cuh"
+#include "fe_resample.cuh"
+#define FE_RS_HAVE_PARAMS
+#include "fe_resample_plan.h"
+#include <map>
+#include <tuple>
 
 // =====================================================================================================
 // kernels
@@ -742,6 +747,120 @@ int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, i
             fe_kaldi_cmn_kernel<<<(unsigned)(nc * slabs), 256, 0, st>>>(p, (int)slabs);
             g_launches++;
         }
+    }
+    FE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------ resample
+namespace {
+
+// tap tables are library-owned constants: built once per (device, ratio, filter) and kept until unload
+struct RsDevicePlan {
+    FeRsPlan plan;
+    float4* taps = nullptr;
+    int32_t* kstart = nullptr;
+};
+typedef std::tuple<int, int, int, int, double, int, double> RsKey;
+std::mutex g_rs_mu;
+std::map<RsKey, RsDevicePlan*> g_rs_plans;
+
+template <bool IN16, int CH, bool TS>
+int rs_launch(unsigned grid, size_t smem, cudaStream_t st, const FeResampleParams& p) {
+    static std::atomic<size_t> attr_bytes[64];
+    int dev = 0;
+    FE_CUDA(cudaGetDevice(&dev));
+    std::atomic<size_t>& have = attr_bytes[dev < 64 ? dev : 0];
+    if (smem > have.load()) {
+        FE_CUDA(cudaFuncSetAttribute(fe_resample_kernel<IN16, CH, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        have.store(smem);
+    }
+    fe_resample_kernel<IN16, CH, TS><<<grid, FeRsCfg::NT, smem, st>>>(p);
+    return 0;
+}
+
+int rs_dispatch(bool in16, int ch, bool ts, unsigned grid, size_t smem, cudaStream_t st, const FeResampleParams& p) {
+#define RS_CASE(A, C, T) if (in16 == A && ch == C && ts == T) return rs_launch<A, C, T>(grid, smem, st, p);
+    RS_CASE(false, 1, false) RS_CASE(false, 1, true) RS_CASE(false, 2, false) RS_CASE(false, 2, true)
+    RS_CASE(true, 1, false) RS_CASE(true, 1, true) RS_CASE(true, 2, false) RS_CASE(true, 2, true)
+#undef RS_CASE
+    return fail(B200FEAT_EINVAL, "resample: unsupported input format");
+}
+
+int rs_get_plan(int orig_freq, int new_freq, int lpfw, double rolloff, int method, double beta, RsDevicePlan** out) {
+    int dev = 0;
+    FE_CUDA(cudaGetDevice(&dev));
+    const RsKey key(dev, orig_freq, new_freq, lpfw, rolloff, method, beta);
+    std::lock_guard<std::mutex> lk(g_rs_mu);
+    auto it = g_rs_plans.find(key);
+    if (it != g_rs_plans.end()) { *out = it->second; return 0; }
+    RsDevicePlan* dp = new RsDevicePlan();
+    dp->plan = fe_rs_make_plan(orig_freq, new_freq, lpfw, rolloff, method, beta);
+    if (!dp->plan.error.empty()) {
+        const int rc = fail(B200FEAT_EINVAL, "resample: %s", dp->plan.error.c_str());
+        delete dp;
+        return rc;
+    }
+    // first call for this filter only: the table upload is synchronous
+    FE_CUDA(cudaMalloc(&dp->taps, dp->plan.taps.size() * sizeof(float)));
+    FE_CUDA(cudaMalloc(&dp->kstart, dp->plan.kstart.size() * sizeof(int32_t)));
+    FE_CUDA(cudaMemcpy(dp->taps, dp->plan.taps.data(), dp->plan.taps.size() * sizeof(float), cudaMemcpyHostToDevice));
+    FE_CUDA(cudaMemcpy(dp->kstart, dp->plan.kstart.data(), dp->plan.kstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    g_rs_plans[key] = dp;
+    *out = dp;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t b200feat_resample_out_len(int64_t n_frames, int32_t orig_freq, int32_t new_freq) {
+    return fe_rs_out_len(n_frames, orig_freq, new_freq);
+}
+
+int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                      const int64_t* lengths, int32_t B, int64_t L_in, int64_t pcm_stride,
+                      int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width, double rolloff,
+                      int32_t method, double beta, float* out, int64_t out_stride, int64_t L_out, void* cuda_stream) {
+    if (pcm_dtype != B200FEAT_F32 && pcm_dtype != B200FEAT_S16)
+        return fail(B200FEAT_EINVAL, "resample: pcm_dtype must be B200FEAT_F32 or B200FEAT_S16, got %d", pcm_dtype);
+    if (channels != 1 && channels != 2) return fail(B200FEAT_EINVAL, "resample: channels must be 1 or 2, got %d", channels);
+    if (orig_freq <= 0 || new_freq <= 0)
+        return fail(B200FEAT_EINVAL, "resample: Original frequency and desired frequecy should be positive");
+    if (B < 0) return fail(B200FEAT_EINVAL, "resample: B = %d < 0", B);
+    if (L_in < 0 || L_in > (int64_t)1 << 40) return fail(B200FEAT_EINVAL, "resample: bad L_in = %lld", (long long)L_in);
+    if (pcm_stride < L_in * channels) return fail(B200FEAT_EINVAL, "resample: pcm_stride %lld < L_in * channels", (long long)pcm_stride);
+    const int64_t full = fe_rs_out_len(L_in, orig_freq, new_freq);
+    if (L_out < 0 || L_out > full) return fail(B200FEAT_EINVAL, "resample: L_out %lld not in [0, %lld]", (long long)L_out, (long long)full);
+    if (out_stride < L_out) return fail(B200FEAT_EINVAL, "resample: out_stride %lld < L_out %lld", (long long)out_stride, (long long)L_out);
+    if (B > 0 && L_out > 0 && (pcm == nullptr || out == nullptr)) return fail(B200FEAT_EINVAL, "resample: null pcm/out pointer");
+    if (B == 0 || L_out == 0) return 0;
+    if (int rc = check_device_arch()) return rc;
+    if (method == FE_RS_KAISER) beta = (double)(float)beta;    // the reference holds beta in a float32 tensor
+    else beta = 0.0;
+    RsDevicePlan* dp = nullptr;
+    if (int rc = rs_get_plan(orig_freq, new_freq, lowpass_filter_width, rolloff, method, beta, &dp)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    FeResampleParams p;
+    memset(&p, 0, sizeof(p));
+    fe_rs_fill_params(p, dp->plan, L_in, L_out, channels, pcm_dtype == B200FEAT_S16, mix_host);
+    p.in = pcm; p.lengths = lengths; p.out = out; p.in_stride = pcm_stride; p.out_stride = out_stride;
+    p.taps = dp->taps; p.kstart = dp->kstart;
+    const int64_t frame_bytes = (int64_t)channels * (pcm_dtype == B200FEAT_S16 ? 2 : 4);
+    p.vec_ok = (reinterpret_cast<uintptr_t>(pcm) % frame_bytes == 0 && pcm_stride % channels == 0) ? 1 : 0;
+    const int64_t tiles = p.tiles_per_clip;
+    int64_t per_launch = 0x7fffffff / tiles;
+    if (per_launch < 1) return fail(B200FEAT_EINVAL, "resample: clip too long");
+    for (int64_t c0 = 0; c0 < B; c0 += per_launch) {
+        const int64_t nc = (B - c0 < per_launch) ? (B - c0) : per_launch;
+        p.clip0 = (int32_t)c0;
+        ProfScope ps(st, 0);
+        if (int rc = rs_dispatch(pcm_dtype == B200FEAT_S16, channels, dp->plan.taps_smem, (unsigned)(nc * tiles),
+                                 dp->plan.smem_bytes, st, p)) return rc;
+        g_launches++;
     }
     FE_CUDA(cudaGetLastError());
     return 0;

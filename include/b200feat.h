@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define B200FEAT_VERSION 100 /* major*10000 + minor*100 + patch */
+#define B200FEAT_VERSION 101 /* major*10000 + minor*100 + patch */
 
 enum {
     B200FEAT_OK = 0,
@@ -107,6 +107,34 @@ int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, i
                          int64_t wave_stride, int32_t subtract_mean, float* out,
                          int64_t out_batch_stride, int64_t T_out,
                          void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
+/* Waveform conditioning in front of the featurizers: interleaved PCM -> mono mix ->
+ * band-limited polyphase resampling, fused in one kernel (the PCM is read once, nothing intermediate touches HBM).
+ * Replaces
+ *   torchaudio.transforms.Resample(orig_freq, 16000, lowpass_filter_width=128, rolloff=0.95,
+ *       resampling_method='kaiser_window', beta=14.769656459379492)(audio) followed by the stereo -> mono mix at
+ *       /root/reference/Backend/services/audio_processor.py:295-319 (mean of the channels, or mid + 0.3 * side =
+ *       0.65 L + 0.35 R: both are `mix` weights; resampling and mixing are linear, so their order does not matter),
+ *   torchaudio.functional.resample(wave, 44100, 16000) of SURVEY.md's cfg1 recipe (Backend/harvard.wav), and the
+ *   CosyVoice frontend's Resample(16000 -> 24000) (UPSTREAM, reached from /root/reference/Docker/cosyvoice_api.py:128).
+ * Arithmetic: site-packages/torchaudio/functional/functional.py:1305-1432 (`_get_sinc_resample_kernel`, taps computed
+ * in float64 and stored as float32 like transforms.Resample does; `_apply_sinc_resample_kernel`), float32 accumulation,
+ * only the taps inside the window's support are evaluated.
+ *   pcm        device pointer, (B, L_in, channels) interleaved; pcm_dtype B200FEAT_F32 or B200FEAT_S16 (int16 is scaled by
+ *              1/32768 like whisper.audio.load_audio); pcm_stride = elements between clips (>= L_in * channels)
+ *   channels   1 or 2;  mix_host: HOST pointer to `channels` weights, NULL = mean of the channels
+ *   lengths    device int64[B] input frames per clip or NULL; a clip yields ceil(new * len / orig) samples, the rest
+ *              of its row up to L_out is written as 0
+ *   method     B200FEAT_RESAMPLE_HANN ("sinc_interp_hann") or B200FEAT_RESAMPLE_KAISER ("sinc_interp_kaiser", beta)
+ *   out        (B, out_stride) float32, L_out <= b200feat_resample_out_len(L_in, orig, new) samples per row
+ * The tap table of a (device, ratio, filter) is built and uploaded on its first use (that one call copies
+ * synchronously) and owned by the library; every other call is asynchronous on cuda_stream. */
+enum { B200FEAT_RESAMPLE_HANN = 0, B200FEAT_RESAMPLE_KAISER = 1 };
+int64_t b200feat_resample_out_len(int64_t n_frames, int32_t orig_freq, int32_t new_freq);
+int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                      const int64_t* lengths, int32_t B, int64_t L_in, int64_t pcm_stride,
+                      int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width, double rolloff,
+                      int32_t method, double beta, float* out, int64_t out_stride, int64_t L_out, void* cuda_stream);
 
 /* Host-buffer variants (the end-to-end path): wave_host / out_host are HOST pointers (pinned memory
  * gives full PCIe bandwidth); clips are streamed through a library-owned device arena in chunks with

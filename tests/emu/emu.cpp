@@ -177,3 +177,41 @@ extern "C" int emu_cosy(const float* wave, const int64_t* lengths, int B, int64_
     }
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------ resample
+#include "fe_resample.cuh"
+#define FE_RS_HAVE_PARAMS
+#include "fe_resample_plan.h"
+template <bool IN16, int CH>
+static void emu_rs_run(FeResampleParams& p, const FeRsPlan& pl, int B) {
+    std::vector<float> xs(pl.xs_floats), ost((size_t)32 * pl.OP);
+    for (int cta = 0; cta < B * p.tiles_per_clip; ++cta) {
+        std::fill(xs.begin(), xs.end(), 1e30f);      // anything read but not loaded shows up
+        std::fill(ost.begin(), ost.end(), 1e30f);
+        for (int tid = 0; tid < FeRsCfg::NT; ++tid) fe_rs_load<IN16, CH>(p, xs.data(), tid, cta);
+        for (int tid = 0; tid < FeRsCfg::NT; ++tid) fe_rs_compute(p, xs.data(), ost.data(), p.taps, tid);
+        for (int tid = 0; tid < FeRsCfg::NT; ++tid) fe_rs_store(p, ost.data(), tid, cta);
+    }
+}
+
+// in: (B, L_in, channels) interleaved float32 or int16; out: (B, L_out) with L_out = ceil(new * L_in / orig);
+// info (optional, 8 ints): orig, new, m, width, G, J, smem_bytes, taps_smem
+extern "C" int emu_resample(const void* in, int in_s16, int channels, const float* mix, const int64_t* lengths, int B,
+                            int64_t L_in, int orig_freq, int new_freq, int lpfw, double rolloff, int method,
+                            double beta, float* out, int64_t L_out, int* info) {
+    FeRsPlan pl = fe_rs_make_plan(orig_freq, new_freq, lpfw, rolloff, method, beta);
+    if (!pl.error.empty()) return -1;
+    if (info) {
+        info[0] = pl.orig; info[1] = pl.newf; info[2] = pl.m; info[3] = pl.width; info[4] = pl.G; info[5] = pl.J;
+        info[6] = (int)pl.smem_bytes; info[7] = pl.taps_smem;
+    }
+    FeResampleParams p;
+    memset(&p, 0, sizeof(p));
+    fe_rs_fill_params(p, pl, L_in, L_out, channels, in_s16 != 0, mix);
+    p.in = in; p.lengths = lengths; p.out = out; p.in_stride = L_in * channels; p.out_stride = L_out;
+    p.taps = (const float4*)pl.taps.data(); p.kstart = pl.kstart.data(); p.clip0 = 0;
+    p.vec_ok = ((uintptr_t)in % (size_t)(channels * (in_s16 ? 2 : 4)) == 0) ? 1 : 0;
+    if (in_s16) { if (channels == 1) emu_rs_run<true, 1>(p, pl, B); else emu_rs_run<true, 2>(p, pl, B); }
+    else        { if (channels == 1) emu_rs_run<false, 1>(p, pl, B); else emu_rs_run<false, 2>(p, pl, B); }
+    return 0;
+}

@@ -40,7 +40,7 @@ def test_no_torch_or_cxx_types_in_header():
 
 
 def test_version_frames_workspace(lib):
-    assert lib.b200feat_version() == 100
+    assert lib.b200feat_version() == 101
     assert lib.b200feat_num_frames(0, 480000, 0) == 3000
     assert lib.b200feat_num_frames(0, 960000, 480000) == 9000
     assert lib.b200feat_num_frames(0, 293700, 0) == 1835

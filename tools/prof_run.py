@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Small driver for ncu captures: a few launches of one featurizer on a short batch.
-    python tools/prof_run.py whisper128|whisper80|kaldi|cosy [clips]
+    python tools/prof_run.py whisper128|whisper80|kaldi|cosy|resample|resample_kaiser [clips]
 """
 import os
 import sys
@@ -16,6 +16,11 @@ if kind.startswith("whisper"):
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 64
     x = (0.1 * torch.randn(n, 480000, generator=g, device="cuda")).clamp_(-1, 1)
     f = lambda: fe.whisper_log_mel_batch(x, n_mels=int(kind[7:]))
+elif kind.startswith("resample"):           # resample | resample_kaiser : 30-s clips of 44.1 kHz stereo int16 -> 16 kHz mono
+    n = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+    x = torch.randint(-20000, 20000, (n, 1323000, 2), generator=g, dtype=torch.int16, device="cuda")
+    kw = dict(lowpass_filter_width=128, rolloff=0.95, resampling_method="sinc_interp_kaiser") if kind.endswith("kaiser") else {}
+    f = lambda: fe.condition_pcm(x, 44100, 16000, **kw)
 elif kind == "kaldi":
     n = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
     x = (0.1 * torch.randn(n, 80000, generator=g, device="cuda")).clamp_(-1, 1)
