@@ -102,6 +102,21 @@ class Workload:
             self.featurizer = "whisper_log_mel"
             self.traffic_key = None
             self.cpu_desc = "oracle fp32 = torch.stft + dense mel matmul + log10/max-8 (the ops whisper.audio runs)"
+        elif key == "cfg2pcm":
+            # cfg2 as the audio really arrives -- 44.1 kHz stereo int16 PCM -> mono mix +
+            # torchaudio-compatible resampling to 16 kHz (b200feat_resample) -> Whisper 128-bin log-mel, device-resident
+            self.B, self.L, self.sr, self.n_mels = 1024, 480000, 16000, 128
+            self.pcm_sr, self.pcm_L, self.pcm_ch = 44100, 1323000, 2
+            self.T = self.L // 160
+            self.out_shape = (self.B, self.n_mels, self.T)
+            self.kernel = "fe_resample_kernel<1, 2, 1>"
+            self.cpu_clips = 32
+            self.desc = ("SURVEY 8(f)1 in front of BASELINE configs[1]: 1024 x 30 s of 44.1 kHz stereo int16 PCM -> mono + resample to "
+                         "16 kHz -> Whisper large-v3 128-bin log-mel per GPU")
+            self.featurizer = "condition_pcm + whisper_log_mel"
+            self.traffic_key = "fe_resample_kernel_s16x2_dram_bytes_per_1024_clips"
+            self.cpu_desc = ("mean of the channels + torchaudio.functional.resample(44100 -> 16000) + oracle fp32 log-mel "
+                             "(torch.stft + dense mel matmul + log10/max-8): the reference's own ops")
         else:
             raise ValueError(key)
         self.audio_s_per_step = self.B * self.L / self.sr              # this rank's share
@@ -111,16 +126,26 @@ class Workload:
         self.e2e_clips = min(self.B, 1024)                              # clips of the shard the host-buffer leg streams per step
         self.out_per_clip = self.out_shape[1] * self.out_shape[2]
         self.bytes_per_clip = 4 * self.L + 4 * self.out_per_clip     # algorithmic: 4*(in) + 4*(out)
+        if key == "cfg2pcm":                                          # the roofline kernel here is the resampler: PCM in + waveform out
+            self.bytes_per_clip = self.pcm_L * self.pcm_ch * 2 + 4 * self.L
 
     def config(self, n_gpus):
         tot_in, tot_out = self.B * self.L * 4 / 1e9, self.B * self.out_per_clip * 4 / 1e9
         return {"workload": self.desc, "featurizer": self.featurizer, "n_mels": self.n_mels, "clips_per_gpu": self.B,
-                "samples_per_clip": self.L, "global_clips": self.total_clips if self.key == "cfg5" else self.B * n_gpus,
+                "samples_per_clip": self.L, "pcm": (f"{self.pcm_sr} Hz x {self.pcm_ch} ch int16, {self.pcm_L} frames per clip"
+                                                    if self.key == "cfg2pcm" else None), "global_clips": self.total_clips if self.key == "cfg5" else self.B * n_gpus,
                 "norm": "per_clip" if self.key in ("cfg2", "cfg5") else None,
                 "parallelism": f"clip-sharded x{n_gpus}, no collective",
                 "l2_policy": f"inputs ({tot_in:.2f} GB) and outputs ({tot_out:.2f} GB) per step exceed the 126 MB L2; no flush needed"}
 
     def device_step(self, fe, x, out):
+        if self.key == "cfg2pcm":
+            wav = torch.empty((self.B, self.L), dtype=torch.float32, device=x.device)
+
+            def chain():
+                fe.condition_pcm(x, self.pcm_sr, self.sr, out=wav)
+                fe.whisper_log_mel_batch(wav, n_mels=self.n_mels, norm="per_clip", out=out)
+            return chain
         if self.key == "cfg2":
             return lambda: fe.whisper_log_mel_batch(x, n_mels=self.n_mels, norm="per_clip", out=out)
         if self.key == "cfg5":
@@ -135,6 +160,26 @@ class Workload:
         return lambda: fe.kaldi_fbank_batch(x, subtract_mean=True, out=out)
 
     def host_step(self, fe, xh, oh, dev):
+        if self.key == "cfg2pcm":
+            # pinned int16 PCM in -> pinned float32 features out, 128 clips at a time on two streams so that the copies of
+            # one slice overlap the kernels of the other (the library has no host-buffer twin of the resampler yet)
+            streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
+            n = 128
+            xd = [torch.empty((n,) + tuple(xh.shape[1:]), dtype=torch.int16, device=dev) for _ in streams]
+            wd = [torch.empty((n, self.L), dtype=torch.float32, device=dev) for _ in streams]
+            od = [torch.empty((n,) + tuple(self.out_shape[1:]), dtype=torch.float32, device=dev) for _ in streams]
+
+            def chain_host():
+                for i, (lo, hi) in enumerate(manifest.sub_batches(0, xh.shape[0], n)):
+                    k, m = i % 2, hi - lo
+                    with torch.cuda.stream(streams[k]):
+                        xd[k][:m].copy_(xh[lo:hi], non_blocking=True)
+                        fe.condition_pcm(xd[k][:m], self.pcm_sr, self.sr, out=wd[k][:m])
+                        fe.whisper_log_mel_batch(wd[k][:m], n_mels=self.n_mels, norm="per_clip", out=od[k][:m])
+                        oh[lo:hi].copy_(od[k][:m], non_blocking=True)
+                for st in streams:
+                    st.synchronize()
+            return chain_host
         if self.key in ("cfg2", "cfg5"):
             return lambda: fe.whisper_log_mel_host(xh, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
         if self.key == "cfg3":
@@ -144,6 +189,14 @@ class Workload:
     def cpu_step(self):
         import oracle
         g = torch.Generator().manual_seed(1234)
+        if self.key == "cfg2pcm":
+            from oracle import resample as orc
+            pcm = torch.randint(-20000, 20000, (self.cpu_clips, self.pcm_L, self.pcm_ch), generator=g, dtype=torch.int16)
+
+            def ref_chain():
+                mono = (pcm.to(torch.float32) / 32768.0).mean(dim=2)
+                return oracle.whisper_log_mel(orc.reference_resample(mono, self.pcm_sr, self.sr), self.n_mels, norm="per_clip")
+            return ref_chain, self.cpu_clips * self.L / self.sr
         x = (0.1 * torch.randn(self.cpu_clips, self.L, generator=g)).clamp_(-1, 1)
         if self.key in ("cfg2", "cfg5"):
             return (lambda: oracle.whisper_log_mel(x, self.n_mels, norm="per_clip")), self.cpu_clips * self.L / self.sr
@@ -278,6 +331,8 @@ def run_ours(args, rank, world, local_rank):
         x = torch.empty(WL.B, WL.L, dtype=torch.float32, device=dev)    # 38.4 GB at N = 1: filled in place, 256 clips at a time
         for lo, hi in manifest.sub_batches(0, WL.B, 256):
             x[lo:hi].normal_(generator=gen).mul_(0.1).clamp_(-1, 1)
+    elif WL.key == "cfg2pcm":
+        x = torch.randint(-20000, 20000, (WL.B, WL.pcm_L, WL.pcm_ch), generator=gen, dtype=torch.int16, device=dev)
     else:
         x = (0.1 * torch.randn(WL.B, WL.L, generator=gen, device=dev)).clamp_(-1, 1)
     out = torch.empty(WL.out_shape, dtype=torch.float32, device=dev)
@@ -304,8 +359,14 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- the featurizer kernel alone (per-launch CUDA events inside the library), rank 0 reports
     fe.profile_begin()
-    for _ in range(args.steps):
-        step()
+    if WL.key == "cfg2pcm":
+        wav_r = torch.empty((WL.B, WL.L), dtype=torch.float32, device=dev)
+        for _ in range(args.steps):
+            fe.condition_pcm(x, WL.pcm_sr, WL.sr, out=wav_r)          # the row's own kernel; the log-mel kernel is cfg2's roofline
+        del wav_r
+    else:
+        for _ in range(args.steps):
+            step()
     torch.cuda.synchronize()
     prof = fe.profile_end()
     k_ms = prof["feature_ms"] / max(prof["feature_launches"], 1)
@@ -332,6 +393,12 @@ def run_ours(args, rank, world, local_rank):
                 "epilogue_ms_per_step": prof["epilogue_ms"] / args.steps,
                 "step_frac": (WL.B * WL.bytes_per_clip / (ms_step / 1.0 * 1e-3) / 1e9) / peak if world == 1 else None}
 
+    if WL.key == "cfg2pcm":
+        roofline["kernel_share_of_step"] = k_ms / ms_step
+        roofline["note"] = ("the row's own kernel (mono mix + resampler) timed alone; the rest of the step is cfg2's log-mel kernel, "
+                            "whose roofline is the default workload's line")
+        roofline["step_frac"] = None
+
     # ---- device-resident step with the narrow dtypes (int16 PCM in, float16 out), Whisper workloads only
     narrow_dev_ms = None
     if WL.featurizer == "whisper_log_mel":
@@ -354,7 +421,10 @@ def run_ours(args, rank, world, local_rank):
     bound = None if os.environ.get("B200FEAT_NO_NUMA_BIND") else manifest.bind_host_to_gpu(local_rank)
     del out
     ne = WL.e2e_clips
-    xh = torch.empty((ne, WL.L), dtype=torch.float32, pin_memory=True)
+    if WL.key == "cfg2pcm":
+        xh = torch.empty((ne, WL.pcm_L, WL.pcm_ch), dtype=torch.int16, pin_memory=True)
+    else:
+        xh = torch.empty((ne, WL.L), dtype=torch.float32, pin_memory=True)
     xh.copy_(x[:ne])
     del x
     oh = torch.empty((ne,) + tuple(WL.out_shape[1:]), dtype=torch.float32, pin_memory=True)
@@ -373,9 +443,11 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
     e2e = {"value": world * ne * WL.L / WL.sr / (e2e_ms * 1e-3), "unit": UNIT,
-           "h2d_bytes_per_step": ne * WL.L * 4, "d2h_bytes_per_step": ne * WL.out_per_clip * 4,
+           "h2d_bytes_per_step": xh.numel() * xh.element_size(), "d2h_bytes_per_step": ne * WL.out_per_clip * 4,
            "ms_per_step": e2e_ms, "steps": e2e_steps, "clips_per_step_per_gpu": ne, "host_cpus_bound": len(bound) if bound else None,
-           "api": f"{WL.featurizer}_host -> b200feat_*_host (pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"}
+           "api": (f"{WL.featurizer}_host -> b200feat_*_host (pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"
+                   if WL.key != "cfg2pcm" else
+                   "pinned int16 PCM -> condition_pcm + whisper_log_mel_batch on two streams, 128 clips per slice -> pinned float32 features")}
 
     # ---- the same leg with the narrow dtypes either side of the path: int16 PCM in, float16
     # features out -- half the PCIe bytes.  Reported next to e2e, never instead of it (the reference API is float32).
@@ -420,7 +492,8 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": WL.scaling, "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic (0.1*N(0,1) clipped to [-1,1], seed 1234+rank, generated on device)",
+                "data": ("synthetic (0.1*N(0,1) clipped to [-1,1], seed 1234+rank, generated on device)" if WL.key != "cfg2pcm" else
+                         "synthetic (uniform int16 in [-20000, 20000), stereo, seed 1234+rank, generated on device)"),
                 "config": WL.config(world), "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
                 "gpu_launches": launches, "clocks": clk}
         if world > 1:
@@ -434,9 +507,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4", "cfg5"],
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4", "cfg5", "cfg2pcm"],
                     help="BASELINE.json config: cfg2 = Whisper 128-bin (the headline; default), cfg3 = CosyVoice mel, cfg4 = kaldi fbank, "
-                         "cfg5 = manifest sweep (10 000 x 60 s, Whisper 80-bin, strong scaling)")
+                         "cfg5 = manifest sweep (10 000 x 60 s, Whisper 80-bin, strong scaling), cfg2pcm = cfg2 fed with 44.1 kHz stereo "
+                         "int16 PCM through the fused mono-mix + resampler (SURVEY 8(f) item 1)")
     args = ap.parse_args()
     global WL
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)

@@ -63,20 +63,22 @@ FE_HD FE_INLINE int64_t fe_rs_len(const FeResampleParams& p, int clip) {
 template <bool IN16, int CH> struct FeRsRaw;
 template <> struct FeRsRaw<true, 1> {
     int v;
+    static constexpr int FRAME_BYTES = 2;
     FE_HD FE_INLINE void zero() { v = 0; }
-    FE_HD FE_INLINE void load(const FeResampleParams&, const void* row, int64_t g) { v = ((const short*)row)[g]; }
+    FE_HD FE_INLINE void load(const FeResampleParams&, const char* src, int n) { v = ((const short*)src)[n]; }
     FE_HD FE_INLINE float value(const FeResampleParams& p) const {
         return p.w0 * (fe_int_bits_as_float(0x4B400000 + v) - 12582912.0f);
     }
 };
 template <> struct FeRsRaw<true, 2> {
     int v;   // low half = channel 0, high half = channel 1
+    static constexpr int FRAME_BYTES = 4;
     FE_HD FE_INLINE void zero() { v = 0; }
-    FE_HD FE_INLINE void load(const FeResampleParams& p, const void* row, int64_t g) {
-        if (p.vec_ok) v = ((const int*)row)[g];
+    FE_HD FE_INLINE void load(const FeResampleParams& p, const char* src, int n) {
+        if (p.vec_ok) v = ((const int*)src)[n];
         else {
-            const unsigned short* s = (const unsigned short*)row;
-            v = (int)((unsigned)s[2 * g] | ((unsigned)s[2 * g + 1] << 16));
+            const unsigned short* s = (const unsigned short*)src;
+            v = (int)((unsigned)s[2 * n] | ((unsigned)s[2 * n + 1] << 16));
         }
     }
     FE_HD FE_INLINE float value(const FeResampleParams& p) const {
@@ -87,46 +89,67 @@ template <> struct FeRsRaw<true, 2> {
 };
 template <> struct FeRsRaw<false, 1> {
     float v;
+    static constexpr int FRAME_BYTES = 4;
     FE_HD FE_INLINE void zero() { v = 0.0f; }
-    FE_HD FE_INLINE void load(const FeResampleParams&, const void* row, int64_t g) { v = ((const float*)row)[g]; }
+    FE_HD FE_INLINE void load(const FeResampleParams&, const char* src, int n) { v = ((const float*)src)[n]; }
     FE_HD FE_INLINE float value(const FeResampleParams& p) const { return p.w0 * v; }
 };
 template <> struct FeRsRaw<false, 2> {
     float2 v;
+    static constexpr int FRAME_BYTES = 8;
     FE_HD FE_INLINE void zero() { v.x = 0.0f; v.y = 0.0f; }
-    FE_HD FE_INLINE void load(const FeResampleParams& p, const void* row, int64_t g) {
-        if (p.vec_ok) v = ((const float2*)row)[g];
-        else { v.x = ((const float*)row)[2 * g]; v.y = ((const float*)row)[2 * g + 1]; }
+    FE_HD FE_INLINE void load(const FeResampleParams& p, const char* src, int n) {
+        if (p.vec_ok) v = ((const float2*)src)[n];
+        else { v.x = ((const float*)src)[2 * n]; v.y = ((const float*)src)[2 * n + 1]; }
     }
     FE_HD FE_INLINE float value(const FeResampleParams& p) const { return fmaf(p.w1, v.y, p.w0 * v.x); }
 };
 
-// phase 1: mono-mixed input tile -> shared memory rows of orig_e samples, pitch P
+// phase 1: mono-mixed input tile -> shared memory rows of orig_e samples, pitch P.  Tile sample n is clip frame
+// g0 + n; frames [nlo, nhi) of the tile exist, the rest is zero padding.  Batches of eight frames per thread that lie
+// wholly inside take the unpredicated path (32-bit indices, every later address an immediate off the first).
 template <bool IN16, int CH>
 FE_HD FE_INLINE void fe_rs_load(const FeResampleParams& p, float* xs, int tid, int cta) {
-    constexpr int U = 8;
+    typedef FeRsRaw<IN16, CH> Raw;
+    constexpr int U = 8, NT = FeRsCfg::NT;
     const int clip = p.clip0 + cta / p.tiles_per_clip;
     const int tile = cta % p.tiles_per_clip;
     const int64_t len = fe_rs_len(p, clip);
-    const char* row = (const char*)p.in + (int64_t)clip * p.in_stride * (IN16 ? 2 : 4);
     const int64_t g0 = (int64_t)tile * FeRsCfg::QB * p.orig_e - p.width;
+    const char* src = (const char*)p.in + ((int64_t)clip * p.in_stride * (IN16 ? 2 : 4) + g0 * Raw::FRAME_BYTES);
+    const int nlo = g0 < 0 ? (int)(-g0) : 0;
+    const int64_t rest = len - g0;
+    const int nhi = rest <= 0 ? 0 : (rest < p.nx ? (int)rest : p.nx);
     const bool skew = p.P != p.orig_e;
-    for (int n0 = tid; n0 < p.nx; n0 += U * FeRsCfg::NT) {
-        FeRsRaw<IN16, CH> raw[U];
+    for (int n0 = tid; n0 < p.nx; n0 += U * NT) {
+        Raw raw[U];
+        if (n0 >= nlo && n0 + (U - 1) * NT < nhi) {
 #if defined(__CUDACC__)
 #pragma unroll
 #endif
-        for (int u = 0; u < U; ++u) {
-            const int n = n0 + u * FeRsCfg::NT;
-            const int64_t g = g0 + n;
-            raw[u].zero();
-            if (n < p.nx && g >= 0 && g < len) raw[u].load(p, row, g);
+            for (int u = 0; u < U; ++u) raw[u].load(p, src, n0 + u * NT);
+            if (!skew) {
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+                for (int u = 0; u < U; ++u) xs[n0 + u * NT] = raw[u].value(p);
+                continue;
+            }
+        } else {
+#if defined(__CUDACC__)
+#pragma unroll
+#endif
+            for (int u = 0; u < U; ++u) {
+                const int n = n0 + u * NT;
+                raw[u].zero();
+                if (n >= nlo && n < nhi) raw[u].load(p, src, n);
+            }
         }
 #if defined(__CUDACC__)
 #pragma unroll
 #endif
         for (int u = 0; u < U; ++u) {
-            const int n = n0 + u * FeRsCfg::NT;
+            const int n = n0 + u * NT;
             if (n < p.nx) {
                 const int a = skew ? n + (int)((unsigned)n / (unsigned)p.orig_e) : n;
                 xs[a] = raw[u].value(p);
@@ -135,7 +158,8 @@ FE_HD FE_INLINE void fe_rs_load(const FeResampleParams& p, float* xs, int tid, i
     }
 }
 
-// phase 2: warp <-> phase group, lane <-> block; results to the transposed output tile
+// phase 2: warp <-> phase group, lane <-> block; results to the transposed output tile.  The four accumulators are
+// two packed pairs: one FFMA2 (sample broadcast by the instruction) per two phases.
 FE_HD FE_INLINE void fe_rs_compute(const FeResampleParams& p, const float* xs, float* ost, const float4* taps,
                                    int tid) {
     const int warp = tid >> 5, lane = tid & 31;
@@ -147,7 +171,7 @@ FE_HD FE_INLINE void fe_rs_compute(const FeResampleParams& p, const float* xs, f
         int col = k0 % p.orig_e;
         const int off = (k0 / p.orig_e) * p.P + col;
         const float4* tg = taps + (int64_t)g * p.J;
-        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+        fe2 a01 = fe_mk2(0.0f, 0.0f), a23 = fe_mk2(0.0f, 0.0f);
         const float* xp = xl + off;
         // the J samples of the window are contiguous within a row; with an odd orig_e (no pitch padding) across rows too
         for (int j = 0; j < p.J;) {
@@ -159,36 +183,39 @@ FE_HD FE_INLINE void fe_rs_compute(const FeResampleParams& p, const float* xs, f
             for (int i = 0; i < run; ++i) {
                 const float4 t = tg[i];
                 const float x = xp[i];
-                a0 = fmaf(t.x, x, a0);
-                a1 = fmaf(t.y, x, a1);
-                a2 = fmaf(t.z, x, a2);
-                a3 = fmaf(t.w, x, a3);
+                a01 = fe_fmac(x, fe_mk2(t.x, t.y), a01);
+                a23 = fe_fmac(x, fe_mk2(t.z, t.w), a23);
             }
             j += run; tg += run; xp += run + wrap; col = 0;
         }
         const int pe = g * FeRsCfg::R;
-        ol[pe] = a0;
-        if (pe + 1 < p.new_e) ol[pe + 1] = a1;
-        if (pe + 2 < p.new_e) ol[pe + 2] = a2;
-        if (pe + 3 < p.new_e) ol[pe + 3] = a3;
+        ol[pe] = a01.x;
+        if (pe + 1 < p.new_e) ol[pe + 1] = a01.y;
+        if (pe + 2 < p.new_e) ol[pe + 2] = a23.x;
+        if (pe + 3 < p.new_e) ol[pe + 3] = a23.y;
     }
 }
 
-// phase 3: output tile -> global, one block row (new_e consecutive samples) per warp step
+// phase 3: output tile -> global, one block row (new_e consecutive samples) per warp step; tile-relative 32-bit
+// indices: [0, nvalid) carries samples, [nvalid, nwrite) the zeros past a ragged clip's end
 FE_HD FE_INLINE void fe_rs_store(const FeResampleParams& p, const float* ost, int tid, int cta) {
     const int clip = p.clip0 + cta / p.tiles_per_clip;
     const int tile = cta % p.tiles_per_clip;
     const int64_t len = fe_rs_len(p, clip);
     const int64_t len_out = (len * p.newf + p.orig - 1) / p.orig;
-    float* orow = p.out + (int64_t)clip * p.out_stride;
     const int64_t i0 = (int64_t)tile * FeRsCfg::QB * p.new_e;
+    const int tile_out = FeRsCfg::QB * p.new_e;
+    float* orow = p.out + ((int64_t)clip * p.out_stride + i0);
+    const int64_t v64 = len_out - i0, w64 = p.L_out - i0;
+    const int nvalid = v64 <= 0 ? 0 : (v64 < tile_out ? (int)v64 : tile_out);
+    const int nwrite = w64 <= 0 ? 0 : (w64 < tile_out ? (int)w64 : tile_out);
     const int warp = tid >> 5, lane = tid & 31;
     for (int blk = warp; blk < FeRsCfg::QB; blk += FeRsCfg::NW) {
-        const int64_t ib = i0 + (int64_t)blk * p.new_e;
         const float* src = ost + blk * p.OP;
+        const int ib = blk * p.new_e;
         for (int pe = lane; pe < p.new_e; pe += 32) {
-            const int64_t i = ib + pe;
-            if (i < p.L_out) orow[i] = (i < len_out) ? src[pe] : 0.0f;
+            const int i = ib + pe;
+            if (i < nwrite) orow[i] = (i < nvalid) ? src[pe] : 0.0f;
         }
     }
 }
