@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200feat.so")
+# B200FEAT_LIB: another build of the same library (A/B timing of kernel variants); there is still no fallback
+LIB_PATH = os.environ.get("B200FEAT_LIB") or os.path.join(_HERE, "lib", "libb200feat.so")
 
 KIND_WHISPER, KIND_COSY, KIND_KALDI = 0, 1, 2
 NORM_PER_CLIP, NORM_PER_CALL = 0, 1
