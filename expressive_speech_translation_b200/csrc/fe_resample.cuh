@@ -158,14 +158,54 @@ FE_HD FE_INLINE void fe_rs_load(const FeResampleParams& p, float* xs, int tid, i
     }
 }
 
-// phase 2: warp <-> phase group, lane <-> block; results to the transposed output tile.  The four accumulators are
-// two packed pairs: one FFMA2 (sample broadcast by the instruction) per two phases.
+// phase 2: warp <-> phase group, lane <-> block; results to the transposed output tile.  The four accumulators of a
+// group are two packed pairs: one FFMA2 (sample broadcast by the instruction) per two phases.
 FE_HD FE_INLINE void fe_rs_compute(const FeResampleParams& p, const float* xs, float* ost, const float4* taps,
                                    int tid) {
     const int warp = tid >> 5, lane = tid & 31;
     const float* xl = xs + lane * p.P;
     float* ol = ost + lane * p.OP;
     const int wrap = p.P - p.orig_e;
+    if (wrap == 0) {
+        // odd orig_e (no pitch padding): the window is one contiguous run.  A warp's groups are taken two at a time so
+        // that two independent tap / sample streams are in flight (same per-phase summation order as the loop below):
+        // 3.65 -> 3.34 ms on the cfg2-sized 44.1 kHz batch.  Folding the padded-pitch case into the same two-stream
+        // loop (segments between the streams' row crossings) was measured slower for every ratio, so it keeps its own loop.
+        for (int g = warp; g < p.G; g += 2 * FeRsCfg::NW) {
+            const int g2 = g + FeRsCfg::NW;
+            const bool two = g2 < p.G;
+            const float* xa = xl + p.kstart[g];
+            const float* xb = xl + p.kstart[two ? g2 : g];
+            const float4* ta = taps + (int64_t)g * p.J;
+            const float4* tb = taps + (int64_t)(two ? g2 : g) * p.J;
+            fe2 a01 = fe_mk2(0.0f, 0.0f), a23 = fe_mk2(0.0f, 0.0f), b01 = fe_mk2(0.0f, 0.0f), b23 = fe_mk2(0.0f, 0.0f);
+#if defined(__CUDACC__)
+#pragma unroll 4
+#endif
+            for (int j = 0; j < p.J; ++j) {
+                const float4 t = ta[j], u = tb[j];
+                const float x = xa[j], y = xb[j];
+                a01 = fe_fmac(x, fe_mk2(t.x, t.y), a01);
+                a23 = fe_fmac(x, fe_mk2(t.z, t.w), a23);
+                b01 = fe_fmac(y, fe_mk2(u.x, u.y), b01);
+                b23 = fe_fmac(y, fe_mk2(u.z, u.w), b23);
+            }
+            int pe = g * FeRsCfg::R;
+            ol[pe] = a01.x;
+            if (pe + 1 < p.new_e) ol[pe + 1] = a01.y;
+            if (pe + 2 < p.new_e) ol[pe + 2] = a23.x;
+            if (pe + 3 < p.new_e) ol[pe + 3] = a23.y;
+            if (two) {
+                pe = g2 * FeRsCfg::R;
+                ol[pe] = b01.x;
+                if (pe + 1 < p.new_e) ol[pe + 1] = b01.y;
+                if (pe + 2 < p.new_e) ol[pe + 2] = b23.x;
+                if (pe + 3 < p.new_e) ol[pe + 3] = b23.y;
+            }
+        }
+        return;
+    }
+    // even orig_e: rows are padded to an odd pitch, a window may cross into the next row
     for (int g = warp; g < p.G; g += FeRsCfg::NW) {
         const int k0 = p.kstart[g];
         int col = k0 % p.orig_e;
@@ -173,10 +213,9 @@ FE_HD FE_INLINE void fe_rs_compute(const FeResampleParams& p, const float* xs, f
         const float4* tg = taps + (int64_t)g * p.J;
         fe2 a01 = fe_mk2(0.0f, 0.0f), a23 = fe_mk2(0.0f, 0.0f);
         const float* xp = xl + off;
-        // the J samples of the window are contiguous within a row; with an odd orig_e (no pitch padding) across rows too
         for (int j = 0; j < p.J;) {
             const int left = p.J - j, row_left = p.orig_e - col;
-            const int run = (wrap == 0 || left < row_left) ? left : row_left;
+            const int run = left < row_left ? left : row_left;
 #if defined(__CUDACC__)
 #pragma unroll 4
 #endif

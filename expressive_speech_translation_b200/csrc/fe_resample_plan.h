@@ -78,8 +78,10 @@ static inline FeRsPlan fe_rs_make_plan(int orig_freq, int new_freq, int lpfw, do
     }
 
     // blocks run m at a time so that a 32-block tile is a useful amount of work and still fits shared memory
+    // (an odd orig stays odd under an odd m: no pitch padding, and the tap loop takes its two-stream form)
     int m = std::max(1, (128 + pl.newf - 1) / pl.newf);
     for (;; m = (m + 1) / 2) {
+        if ((pl.orig & 1) && !(m & 1)) m += (m == 2) ? -1 : 1;
         pl.m = m;
         pl.orig_e = pl.orig * m;
         pl.new_e = pl.newf * m;
