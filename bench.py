@@ -124,6 +124,8 @@ class Workload:
         # whole-job audio per step: fixed total for the sweep, per-GPU work x N otherwise
         self.global_audio_s = (self.total_clips if key == "cfg5" else self.B * world) * self.L / self.sr
         self.e2e_clips = min(self.B, 1024)                              # clips of the shard the host-buffer leg streams per step
+        if key == "cfg2pcm" and world > 1:
+            self.e2e_clips = 256                                        # 5.3 KB of pinned PCM per audio-ms: keep N ranks' pinned buffers small
         self.out_per_clip = self.out_shape[1] * self.out_shape[2]
         self.bytes_per_clip = 4 * self.L + 4 * self.out_per_clip     # algorithmic: 4*(in) + 4*(out)
         if key == "cfg2pcm":                                          # the roofline kernel here is the resampler: PCM in + waveform out
