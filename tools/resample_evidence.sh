@@ -1,3 +1,5 @@
+#!/bin/bash
+# one gpurun call that refreshes the conditioning row's evidence: GPU tests, smoke, timings, bench line, ncu launch list and full capture
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -x -q -m gpu > gpurun_out/t_all.log 2>&1; echo "rc=$?" >> gpurun_out/t_all.log; tail -3 gpurun_out/t_all.log
 timeout 200 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
