@@ -17,9 +17,15 @@ the authoring container (see ``oracle/make_golden.py``):
   * kaldi fbank      : torchaudio.compliance.kaldi.fbank itself (the real code
                        the reference's CosyVoice frontend calls)
   * CosyVoice mel    : restated from matcha/utils/audio.py::mel_spectrogram with
-                       the parameters bound at /root/reference/greek_sft.yaml:55-63;
-                       single-source ("parity unpinned" for this one), cross-checked
-                       only against an independent numpy/fp64 restatement.
+                       the parameters bound at /root/reference/greek_sft.yaml:55-63 and
+                       pinned against TWO independent implementations of the same mel
+                       (torchaudio.transforms.MelSpectrogram, transformers.audio_utils.
+                       spectrogram; tests/test_oracle.py, arrays stored in
+                       tests/golden/cosy_rand.npz).  Matcha's `+ 1e-9` under the square
+                       root is the one constant neither twin has; its effect is bounded
+                       analytically in the test (<= 5e-6 relative on energies >= 1e-2).
+                       openai-whisper and matcha themselves are not importable here, so
+                       a1 / a2 are pinned to independent twins, not to the upstream files.
 """
 from .filters import slaney_mel_filters, kaldi_mel_banks  # noqa: F401
 from .featurizers import (  # noqa: F401

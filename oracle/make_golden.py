@@ -13,8 +13,12 @@ What pins what
   whisper_rand.npz  seeded noise / speech-like clips, 80 and 128 bins: HF torch path + HF numpy path + fp64 oracle
   kaldi_rand.npz    torchaudio.compliance.kaldi.fbank(num_mel_bins=80, dither=0, sample_frequency=16000)
                     itself (+ CMN) and the fp64 oracle
-  cosy_rand.npz     fp64 oracle and its numpy twin (no second implementation of matcha exists here:
-                    "restated, single-source")
+  cosy_rand.npz     fp64 oracle, its numpy twin, and TWO independent implementations of the same mel fed the
+                    reflect-padded signal: torchaudio.transforms.MelSpectrogram(24000, 1920, 1920, 480, 0, 8000,
+                    n_mels=80, power=1, center=False, norm="slaney", mel_scale="slaney") and
+                    transformers.audio_utils.spectrogram(power=1, mel_filters=mel_filter_bank(961, 80, 0, 8000,
+                    24000, "slaney", "slaney")); parameters = /root/reference/greek_sft.yaml:55-63.  They differ from
+                    matcha only by its `+ 1e-9` under the sqrt (bounded in tests/test_oracle.py)
 """
 import hashlib
 import os
@@ -131,6 +135,26 @@ def main():
         print(f"cosy {name}: |fp32 - fp64| {np.abs(o32 - o64).max():.2e}")
         d[f"{name}_fp32"] = o32
         d[f"{name}_fp64"] = o64.astype(np.float32)
+        # independent implementations (linear mel energies, float64 in, stored float32)
+        from transformers import audio_utils as au
+        xp = torch.nn.functional.pad(x.double().unsqueeze(1), (720, 720), mode="reflect").squeeze(1)
+        ms = torchaudio.transforms.MelSpectrogram(sample_rate=24000, n_fft=1920, win_length=1920, hop_length=480,
+                                                  f_min=0.0, f_max=8000.0, n_mels=80, power=1.0, center=False,
+                                                  norm="slaney", mel_scale="slaney").to(torch.float64)
+        mel_ta = ms(xp).numpy()
+        mf = au.mel_filter_bank(961, 80, 0.0, 8000.0, 24000, norm="slaney", mel_scale="slaney")
+        win = au.window_function(1920, "hann", periodic=True)
+        mel_hf = np.stack([au.spectrogram(xp[b].numpy(), win, frame_length=1920, hop_length=480, fft_length=1920,
+                                          power=1.0, center=False, mel_filters=mf, mel_floor=1e-30)
+                           for b in range(x.shape[0])])
+        M = np.exp(o64)
+        strong = M >= 1e-2
+        print(f"cosy {name}: torchaudio rel {(np.abs(mel_ta - M)[strong] / M[strong]).max():.2e}  "
+              f"transformers rel {(np.abs(mel_hf - M)[strong] / M[strong]).max():.2e}")
+        assert (np.abs(mel_ta - M)[strong] / M[strong]).max() <= 1e-4   # torchaudio builds its filter bank in float32
+        assert (np.abs(mel_hf - M)[strong] / M[strong]).max() <= 5e-6
+        d[f"{name}_torchaudio_mel"] = mel_ta.astype(np.float32)
+        d[f"{name}_hf_mel"] = mel_hf.astype(np.float32)
     np.savez_compressed(os.path.join(GOLD, "cosy_rand.npz"), **d)
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))

@@ -127,6 +127,56 @@ def test_cosy_fixture(golden, name):
         assert np.abs(numpy_ref.cosyvoice_mel_np(x[b]) - o64[b]).max() < 1e-9
 
 
+def _cosy_independent(x):
+    """Two implementations of the CosyVoice / Matcha mel that share no code with oracle.cosyvoice_mel:
+    torchaudio.transforms.MelSpectrogram and transformers.audio_utils.spectrogram, both fed the reflect-padded
+    signal ((n_fft - hop) / 2 = 720 each side) with the parameter block of /root/reference/greek_sft.yaml:55-63
+    (n_fft 1920, num_mels 80, sampling_rate 24000, hop_size 480, win_size 1920, fmin 0, fmax 8000, center False).
+    Neither has matcha's `+ 1e-9` under the square root -- bounded analytically by the caller."""
+    ta = pytest.importorskip("torchaudio")
+    au = pytest.importorskip("transformers.audio_utils")
+    x = torch.as_tensor(x, dtype=torch.float64)
+    xp = torch.nn.functional.pad(x.unsqueeze(1), (720, 720), mode="reflect").squeeze(1)
+    ms = ta.transforms.MelSpectrogram(sample_rate=24000, n_fft=1920, win_length=1920, hop_length=480, f_min=0.0,
+                                      f_max=8000.0, n_mels=80, power=1.0, center=False, norm="slaney",
+                                      mel_scale="slaney").to(torch.float64)
+    mel_ta = ms(xp).numpy()
+    mf = au.mel_filter_bank(961, 80, 0.0, 8000.0, 24000, norm="slaney", mel_scale="slaney")
+    win = au.window_function(1920, "hann", periodic=True)
+    mel_hf = np.stack([au.spectrogram(xp[b].numpy(), win, frame_length=1920, hop_length=480, fft_length=1920, power=1.0,
+                                      center=False, mel_filters=mf, mel_floor=1e-30) for b in range(x.shape[0])])
+    return mel_ta, mel_hf
+
+
+@pytest.mark.parametrize("name", ["noise", "speech"])
+def test_cosy_pinned_by_two_independent_implementations(golden, name):
+    """§8(c) a2: the Matcha mel is not importable here, so the restatement is pinned against torchaudio's
+    MelSpectrogram and transformers' spectrogram (linear mel energies, then ln(max(., 1e-5)) as matcha does).
+
+    The one constant neither twin carries is the 1e-9 under the square root: sqrt(m^2 + 1e-9) - m <= 5e-10 / m, so
+    on a mel energy whose contributing magnitudes are >= 1e-2 the relative effect is <= 5e-6 (and <= 5e-8 for
+    magnitudes >= 1e-1); it is bounded here as a relative tolerance on energies >= 1e-2 instead of being trusted."""
+    g = golden("cosy_rand.npz")
+    x = g[f"{name}_wave"]
+    o64 = oracle.cosyvoice_mel(x, dtype=torch.float64).numpy()
+    mel_ta, mel_hf = _cosy_independent(x)
+    assert mel_ta.shape == mel_hf.shape == o64.shape
+    M = np.exp(o64)
+    strong = M >= 1e-2
+    assert strong.mean() > 0.5            # the check must cover most of the fixture
+    # transformers' filter bank is bit-equal to the librosa formula (SURVEY A.1): only the 1e-9 term separates them
+    assert (np.abs(mel_hf - M)[strong] / M[strong]).max() <= 5e-6
+    # torchaudio builds its slaney filter bank in float32 (weights off by ~1e-6 absolute: 6e-6 relative on noise,
+    # 3e-5 on tones that sit on a filter's skirt)
+    assert (np.abs(mel_ta - M)[strong] / M[strong]).max() <= 1e-4
+    assert np.abs(np.log(np.maximum(mel_hf, 1e-5)) - o64)[strong].max() <= 1e-5
+    assert np.abs(np.log(np.maximum(mel_ta, 1e-5)) - o64)[strong].max() <= 1e-4
+    assert np.abs(np.log(np.maximum(mel_hf, 1e-5)) - o64).max() <= 1e-4       # weak bins: the 1e-9 term + floor
+    # and the stored arrays of the generating run (oracle/make_golden.py) say the same
+    assert np.abs(g[f"{name}_torchaudio_mel"] - mel_ta).max() <= 1e-6 * mel_ta.max()
+    assert np.abs(g[f"{name}_hf_mel"] - mel_hf).max() <= 1e-6 * mel_hf.max()
+
+
 def test_cosy_closed_forms():
     z = oracle.cosyvoice_mel(torch.zeros(1, 24000))
     assert z.shape == (1, 80, 50) and torch.allclose(z, torch.full_like(z, float(np.log(1e-5))))
