@@ -13,6 +13,7 @@ from .api import (  # noqa: F401
     fbank,
     whisper_log_mel_batch,
     cosy_mel_batch,
+    cosy_prompt_feat,
     kaldi_fbank_batch,
     whisper_log_mel_host,
     cosy_mel_host,

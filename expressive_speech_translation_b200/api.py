@@ -461,20 +461,39 @@ def resample(waveform, orig_freq: int, new_freq: int, lowpass_filter_width: int 
     return y.reshape(shape[:-1] + y.shape[-1:]).to(device=waveform.device, dtype=waveform.dtype)
 
 
-class Resample:
+class Resample(torch.nn.Module):
     """torchaudio.transforms.Resample as /root/reference/Backend/services/audio_processor.py:296-303 builds it
-    (orig_freq, new_freq, resampling_method, lowpass_filter_width, rolloff, beta); calling it resamples `(..., time)`."""
+    (orig_freq, new_freq, resampling_method, lowpass_filter_width, rolloff, beta); calling it resamples `(..., time)`.
+    A torch.nn.Module like the class it replaces (install() swaps it in process-wide), so `.to(device)`, `.eval()`,
+    nn.Sequential membership and `state_dict()` keep working; it owns no parameters or buffers -- the tap table is a
+    library-owned constant built once per (device, ratio, filter)."""
 
     def __init__(self, orig_freq: int = 16000, new_freq: int = 16000, resampling_method: str = "sinc_interp_hann",
                  lowpass_filter_width: int = 6, rolloff: float = 0.99, beta=None, *, dtype=None):
+        super().__init__()
         self.orig_freq, self.new_freq, self.resampling_method = orig_freq, new_freq, resampling_method
         self.lowpass_filter_width, self.rolloff, self.beta = lowpass_filter_width, rolloff, beta
+        self.gcd = int(np.gcd(int(orig_freq), int(new_freq)))
 
-    def __call__(self, waveform):
+    def forward(self, waveform):
         return resample(waveform, self.orig_freq, self.new_freq, self.lowpass_filter_width, self.rolloff,
                         self.resampling_method, self.beta)
 
-    forward = __call__
+    def extra_repr(self):
+        return f"orig_freq={self.orig_freq}, new_freq={self.new_freq}, resampling_method={self.resampling_method!r}"
+
+
+def cosy_prompt_feat(wave, token_len=None, lengths=None):
+    """CosyVoice frontend `_extract_speech_feat` + the 24 kHz trim of `frontend_zero_shot` (UPSTREAM cosyvoice/cli/
+    frontend.py, reached from /root/reference/Docker/cosyvoice_api.py:128): (B, L) 24 kHz prompt batch -> frame-major
+    (B, T, 80) ln-mel written in that layout by the kernel (no transpose pass); with `token_len` (speech tokens of
+    the prompt, 25 Hz against 50 Hz mel frames) T is cut to 2 * min(T // 2, token_len) like
+    `speech_feat[:, :2 * token_len]`.  Returns (features view, token_len actually used)."""
+    feat = cosy_mel_batch(wave, lengths=lengths, frame_major=True)
+    if token_len is None:
+        return feat, feat.shape[1] // 2
+    tl = min(feat.shape[1] // 2, int(token_len))
+    return feat[:, :2 * tl], tl
 
 
 # ----------------------------------------------------------------------------------------- install / uninstall
