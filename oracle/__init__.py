@@ -36,3 +36,15 @@ from .featurizers import (  # noqa: F401
     cosyvoice_num_frames,
     kaldi_num_frames,
 )
+
+
+# The ONE statement of the kaldi log-feature tolerance (tests/conftest.py::kaldi_check, __graft_entry__.smoke):
+# |f - f64| <= max(1e-4, KALDI_TOL_FACTOR x max|f32_reference - f64|) on the same input.  Why a factor at all: a
+# float32 FFT carries an error ~1e-7 of the FRAME's energy, so the log of a nearly empty mel bin is off by a few 1e-4
+# in the reference's own float32 path (tests/golden/kaldi_rand.npz: torchaudio fp32 vs fp64 = 4.5e-4 .. 5.3e-4).
+KALDI_TOL_FACTOR = 4.0
+
+
+def kaldi_log_tolerance(f32_reference, f64):
+    import numpy as _np
+    return max(1e-4, KALDI_TOL_FACTOR * float(_np.abs(_np.asarray(f32_reference, dtype=_np.float64) - _np.asarray(f64)).max()))
