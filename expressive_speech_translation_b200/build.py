@@ -12,6 +12,7 @@ DEPS = [
     os.path.join(HERE, "csrc", "b200feat_host.inl"),
     os.path.join(HERE, "csrc", "fe_common.h"),
     os.path.join(HERE, "csrc", "fe_whisper2.cuh"),
+    os.path.join(HERE, "csrc", "fe_whisper3.cuh"),
     os.path.join(HERE, "csrc", "fe_kaldi.cuh"),
     os.path.join(HERE, "csrc", "fe_cosy.cuh"),
     os.path.join(HERE, "csrc", "fe_resample.cuh"),

@@ -17,6 +17,7 @@
 #include "generated/fe_codelets.h"
 #include "generated/fe_tables.h"
 #include "fe_whisper2.cuh"
+#include "fe_whisper3.cuh"
 #include "fe_kaldi.cuh"
 #include "fe_cosy.cuh"
 #include "fe_resample.cuh"
@@ -296,6 +297,299 @@ __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2
     }
 }
 
+
+// =====================================================================================================
+// Whisper, Tensor-Memory formulation (fe_whisper3.cuh)
+// =====================================================================================================
+static __device__ __forceinline__ void fe_tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+static __device__ __forceinline__ void fe_tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// mbarrier wait that cannot hang the GPU: a protocol error traps (the launch fails) instead of spinning forever
+static __device__ __forceinline__ void fe_mbar_wait_bounded(unsigned addr, unsigned parity) {
+    unsigned ok = 0;
+#pragma unroll 1
+    for (int spin = 0; spin < (1 << 22); ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.b32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+static __device__ __forceinline__ void fe_mbar_expect_tx(unsigned addr, unsigned bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(addr), "r"(bytes) : "memory");
+}
+// one arrival per warp, after every lane's prior accesses (shared memory: __syncwarp + release; Tensor Memory: the
+// caller runs the tcgen05 wait + fence first)
+static __device__ __forceinline__ void fe_warp_arrive(unsigned addr, int lane) {
+    __syncwarp();
+    if (lane == 0) fe_mbar_arrive(addr);
+}
+
+struct FeW3Sync {          // shared-window addresses of the mbarriers
+    unsigned wfull, afull, bloaded;   // of this warp's team
+    unsigned pfull, pfree;
+};
+struct FeW3WaitBLoaded {   // phase A, before its first Tensor Memory store of a unit: B(previous unit) has loaded everything
+    unsigned addr, parity; bool on; bool* done;
+    __device__ __forceinline__ void operator()() const {
+        if (on && !*done) { fe_mbar_wait_bounded(addr, parity); fe_tc_fence_after(); *done = true; }
+    }
+};
+struct FeW3ArriveBLoaded { // phase B, after the loads of the member's LAST task of the unit have landed
+    unsigned addr; int lane; bool on;
+    __device__ __forceinline__ void operator()() const {
+        if (on) { fe_tc_fence_before(); fe_warp_arrive(addr, lane); }
+    }
+};
+struct FeW3WaitPFree {     // phase B, before its first store into P of a unit: M(previous unit) has read everything
+    unsigned addr, parity; bool on; bool* done;
+    __device__ __forceinline__ void operator()() const {
+        if (on && !*done) { fe_mbar_wait_bounded(addr, parity); *done = true; }
+    }
+};
+
+// W[q] of unit `t`: 34 bulk copies of one row each (lanes 0..31 a row, lanes 0, 1 also rows 32, 33) that complete on the
+// team's mbarrier; edge units are filled element-wise by this warp; a dead team's phase is completed by a bare arrival
+static __device__ __noinline__ void fe_w3_issue_w(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq,
+                                                  unsigned mb_wfull, int lane) {
+    typedef FeW3Cfg C;
+    const int mode = fe_w3_team_mode(p, t, q);
+    if (mode == 1) {
+        const float* src = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(wq);
+        if (lane == 0) fe_mbar_expect_tx(mb_wfull, C::ROWS * C::ROW_BYTES);
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int r = lane + 32 * k;
+            if (r < C::ROWS)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(dst + (unsigned)(r * C::PITCH * 4)), "l"(src + r * C::HOP), "n"(C::ROW_BYTES), "r"(mb_wfull) : "memory");
+        }
+    } else {
+        if (mode == 2) fe_w3_fill_manual(p, t, q, wq, lane);
+        fe_warp_arrive(mb_wfull, lane);
+    }
+}
+// the rows of the unit after next: into L2 now, so that the bulk copies issued one unit later hit there
+static __device__ __forceinline__ void fe_w3_prefetch_l2(const FeWhisper2Params& p, const FeW3Unit& t, int q, int lane) {
+    typedef FeW3Cfg C;
+    if (lane == 0 && fe_w3_team_mode(p, t, q) == 1) {
+        const float* src = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "n"(C::ROWS * C::ROW_BYTES) : "memory");
+    }
+}
+
+// Per unit `it` of this CTA every warp runs, in program order:
+//   A(it)   : wait WFULL(it); its phase-A tasks [first Tensor Memory store waits BLOADED(it-1)]; arrive AFULL(it)
+//   M(it-1) : wait PFULL(it-1); its share of the mel projection; arrive PFREE(it-1)
+//   B(it)   : wait AFULL(it) [member 1 then issues the copies for W(it+1): every A(it) task has read W];
+//             its phase-B tasks [last task's loads landed: arrive BLOADED(it); first store into P waits PFREE(it-1)];
+//             arrive PFULL(it)
+// A warp arrives on phase k of a barrier only after it has waited for phase k-1 of it (where it waits at all), so no
+// barrier can run two phases ahead of a waiter (parity waits would alias).
+template <int NMELS, bool OUT16>
+__global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhisper2Params p) {
+    typedef FeW3Cfg C;
+    extern __shared__ __align__(16) float sm[];
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int team = warp & 3, member = warp >> 2;
+    float* const wq = sm + C::OFF_W + team * C::WT;
+    float* const P = sm + C::OFF_P;
+    const unsigned mb0 = (unsigned)__cvta_generic_to_shared(sm + C::OFF_MBAR);
+    FeW3Sync sy;
+    sy.wfull = mb0 + 8u * team; sy.afull = mb0 + 8u * (4 + team); sy.bloaded = mb0 + 8u * (8 + team);
+    sy.pfull = mb0 + 8u * 12; sy.pfree = mb0 + 8u * 13;
+    unsigned* const tm_slot = reinterpret_cast<unsigned*>(sm + C::OFF_MBAR + 2 * C::NMBAR);
+    if (tid == 0) {
+        for (int q = 0; q < 4; ++q) {
+            fe_mbar_init(mb0 + 8u * q, 1);
+            fe_mbar_init(mb0 + 8u * (4 + q), C::MEMBERS);
+            fe_mbar_init(mb0 + 8u * (8 + q), C::MEMBERS);
+        }
+        fe_mbar_init(sy.pfull, C::NW);
+        fe_mbar_init(sy.pfree, C::NW);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    fe_w3_copy_tables<NMELS>(sm, tid, C::NT);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((unsigned)__cvta_generic_to_shared(tm_slot)), "n"(C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fe_tc_fence_before();
+    __syncthreads();
+    fe_tc_fence_after();
+    const unsigned tm_base = *tm_slot;
+    FeTm tm;
+    tm.base = tm_base + ((unsigned)(team * 32) << 16);
+
+    const int u0 = blockIdx.x, du = gridDim.x;
+    const int n_it = u0 < p.total_units ? (p.total_units - u0 + du - 1) / du : 0;
+    const int a1 = fe_w3_a_first(member), a2 = fe_w3_a_second(member);
+    const int b1 = fe_w3_b_first(member), b2 = fe_w3_b_second(member);
+    if (member == 1 && n_it > 0) {
+        const FeW3Unit t = fe_w3_unit(p, u0);
+        fe_w3_issue_w(p, t, team, wq, sy.wfull, lane);
+        if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + du), team, lane);
+    }
+    FeW3Unit prev;
+    prev.b = 0; prev.t0 = 0; prev.T = 0; prev.len = 0; prev.lp = 0;
+#pragma unroll 1
+    for (int it = 0; it <= n_it; ++it) {
+        const bool has = it < n_it;
+        const unsigned par = (unsigned)(it & 1), ppar = par ^ 1u;
+        FeW3Unit cur = prev;
+        bool live = false;
+        // ---- A(it)
+        if (has) {
+            cur = fe_w3_unit(p, u0 + it * du);
+            live = cur.t0 + C::FT * team < cur.T;
+            fe_mbar_wait_bounded(sy.wfull, par);
+            if (live) {
+                bool waited = false;
+                const FeW3WaitBLoaded pre{sy.bloaded, ppar, it > 0, &waited};
+#pragma unroll 1
+                for (int k = 0; k < 2; ++k) {           // one call site: the kernel is sensitive to its code size
+                    const int task = k == 0 ? a1 : a2;
+                    if (task >= 0) fe_w3_stage_a(wq, tm, lane, task, pre);
+                }
+                fe_tm_wait_st();
+            }
+            fe_tc_fence_before();
+            fe_warp_arrive(sy.afull, lane);
+        }
+        // ---- M(it - 1)
+        if (it > 0) {
+            fe_mbar_wait_bounded(sy.pfull, ppar);
+            if (prev.t0 < prev.T) {
+                const fe2 mm = fe_w3_phase_mel<NMELS, OUT16>(p, prev, sm, lane, warp);
+                int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
+                kmax = __reduce_max_sync(0xffffffffu, kmax);
+                kmin = __reduce_max_sync(0xffffffffu, kmin);
+                if (lane == 0) {
+                    int* uk = reinterpret_cast<int*>(p.unit_minmax + (u0 + (it - 1) * du));
+                    atomicMax(uk, kmax);                // [0] key of the unit's maximum, [1] key of -minimum
+                    atomicMax(uk + 1, kmin);
+                    atomicMax(p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : prev.b), kmax);
+                }
+            }
+            if (has) fe_warp_arrive(sy.pfree, lane);
+        }
+        // ---- B(it)
+        if (has) {
+            if (member > 0) {
+                fe_mbar_wait_bounded(sy.afull, par);
+                fe_tc_fence_after();
+                if (member == 1) {
+                    if (it + 1 < n_it) fe_w3_issue_w(p, fe_w3_unit(p, u0 + (it + 1) * du), team, wq, sy.wfull, lane);
+                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + (it + 2) * du), team, lane);
+                }
+                bool waited = false;
+                const FeW3WaitPFree pre{sy.pfree, ppar, it > 0, &waited};
+                if (live) {
+#pragma unroll 1
+                    for (int k = 0; k < 2; ++k)
+                        fe_w3_stage_b(P, tm, lane, team, k == 0 ? b1 : b2, FeW3ArriveBLoaded{sy.bloaded, lane, k == 1}, pre);
+                } else {
+                    FeW3ArriveBLoaded{sy.bloaded, lane, true}();
+                }
+            } else {
+                fe_tc_fence_before();
+                fe_warp_arrive(sy.bloaded, lane);
+            }
+            fe_warp_arrive(sy.pfull, lane);
+        }
+        prev = cur;
+    }
+    fe_tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm_base), "n"(C::TMEM_COLS) : "memory");
+}
+
+// Fix-up of the Tensor-Memory kernel's output: 128-frame units, (max, -min) published as order-preserving keys
+template <int NMELS, bool OUT16>
+__global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2Params p) {
+    typedef FeW3Cfg C;
+    __shared__ int list[256];
+    __shared__ int count;
+    const int2* __restrict__ ukeys = reinterpret_cast<const int2*>(p.unit_minmax);
+    for (int base = blockIdx.x * blockDim.x; base < p.total_units; base += gridDim.x * blockDim.x) {
+        if (threadIdx.x == 0) count = 0;
+        __syncthreads();
+        const int u = base + threadIdx.x;
+        if (u < p.total_units) {
+            const FeW3Unit t = fe_w3_unit(p, u);
+            const int n_in = (int)(p.T_out - t.t0 < C::UF ? p.T_out - t.t0 : C::UF);
+            const int n_live = t.T - t.t0;
+            const float umin = -fe_key_float(ukeys[u].y);
+            const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
+            if ((n_live > 0 && umin < thr) || n_live < n_in) list[atomicAdd(&count, 1)] = u;
+        }
+        __syncthreads();
+        const int n = count;
+        for (int j = 0; j < n; ++j) {
+            const int uu = list[j];
+            const FeW3Unit t = fe_w3_unit(p, uu);
+            const int n_in = (int)(p.T_out - t.t0 < C::UF ? p.T_out - t.t0 : C::UF);
+            int n_live = t.T - t.t0;
+            n_live = n_live < 0 ? 0 : (n_live > C::UF ? C::UF : n_live);
+            const float umin = -fe_key_float(ukeys[uu].y);
+            const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
+            const bool clampu = n_live > 0 && umin < thr;
+            constexpr int RSTEP = 256 / C::UF;
+            const int c = threadIdx.x % C::UF, m0 = threadIdx.x / C::UF;
+            if (c < n_in) {
+                if (OUT16) {
+                    __half* __restrict__ q0 = reinterpret_cast<__half*>(p.out) + (int64_t)t.b * p.out_batch_stride + t.t0 + c;
+                    const __half thr_h = __ushort_as_half(fe_f2h_rn(thr));
+                    if (c >= n_live) {
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = __ushort_as_half(0);
+                    } else if (clampu) {
+                        for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
+                            __half v[8];
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) {
+                                const int m = mb + k * RSTEP;
+                                v[k] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr_h;
+                            }
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) {
+                                const int m = mb + k * RSTEP;
+                                if (m < NMELS && __half2float(v[k]) < __half2float(thr_h)) q0[(int64_t)m * p.T_out] = thr_h;
+                            }
+                        }
+                    }
+                } else {
+                    float* __restrict__ q0 = reinterpret_cast<float*>(p.out) + (int64_t)t.b * p.out_batch_stride + t.t0 + c;
+                    if (c >= n_live) {
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = 0.0f;
+                    } else if (clampu) {
+                        for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
+                            float v[8];
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) {
+                                const int m = mb + k * RSTEP;
+                                v[k] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr;
+                            }
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) {
+                                const int m = mb + k * RSTEP;
+                                if (m < NMELS && v[k] < thr) q0[(int64_t)m * p.T_out] = thr;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
 static int tiles_per_cta_env(const char* name, int dflt) {
     const char* s = getenv(name);
     const int t = s ? atoi(s) : dflt;
@@ -405,6 +699,34 @@ static void launch_whisper2(int n_mels, bool out16, bool in16, unsigned grid, cu
     });
 }
 
+// the Tensor-Memory kernel: four instantiations (mel bins x output dtype); float32 input only
+template <class F>
+static int whisper3_for_each(F f) {
+    if (int rc = f(fe_whisper3_kernel<80, false>, 0)) return rc;
+    if (int rc = f(fe_whisper3_kernel<80, true>, 1)) return rc;
+    if (int rc = f(fe_whisper3_kernel<128, false>, 2)) return rc;
+    if (int rc = f(fe_whisper3_kernel<128, true>, 3)) return rc;
+    return 0;
+}
+static int whisper3_smem_attr() {
+    return whisper3_for_each([](void (*k)(const FeWhisper2Params), int) {
+        return cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW3Cfg::SMEM_BYTES) == cudaSuccess ? 0 : 1;
+    });
+}
+static void launch_whisper3(int n_mels, bool out16, unsigned grid, cudaStream_t st, const FeWhisper2Params& p) {
+    const int want = (n_mels == 128 ? 2 : 0) + (out16 ? 1 : 0);
+    whisper3_for_each([&](void (*k)(const FeWhisper2Params), int id) {
+        if (id == want) k<<<grid, FeW3Cfg::NT, FeW3Cfg::SMEM_BYTES, st>>>(p);
+        return 0;
+    });
+}
+// B200FEAT_WHISPER_KERNEL=2 forces the shared-memory frame-pair kernel (A/B timing, profiles/); default: the
+// Tensor-Memory kernel wherever it applies (float32 input, 16-byte aligned rows)
+static int whisper_kernel_choice() {
+    static const int v = [] { const char* s = getenv("B200FEAT_WHISPER_KERNEL"); return s ? atoi(s) : 3; }();
+    return v;
+}
+
 // =====================================================================================================
 // host side
 // =====================================================================================================
@@ -480,6 +802,7 @@ int check_device_arch() {
         state[dev] = (major == 10) ? 1 : -1;
         if (state[dev] == 1) {
             if (whisper2_smem_attr()) return fail(B200FEAT_ECUDA, "cudaFuncSetAttribute(fe_whisper2_kernel, max dynamic shared memory) failed");
+            if (whisper3_smem_attr()) return fail(B200FEAT_ECUDA, "cudaFuncSetAttribute(fe_whisper3_kernel, max dynamic shared memory) failed");
             FE_CUDA(cudaDeviceGetAttribute(&g_num_sms[dev < 64 ? dev : 0], cudaDevAttrMultiProcessorCount, dev));
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeKCfg::SMEM_BYTES));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
@@ -608,8 +931,35 @@ static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* len
     p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
     p.max_keys = reinterpret_cast<int32_t*>(workspace);
     p.unit_minmax = reinterpret_cast<float2*>(reinterpret_cast<char*>(workspace) + keys_bytes);
-    FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)keys_bytes, st));
     const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
+    const bool v3 = !in_s16 && p.vec_ok && whisper_kernel_choice() != 2;
+    if (v3) {
+        // Tensor-Memory kernel: 128-frame units; their (max, -min) keys are accumulated with atomicMax, so the unit
+        // table is initialised together with the per-clip keys
+        const int64_t units3 = (T_out + FeW3Cfg::UF - 1) / FeW3Cfg::UF;
+        p.units_per_clip = (int32_t)units3;
+        p.total_units = (int32_t)(B * units3);
+        FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)(keys_bytes + (int64_t)B * units3 * 8), st));
+        {
+            const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
+            ProfScope ps(st, 0);
+            launch_whisper3(n_mels, out16, grid, st, p);
+            g_launches++;
+        }
+        {
+            const int need = (p.total_units + 255) / 256;
+            const unsigned grid = (unsigned)(need < sms * 8 ? need : sms * 8);
+            ProfScope ps(st, 1);
+            if (n_mels == 80 && !out16) fe_whisper3_fixup_kernel<80, false><<<grid, 256, 0, st>>>(p);
+            else if (n_mels == 80) fe_whisper3_fixup_kernel<80, true><<<grid, 256, 0, st>>>(p);
+            else if (!out16) fe_whisper3_fixup_kernel<128, false><<<grid, 256, 0, st>>>(p);
+            else fe_whisper3_fixup_kernel<128, true><<<grid, 256, 0, st>>>(p);
+            g_launches++;
+        }
+        FE_CUDA(cudaGetLastError());
+        return 0;
+    }
+    FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)keys_bytes, st));
     {
         const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
         ProfScope ps(st, 0);

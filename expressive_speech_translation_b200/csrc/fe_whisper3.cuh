@@ -1,0 +1,457 @@
+// Whisper log-mel featurizer, third formulation: FFT scratch in Tensor Memory, waveform staged by the TMA engine.
+//
+// Replaces whisper/audio.py::log_mel_spectrogram (UPSTREAM openai-whisper; reached from
+// /root/reference/Backend/services/cascaded_backend.py:158, Backend/speech_translation_pipeline.py:140,
+// Backend/gtts_pipeline_fixed.py:64; same arithmetic as transformers/models/whisper/feature_extraction_whisper.py:135-164).
+//
+// Why a third kernel: the frame-pair kernel (fe_whisper2.cuh) is bound by the shared-memory pipe -- every 400-point
+// FFT makes two trips through shared memory (4.9 k wavefronts per 64 frames, 62 % of the LSU pipe at 36 % of the HBM
+// roofline).  Measured on B200 (profiles/r02_ubench_tmem_mma.txt): tcgen05.st / tcgen05.ld move 300-960 / 150-460
+// bytes per cycle and SM -- 2-7 x the shared-memory pipe -- and run beside it.  So the inter-pass buffer A moves to
+// Tensor Memory (420 of the 512 columns, lane = frame), the waveform is staged by cp.async.bulk (no loader warps), and
+// shared memory only carries the raw samples (read once per frame) and the power spectrum P.
+//
+//   CTA     : persistent, 16 warps.  Warp w belongs to team q = w % 4 (= its SM sub-partition = its TMEM lane quadrant)
+//             and is member j = w / 4 of it.  A CTA unit = 128 consecutive frames of one clip; team q owns frames
+//             t0 + 32 q + lane (ONE frame per lane).  Packed FP32 (FADD2 / FMUL2 / FFMA2) now pairs two independent
+//             sub-transforms of the SAME frame: two sub-sequences n2 in phase A, two rows k1 in phase B, two frames of
+//             two different teams in phase M.
+//   W[q]    : the team's samples, 34 rows of 160 (row r = samples of hop t0 + 32 q + r, starting 200 before the frame
+//             centre), row pitch 164 floats: a lane's frame starts at its own row, and LDS.128 with lane stride 164
+//             (= 4 x 41) is conflict-free.  Filled by 34 cp.async.bulk copies of 640 bytes (interior units) or by the
+//             issuing warp element-wise (reflect padding, ragged ends: 2 team-units of ~94 per 30-s clip).
+//   phase A : 5 tasks per team; task i loads x[20 n1 + 4 i .. + 3] (n1 = 0..19) with 20 LDS.128, windows them, runs two
+//             packed real 20-point DFTs (sub-sequences (4i, 4i+1) and (4i+2, 4i+3)), twiddles by W_400^(n2 k1) and stores
+//             Y[n2][k1] to Tensor Memory: 84 columns per task (tcgen05.st x4 / x8).
+//   phase B : 6 tasks per team; rows (k1, k1 + 1) = (1,2) (3,4) (5,6) (7,8) (9,10) as one packed complex 20-point DFT
+//             over n2 (80 tcgen05.ld x1: the load does the 2 x 2 transposition between the two packings for free),
+//             row k1 = 0 as a scalar real-input DFT; |X|^2 -> P[bin][4 * lane + (q ^ (lane >> 3))] (conflict-free
+//             32-bit stores; a lane's four teams sit in one 16-byte word).
+//   phase M : all 16 warps, chunk = warp: one LDS.128 per tap fetches the power of FOUR frames (one per team), two
+//             FFMA2 per tap; log10, (x + 4) / 4, four 32-byte-sector stores per filter and lane group, running min / max.
+//   sync    : five kinds of mbarrier, no CTA-wide barrier in the steady state (fe_whisper3_kernel in b200feat.cu).
+// Floor / clamp / ragged zero-fill: the same second, tiny fix-up kernel as before, on 128-frame units.
+#pragma once
+#include "fe_common.h"
+#include "fe_whisper2.cuh"
+
+struct FeW3Cfg {
+    static constexpr int N = 400, HOP = 160, PADL = 200, R = 20;
+    static constexpr int TEAMS = 4, MEMBERS = 4, NW = TEAMS * MEMBERS, NT = NW * 32;
+    static constexpr int FT = 32;                        // frames per team and unit
+    static constexpr int UF = TEAMS * FT;                // frames per CTA unit (128)
+    static constexpr int ROWS = 34, PITCH = 164;         // W[q]: rows of HOP samples, pitch in floats
+    static constexpr int WT = ROWS * PITCH;              // floats per team
+    static constexpr int ROW_BYTES = HOP * 4;
+    static constexpr int NBINS = 200;
+    static constexpr int ATASKS = 5, ACOLS = 84;         // Tensor Memory columns per phase-A task
+    static constexpr int TMEM_COLS = 512;                // allocation (power of two >= ATASKS * ACOLS = 420)
+    static constexpr int OFF_W = 0;
+    static constexpr int OFF_P = OFF_W + TEAMS * WT;                 // P[bin][UF]
+    static constexpr int OFF_MBAR = OFF_P + NBINS * UF;              // 14 mbarriers (8 bytes each) + the TMEM base slot
+    static constexpr int NMBAR = 14;
+    static constexpr int OFF_MDESC = OFF_MBAR + 2 * NMBAR + 4;       // mel descriptors (2 ints per filter, <= 128 filters)
+    static constexpr int OFF_MW = OFF_MDESC + 256;                   // padded taps
+    static constexpr int MW_MAX = 576;
+    static constexpr int SMEM_FLOATS = OFF_MW + MW_MAX;
+    static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
+    static_assert(OFF_P % 4 == 0 && OFF_MBAR % 2 == 0 && OFF_MDESC % 4 == 0 && OFF_MW % 4 == 0, "alignment of the carve-up");
+    static_assert(WT % 4 == 0 && PITCH % 4 == 0, "cp.async.bulk needs 16-byte aligned rows");
+    static_assert(SMEM_BYTES <= 232448, "more than 227 KB of shared memory");
+    static constexpr float LOG_SCALE = FeW2Cfg::LOG_SCALE;
+};
+
+// ---------------------------------------------------------------- Tensor Memory as per-lane scratch
+// Device: `base` = address of column 0 in the warp's own lane quadrant; every access is warp-wide (.sync.aligned), lane l
+// touching its own lane row.  Host emulation: `row` = the 512 columns of one (team, lane).
+struct FeTm {
+#if defined(__CUDACC__)
+    uint32_t base;
+#else
+    float* row;
+#endif
+};
+
+FE_HD FE_INLINE void fe_tm_st4(const FeTm& tm, int col, float a, float b, float c, float d) {
+#if defined(__CUDACC__)
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(tm.base + col), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+#else
+    tm.row[col] = a; tm.row[col + 1] = b; tm.row[col + 2] = c; tm.row[col + 3] = d;
+#endif
+}
+FE_HD FE_INLINE void fe_tm_st8(const FeTm& tm, int col, fe2 a, fe2 b, fe2 c, fe2 d) {
+#if defined(__CUDACC__)
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(tm.base + col), "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y), "f"(d.x), "f"(d.y) : "memory");
+#else
+    float* r = tm.row + col;
+    r[0] = a.x; r[1] = a.y; r[2] = b.x; r[3] = b.y; r[4] = c.x; r[5] = c.y; r[6] = d.x; r[7] = d.y;
+#endif
+}
+// asynchronous on the device: the value is defined only after fe_tm_wait_ld() AND fe_tm_tie() on it
+FE_HD FE_INLINE float fe_tm_ld1(const FeTm& tm, int col) {
+#if defined(__CUDACC__)
+    float v;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=f"(v) : "r"(tm.base + col) : "memory");
+    return v;
+#else
+    return tm.row[col];
+#endif
+}
+FE_HD FE_INLINE void fe_tm_wait_ld() {
+#if defined(__CUDACC__)
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#endif
+}
+FE_HD FE_INLINE void fe_tm_wait_st() {
+#if defined(__CUDACC__)
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+#endif
+}
+// ties a loaded register to the preceding wait: the compiler may not move a use of `v` above it
+FE_HD FE_INLINE void fe_tm_tie(float& v) {
+#if defined(__CUDACC__)
+    asm volatile("" : "+f"(v));
+#else
+    (void)v;
+#endif
+}
+FE_HD FE_INLINE void fe_tm_tie(fe2& v) { fe_tm_tie(v.x); fe_tm_tie(v.y); }
+
+// ---------------------------------------------------------------- units
+struct FeW3Unit {
+    int b;          // clip
+    int t0;         // first frame of the CTA unit
+    int T;          // frames of this clip (<= T_out)
+    int64_t len;    // valid samples
+    int64_t lp;     // len + padding
+};
+
+FE_HD FE_INLINE FeW3Unit fe_w3_unit(const FeWhisper2Params& p, int u) {
+    FeW3Unit t;
+    t.b = u / p.units_per_clip;
+    t.t0 = (u - t.b * p.units_per_clip) * FeW3Cfg::UF;
+    t.len = fe_clip_len(p.lengths, t.b, p.L);
+    t.lp = t.len + p.padding;
+    const int64_t T = t.lp / FeW3Cfg::HOP;
+    t.T = (int)(T < p.T_out ? T : p.T_out);
+    return t;
+}
+
+// how W[q] of a unit is filled: 0 nothing (no live frame), 1 bulk copies (every sample of the 34 rows lies inside the
+// clip and rows are 16-byte aligned in global memory), 2 element-wise (reflect / zero padding, ragged ends)
+FE_HD FE_INLINE int fe_w3_team_mode(const FeWhisper2Params& p, const FeW3Unit& t, int q) {
+    typedef FeW3Cfg C;
+    const int f0 = t.t0 + C::FT * q;
+    if (!(f0 < t.T)) return 0;
+    const int64_t g0 = (int64_t)f0 * C::HOP - C::PADL;
+    if (p.vec_ok && g0 >= 0 && g0 + (int64_t)C::ROWS * C::HOP <= t.len) return 1;
+    return 2;
+}
+
+// element-wise fill of one team's rows by ONE warp (edge units only)
+FE_HD FE_INLINE void fe_w3_fill_manual(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq, int lane) {
+    typedef FeW3Cfg C;
+    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
+    const int64_t g0 = ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+    constexpr int NB = 4;      // rows per batch: 20 independent loads per lane in flight
+#pragma unroll 1
+    for (int r0 = 0; r0 < C::ROWS; r0 += NB) {
+        float v[NB][5];
+#pragma unroll
+        for (int k = 0; k < NB; ++k)
+#pragma unroll
+            for (int j = 0; j < 5; ++j) {
+                const int r = r0 + k;
+                v[k][j] = r < C::ROWS ? fe_fetch_reflect(x, g0 + (int64_t)r * C::HOP + lane + 32 * j, t.len, t.lp) : 0.0f;
+            }
+#pragma unroll
+        for (int k = 0; k < NB; ++k)
+#pragma unroll
+            for (int j = 0; j < 5; ++j)
+                if (r0 + k < C::ROWS) wq[(r0 + k) * C::PITCH + lane + 32 * j] = v[k][j];
+    }
+}
+
+// host emulation of the bulk copies (the device issues cp.async.bulk, b200feat.cu)
+FE_HD FE_INLINE void fe_w3_fill_rows_host(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq) {
+    typedef FeW3Cfg C;
+    const float* x = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+    for (int r = 0; r < C::ROWS; ++r)
+        for (int c = 0; c < C::HOP; ++c) wq[r * C::PITCH + c] = x[r * C::HOP + c];
+}
+
+template <int NMELS>
+FE_HD FE_INLINE void fe_w3_copy_tables(float* sm, int tid, int nthreads) {
+    typedef FeW3Cfg C;
+    static_assert(FE_MELLOOP3_W80_NW <= C::MW_MAX && FE_MELLOOP3_W128_NW <= C::MW_MAX, "MW_MAX too small");
+    const int* __restrict__ desc = NMELS == 80 ? fe_melloop3_w80_desc : fe_melloop3_w128_desc;
+    const float* __restrict__ w = NMELS == 80 ? fe_melloop3_w80_w : fe_melloop3_w128_w;
+    const int nw = NMELS == 80 ? FE_MELLOOP3_W80_NW : FE_MELLOOP3_W128_NW;
+    int* d = reinterpret_cast<int*>(sm + C::OFF_MDESC);
+    for (int i = tid; i < 2 * NMELS; i += nthreads) d[i] = desc[i];
+    for (int i = tid; i < nw; i += nthreads) sm[C::OFF_MW + i] = w[i];
+}
+
+// ---------------------------------------------------------------- task maps
+// member -> phase-A tasks (two for member 0), phase-B tasks (pairs p = 0..4 = rows (2p+1, 2p+2); 5 = row 0), and the
+// share of the mel projection (generated/fe_tables.h: fe_melloop3_*_ranges, chunk = warp)
+FE_HD FE_INLINE int fe_w3_a_first(int member) { return member == 0 ? 0 : member + 1; }     // 0, 2, 3, 4
+FE_HD FE_INLINE int fe_w3_a_second(int member) { return member == 0 ? 1 : -1; }
+FE_HD FE_INLINE int fe_w3_b_first(int member) { return member == 1 ? 0 : (member == 2 ? 2 : (member == 3 ? 4 : -1)); }
+FE_HD FE_INLINE int fe_w3_b_second(int member) { return member == 1 ? 1 : (member == 2 ? 3 : (member == 3 ? 5 : -1)); }
+
+// ---------------------------------------------------------------- phase A
+// fe_w3_tab: per task 160 floats = window w[20 n1 + 4 i + c] as [n1][c] (80), then for k1 = 1..10 the twiddles
+// W_400^((4 i + c) k1) as [k1][wr_c0, wr_c1, wi_c0, wi_c1, wr_c2, wr_c3, wi_c2, wi_c3] (80)
+template <class PreStore>
+FE_HD FE_INLINE void fe_w3_stage_a(const float* wq, const FeTm& tm, int lane, int task, PreStore pre_store) {
+    typedef FeW3Cfg C;
+    // sample n = 20 n1 + 4 task + c of this lane's frame: row lane + n / 160, column n % 160; n / 160 == n1 / 8
+    const float4* __restrict__ s = reinterpret_cast<const float4*>(wq + C::PITCH * lane) + task;
+    const float4* __restrict__ tab = reinterpret_cast<const float4*>(fe_w3_tab + 160 * task);
+    fe2 x01[C::R], x23[C::R];
+#pragma unroll
+    for (int n1 = 0; n1 < C::R; ++n1) {
+        const float4 v = s[5 * n1 + n1 / 8];
+        const float4 w = tab[n1];
+        x01[n1] = fe_mul(fe_mk2(w.x, w.y), fe_mk2(v.x, v.y));
+        x23[n1] = fe_mul(fe_mk2(w.z, w.w), fe_mk2(v.z, v.w));
+    }
+    const int col = C::ACOLS * task;
+    fe2 yr[11], yi[11];
+    fe_rdft20_h11(x01, yr, yi);
+    pre_store();   // Tensor Memory may still be read by phase B of the previous unit
+    const fe2 y0 = yr[0];
+    {
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            fe2 re[2], im[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int k1 = 2 * j + 1 + h;
+                const float4 t = tab[20 + 2 * (k1 - 1)];
+                const fe2 wr = fe_mk2(t.x, t.y), wi = fe_mk2(t.z, t.w);
+                if (k1 < 10) {
+                    re[h] = fe_fma(fe_neg(wi), yi[k1], fe_mul(wr, yr[k1]));     // wr*yr - wi*yi
+                    im[h] = fe_fma(wi, yr[k1], fe_mul(wr, yi[k1]));             // wr*yi + wi*yr
+                } else {                                                        // k1 = 10: the real DFT's Nyquist row
+                    re[h] = fe_mul(wr, yr[10]);
+                    im[h] = fe_mul(wi, yr[10]);
+                }
+            }
+            fe_tm_st8(tm, col + 4 + 16 * j, re[0], im[0], re[1], im[1]);
+        }
+    }
+    fe_rdft20_h11(x23, yr, yi);
+    fe_tm_st4(tm, col, y0.x, y0.y, yr[0].x, yr[0].y);
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        fe2 re[2], im[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int k1 = 2 * j + 1 + h;
+            const float4 t = tab[20 + 2 * (k1 - 1) + 1];
+            const fe2 wr = fe_mk2(t.x, t.y), wi = fe_mk2(t.z, t.w);
+            if (k1 < 10) {
+                re[h] = fe_fma(fe_neg(wi), yi[k1], fe_mul(wr, yr[k1]));
+                im[h] = fe_fma(wi, yr[k1], fe_mul(wr, yi[k1]));
+            } else {
+                re[h] = fe_mul(wr, yr[10]);
+                im[h] = fe_mul(wi, yr[10]);
+            }
+        }
+        fe_tm_st8(tm, col + 4 + 16 * j + 8, re[0], im[0], re[1], im[1]);
+    }
+}
+
+// Tensor Memory column of Y[n2][k1]: task n2 / 4, sub-sequence c = n2 % 4
+FE_HD FE_INLINE constexpr int fe_w3_col_re(int n2, int k1) {
+    return FeW3Cfg::ACOLS * (n2 / 4) + (k1 == 0 ? (n2 % 4)
+                                                : 4 + 16 * ((k1 - 1) / 2) + 8 * ((n2 % 4) / 2) + 4 * ((k1 - 1) % 2) + ((n2 % 4) % 2));
+}
+FE_HD FE_INLINE constexpr int fe_w3_col_im(int n2, int k1) { return fe_w3_col_re(n2, k1) + 2; }
+
+// ---------------------------------------------------------------- phase B
+// P[bin][slot], slot = 4 * lane + (team ^ (lane >> 3)): 32 lanes of a warp hit 32 different banks, and the four teams'
+// values of one lane index share a 16-byte word (phase M reads it with one LDS.128)
+FE_HD FE_INLINE int fe_w3_p_slot(int lane, int team) { return 4 * lane + (team ^ (lane >> 3)); }
+
+// rows (k1a, k1b) = (2 pr + 1, 2 pr + 2): one packed complex 20-point DFT over n2
+template <class PostLoad, class PreStore>
+FE_HD FE_INLINE void fe_w3_stage_b_pair(float* P, const FeTm& tm, int lane, int team, int pr, PostLoad post_load, PreStore pre_store) {
+    typedef FeW3Cfg C;
+    FeTm t = tm;
+#if defined(__CUDACC__)
+    t.base += 16 * pr;
+#else
+    t.row += 16 * pr;
+#endif
+    fe2 xr[20], xi[20], yr[20], yi[20];
+#pragma unroll
+    for (int n2 = 0; n2 < 20; ++n2) {
+        const int c = fe_w3_col_re(n2, 1);
+        xr[n2].x = fe_tm_ld1(t, c); xi[n2].x = fe_tm_ld1(t, c + 2);
+        xr[n2].y = fe_tm_ld1(t, c + 4); xi[n2].y = fe_tm_ld1(t, c + 6);
+    }
+    fe_tm_wait_ld();
+#pragma unroll
+    for (int n2 = 0; n2 < 20; ++n2) { fe_tm_tie(xr[n2]); fe_tm_tie(xi[n2]); }
+    post_load();
+    fe_cdft20(xr, xi, yr, yi);
+    fe2 pw[20];
+#pragma unroll
+    for (int k = 0; k < 20; ++k) pw[k] = fe_fma(yr[k], yr[k], fe_mul(yi[k], yi[k]));
+    pre_store();
+    const int k1a = 2 * pr + 1;
+    float* __restrict__ pa = P + fe_w3_p_slot(lane, team) + C::UF * k1a;            // bins k1a + 20 j  (and k1a + 1 + 20 j)
+    float* __restrict__ pb = P + fe_w3_p_slot(lane, team) + C::UF * (C::R - k1a);   // bins (20 - k1a) + 20 j  (one lower for k1b)
+#pragma unroll
+    for (int j = 0; j < 10; ++j) {
+        pa[C::UF * C::R * j] = pw[j].x;
+        pa[C::UF * C::R * j + C::UF] = pw[j].y;
+        pb[C::UF * C::R * j] = pw[19 - j].x;
+    }
+    if (pr < 4) {      // k1b = 10 is its own mirror: bins 10 + 20 j were just written
+#pragma unroll
+        for (int j = 0; j < 10; ++j) pb[C::UF * C::R * j - C::UF] = pw[19 - j].y;
+    }
+}
+
+// row k1 = 0: real input, bins 20 j
+template <class PostLoad, class PreStore>
+FE_HD FE_INLINE void fe_w3_stage_b_k0(float* P, const FeTm& tm, int lane, int team, PostLoad post_load, PreStore pre_store) {
+    typedef FeW3Cfg C;
+    float xr[20], yr[10], yi[10];
+#pragma unroll
+    for (int n2 = 0; n2 < 20; ++n2) xr[n2] = fe_tm_ld1(tm, fe_w3_col_re(n2, 0));
+    fe_tm_wait_ld();
+#pragma unroll
+    for (int n2 = 0; n2 < 20; ++n2) fe_tm_tie(xr[n2]);
+    post_load();
+    yi[0] = 0.0f;
+    fe_rdft20_h10(xr, yr, yi);
+    pre_store();
+    float* __restrict__ pa = P + fe_w3_p_slot(lane, team);
+#pragma unroll
+    for (int j = 0; j < 10; ++j) pa[C::UF * C::R * j] = fmaf(yr[j], yr[j], yi[j] * yi[j]);
+}
+
+template <class PostLoad, class PreStore>
+FE_HD FE_INLINE void fe_w3_stage_b(float* P, const FeTm& tm, int lane, int team, int task, PostLoad post_load, PreStore pre_store) {
+    if (task < 5) fe_w3_stage_b_pair(P, tm, lane, team, task, post_load, pre_store);
+    else fe_w3_stage_b_k0(P, tm, lane, team, post_load, pre_store);
+}
+
+// ---------------------------------------------------------------- phase M
+// A lane handles the four frames t0 + 32 * (c ^ (lane >> 3)) + lane, c = 0..3 (component c of its 16-byte words of P).
+struct FeW3MelCtx {
+    const char* Pl;      // P + 16 * lane bytes
+    const char* wtab;    // padded weights (shared memory)
+    const int2* desc;    // descriptors (shared memory)
+    char* ob[4];         // out + clip offset + the frame of component c
+    unsigned rs;         // output row pitch in bytes
+    fe2 one01, one23;    // 1 for live frames, NaN for dead ones
+    bool lv[4];
+    float mn, mx;
+};
+
+template <int CAP, bool OUT16>
+FE_HD FE_INLINE void fe_w3_mel_class(FeW3MelCtx& c, int i0, int i1) {
+    typedef FeW3Cfg C;
+#pragma unroll(CAP <= 2 ? 2 : 1)
+    for (int i = i0; i < i1; ++i) {
+        const int2 d = c.desc[i];
+        const float4* __restrict__ P = reinterpret_cast<const float4*>(c.Pl + (size_t)(d.x & 0xffff) * (C::UF * 4));
+        float w[(CAP + 3) / 4 * 4];
+        if (CAP == 1) {
+            w[0] = *reinterpret_cast<const float*>(c.wtab + d.y);
+        } else if (CAP == 2) {
+            const float2 v = *reinterpret_cast<const float2*>(c.wtab + d.y);
+            w[0] = v.x; w[1] = v.y;
+        } else {
+            const float4* __restrict__ w4 = reinterpret_cast<const float4*>(c.wtab + d.y);
+#pragma unroll
+            for (int j = 0; j < (CAP + 3) / 4; ++j) {
+                const float4 v = w4[j];
+                w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
+            }
+        }
+        float4 v = P[0];
+        fe2 a01 = fe_mulc(w[0], fe_mk2(v.x, v.y)), a23 = fe_mulc(w[0], fe_mk2(v.z, v.w));
+#pragma unroll
+        for (int j = 1; j < CAP; ++j) {
+            v = P[(C::UF / 4) * j];
+            a01 = fe_fmac(w[j], fe_mk2(v.x, v.y), a01);
+            a23 = fe_fmac(w[j], fe_mk2(v.z, v.w), a23);
+        }
+        const fe2 y01 = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(a01.x), fe_w2_lg2(a01.y)), c.one01);   // (log10(v) + 4) / 4
+        const fe2 y23 = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(a23.x), fe_w2_lg2(a23.y)), c.one23);
+        const unsigned m = (unsigned)d.x >> 16;
+        if (OUT16) {   // min / max stay on the unrounded values: the fix-up decides in float32 like the reference
+            if (c.lv[0]) fe_stg_h<0>(fe_row_ptr(c.ob[0], c.rs, m), y01.x);
+            if (c.lv[1]) fe_stg_h<0>(fe_row_ptr(c.ob[1], c.rs, m), y01.y);
+            if (c.lv[2]) fe_stg_h<0>(fe_row_ptr(c.ob[2], c.rs, m), y23.x);
+            if (c.lv[3]) fe_stg_h<0>(fe_row_ptr(c.ob[3], c.rs, m), y23.y);
+        } else {
+            if (c.lv[0]) fe_stg<0>(fe_row_ptr(c.ob[0], c.rs, m), y01.x);
+            if (c.lv[1]) fe_stg<0>(fe_row_ptr(c.ob[1], c.rs, m), y01.y);
+            if (c.lv[2]) fe_stg<0>(fe_row_ptr(c.ob[2], c.rs, m), y23.x);
+            if (c.lv[3]) fe_stg<0>(fe_row_ptr(c.ob[3], c.rs, m), y23.y);
+        }
+        c.mx = fe_max3(c.mx, y01.x, y01.y); c.mx = fe_max3(c.mx, y23.x, y23.y);
+        c.mn = fe_min3(c.mn, y01.x, y01.y); c.mn = fe_min3(c.mn, y23.x, y23.y);
+    }
+}
+
+template <int NMELS> struct FeW3MelCaps;
+template <> struct FeW3MelCaps<80> {
+    static constexpr int N = FE_MELLOOP3_W80_NCLS;
+    static FE_HD constexpr int cap(int k) { constexpr int c[N] = {FE_MELLOOP3_W80_CAPS}; return c[k]; }
+};
+template <> struct FeW3MelCaps<128> {
+    static constexpr int N = FE_MELLOOP3_W128_NCLS;
+    static FE_HD constexpr int cap(int k) { constexpr int c[N] = {FE_MELLOOP3_W128_CAPS}; return c[k]; }
+};
+template <int NMELS, bool OUT16, int K, bool END = (K == FeW3MelCaps<NMELS>::N)>
+struct FeW3MelRun {
+    static FE_HD FE_INLINE void run(FeW3MelCtx& c, const int* r) {
+        fe_w3_mel_class<FeW3MelCaps<NMELS>::cap(K), OUT16>(c, r[K], r[K + 1]);
+        FeW3MelRun<NMELS, OUT16, K + 1>::run(c, r);
+    }
+};
+template <int NMELS, bool OUT16, int K>
+struct FeW3MelRun<NMELS, OUT16, K, true> {
+    static FE_HD FE_INLINE void run(FeW3MelCtx&, const int*) {}
+};
+
+// returns this thread's (min, max) over its live outputs
+template <int NMELS, bool OUT16>
+FE_HD FE_INLINE fe2 fe_w3_phase_mel(const FeWhisper2Params& p, const FeW3Unit& t, float* sm, int lane, int warp) {
+    typedef FeW3Cfg C;
+    constexpr int NCLS = FeW3MelCaps<NMELS>::N;
+    const int* __restrict__ ranges = (NMELS == 80 ? fe_melloop3_w80_ranges : fe_melloop3_w128_ranges) + (NCLS + 1) * warp;
+    FeW3MelCtx c;
+    c.Pl = reinterpret_cast<const char*>(sm + C::OFF_P + 4 * lane);
+    c.wtab = reinterpret_cast<const char*>(sm + C::OFF_MW);
+    c.desc = reinterpret_cast<const int2*>(sm + C::OFF_MDESC);
+    constexpr int ESZ = OUT16 ? 2 : 4;
+    c.rs = (unsigned)p.T_out * (unsigned)ESZ;     // row pitch in bytes; the host guarantees T_out < 2^24
+    union { unsigned u; float f; } qnan;
+    qnan.u = 0x7fc00000u;
+    float one[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int f = t.t0 + C::FT * (k ^ (lane >> 3)) + lane;
+        c.lv[k] = f < t.T;
+        c.ob[k] = reinterpret_cast<char*>(p.out) + ((int64_t)t.b * p.out_batch_stride + f) * ESZ;
+        one[k] = c.lv[k] ? 1.0f : qnan.f;
+    }
+    c.one01 = fe_mk2(one[0], one[1]); c.one23 = fe_mk2(one[2], one[3]);
+    c.mn = 3.0e38f; c.mx = -3.0e38f;
+    int r[NCLS + 1];
+#pragma unroll
+    for (int k = 0; k <= NCLS; ++k) r[k] = ranges[k];
+    FeW3MelRun<NMELS, OUT16, 0>::run(c, r);
+    return fe_mk2(c.mn, c.mx);
+}

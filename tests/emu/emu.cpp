@@ -8,6 +8,7 @@
 #include "generated/fe_codelets.h"
 #include "generated/fe_tables.h"
 #include "fe_whisper2.cuh"
+#include "fe_whisper3.cuh"
 
 // one unit at a time: loader threads, then the compute warps phase by phase (what the named barriers order on the GPU)
 template <int NMELS, bool OUT16>
@@ -44,6 +45,56 @@ static void run_whisper(const FeWhisper2Params& p) {
     }
 }
 
+// Tensor-Memory kernel (fe_whisper3.cuh): Tensor Memory is a plain [team][lane][512] array here; per CTA unit the teams'
+// rows are filled (bulk-copy path or element-wise path, as the kernel picks them), then phases A, B and M run in the
+// order the mbarriers enforce on the GPU.  unit_minmax holds (max key, -min key) like the kernel's atomics.
+template <int NMELS, bool OUT16>
+static void run_whisper3(const FeWhisper2Params& p) {
+    typedef FeW3Cfg C;
+    std::vector<float> sm(C::SMEM_FLOATS, 0.0f);
+    std::vector<float> tmem((size_t)C::TEAMS * 32 * C::TMEM_COLS, 0.0f);
+    fe_w3_copy_tables<NMELS>(sm.data(), 0, 1);
+    float* P = sm.data() + C::OFF_P;
+    for (int u = 0; u < p.total_units; ++u) {
+        const FeW3Unit t = fe_w3_unit(p, u);
+        float mn = 3.0e38f, mx = -3.0e38f;
+        if (t.t0 < t.T) {
+            for (int q = 0; q < C::TEAMS; ++q) {
+                float* wq = sm.data() + C::OFF_W + q * C::WT;
+                const int mode = fe_w3_team_mode(p, t, q);
+                if (mode == 1) fe_w3_fill_rows_host(p, t, q, wq);
+                else if (mode == 2) for (int l = 0; l < 32; ++l) fe_w3_fill_manual(p, t, q, wq, l);
+                if (mode == 0) continue;
+                for (int member = 0; member < C::MEMBERS; ++member)
+                    for (int k = 0; k < 2; ++k) {
+                        const int task = k == 0 ? fe_w3_a_first(member) : fe_w3_a_second(member);
+                        if (task < 0) continue;
+                        for (int l = 0; l < 32; ++l) {
+                            FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
+                            fe_w3_stage_a(wq, tm, l, task, FeNoHook());
+                        }
+                    }
+                for (int member = 1; member < C::MEMBERS; ++member)
+                    for (int k = 0; k < 2; ++k) {
+                        const int task = k == 0 ? fe_w3_b_first(member) : fe_w3_b_second(member);
+                        for (int l = 0; l < 32; ++l) {
+                            FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
+                            fe_w3_stage_b(P, tm, l, q, task, FeNoHook(), FeNoHook());
+                        }
+                    }
+            }
+            for (int w = 0; w < C::NW; ++w) for (int l = 0; l < 32; ++l) {
+                const fe2 mm = fe_w3_phase_mel<NMELS, OUT16>(p, t, sm.data(), l, w);
+                mn = std::min(mn, mm.x); mx = std::max(mx, mm.y);
+            }
+        }
+        int* uk = reinterpret_cast<int*>(p.unit_minmax + u);
+        uk[0] = fe_float_key(mx); uk[1] = fe_float_key(-mn);
+        int* slot = p.max_keys + (p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b);
+        *slot = std::max(*slot, fe_float_key(mx));
+    }
+}
+
 // float32 -> binary16 -> float32 (host form of fe_f2h_rn; the inverse is exact)
 static float half_bits_to_float(unsigned short h) {
     const unsigned sign = (unsigned)(h & 0x8000u) << 16, e = (h >> 10) & 31u, m = h & 1023u;
@@ -64,7 +115,7 @@ extern "C" void emu_f2h(const float* in, unsigned short* out, int64_t n) {
 }
 
 static int emu_whisper_any(const void* wave, bool in_s16, const int64_t* lengths, int B, int64_t L, int64_t stride,
-                           int n_mels, int padding, int norm_mode, void* out, bool out16, int64_t T_out) {
+                           int n_mels, int padding, int norm_mode, void* out, bool out16, int64_t T_out, int version = 2) {
     typedef FeW2Cfg C;
     std::vector<int> keys(B > 0 ? B : 1, FE_KEY_INIT);
     FeWhisper2Params p;
@@ -76,6 +127,15 @@ static int emu_whisper_any(const void* wave, bool in_s16, const int64_t* lengths
     p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
     std::vector<float2> mm((size_t)std::max(p.total_units, 1));
     p.max_keys = keys.data(); p.unit_minmax = mm.data();
+    if (version == 3) {
+        if (in_s16) return -2;
+        p.units_per_clip = (int)((T_out + FeW3Cfg::UF - 1) / FeW3Cfg::UF); p.total_units = B * p.units_per_clip;
+        if (n_mels == 80 && !out16) run_whisper3<80, false>(p);
+        else if (n_mels == 80) run_whisper3<80, true>(p);
+        else if (n_mels == 128 && !out16) run_whisper3<128, false>(p);
+        else if (n_mels == 128) run_whisper3<128, true>(p);
+        else return -1;
+    } else
     if (n_mels == 80 && !out16) run_whisper<80, false>(p);
     else if (n_mels == 80) run_whisper<80, true>(p);
     else if (n_mels == 128 && !out16) run_whisper<128, false>(p);
@@ -106,6 +166,11 @@ static int emu_whisper_any(const void* wave, bool in_s16, const int64_t* lengths
 extern "C" int emu_whisper(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
                            int n_mels, int padding, int norm_mode, float* out, int64_t T_out) {
     return emu_whisper_any(wave, false, lengths, B, L, stride, n_mels, padding, norm_mode, out, false, T_out);
+}
+
+extern "C" int emu_whisper3(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                            int n_mels, int padding, int norm_mode, void* out, int out16, int64_t T_out) {
+    return emu_whisper_any(wave, false, lengths, B, L, stride, n_mels, padding, norm_mode, out, out16 != 0, T_out, 3);
 }
 
 extern "C" int emu_whisper_f16(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,

@@ -46,6 +46,23 @@ def emu_whisper_f16(emu, x, n_mels=80, padding=0, norm=0, lengths=None):
     return out
 
 
+def emu_whisper3(emu, x, n_mels=80, padding=0, norm=0, lengths=None, f16=False, misalign=False):
+    """the Tensor-Memory kernel's phases (fe_whisper3.cuh); misalign=True shifts the waveform off 16-byte alignment,
+    which sends every unit down the element-wise loader path instead of the bulk-copy path"""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    if misalign:
+        buf = np.zeros(B * L + 1, dtype=np.float32)
+        buf[1:] = x.reshape(-1)
+        x = buf[1:].reshape(B, L)
+        assert x.ctypes.data % 16 != 0
+    T = (L + padding) // 160
+    out = np.full((B, n_mels, T), 7.0, dtype=np.float16 if f16 else np.float32)
+    keep, lp = _lens(lengths)
+    assert emu.emu_whisper3(x.ctypes.data_as(vp), lp, B, L, L, n_mels, padding, norm, out.ctypes.data_as(vp), int(f16), T) == 0
+    return out
+
+
 def emu_kaldi(emu, x, cmn=1, lengths=None):
     x = np.ascontiguousarray(x, dtype=np.float32)
     B, L = x.shape
@@ -185,3 +202,51 @@ def test_cosy_speech_zeros_ragged(emu):
     ref = oracle.cosyvoice_mel(y[1, :7777], dtype=torch.float64).numpy()
     assert np.abs(got[1, :, :ref.shape[1]] - ref).max() <= 1e-4
     assert not got[1, :, ref.shape[1]:].any()
+
+
+# ------------------------------------------------------------------------------------------------ Tensor-Memory kernel
+@pytest.mark.parametrize("B,L,nm,pad", [(2, 48000, 80, 0), (1, 12345, 128, 777), (3, 4000, 128, 0), (1, 8000, 80, 48000),
+                                        (1, 160 * 300 + 57, 128, 0)])
+def test_whisper3_noise(emu, B, L, nm, pad):
+    x = (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(L))).clamp(-1, 1)
+    ref = oracle.whisper_log_mel(x, nm, padding=pad, dtype=torch.float64, norm="per_clip").numpy()
+    got = emu_whisper3(emu, x.numpy(), nm, pad)
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= 1e-4
+    # the element-wise loader path (misaligned rows) must give the bulk-copy path's result bit for bit
+    assert np.array_equal(emu_whisper3(emu, x.numpy(), nm, pad, misalign=True), got)
+
+
+def test_whisper3_equals_frame_pair_kernel_closely(emu):
+    """both formulations compute the same 20 x 20 FFT with the same codelets and tables; only the mel summation
+    order differs (two chains per filter in the frame-pair kernel, one here)"""
+    x = (0.1 * torch.randn(2, 40000, generator=torch.Generator().manual_seed(1))).clamp(-1, 1).numpy()
+    for nm in (80, 128):
+        assert np.abs(emu_whisper3(emu, x, nm) - emu_whisper(emu, x, nm)).max() <= 2e-6
+
+
+def test_whisper3_speech_sine_zeros_percall_ragged(emu):
+    gen = torch.Generator().manual_seed(5)
+    x = speech_like(gen, 2, 48000, 16000)
+    ref = oracle.whisper_log_mel(x, 128, dtype=torch.float64, norm="per_clip").numpy()
+    assert np.abs(emu_whisper3(emu, x.numpy(), 128) - ref).max() <= 1e-4
+    ref = oracle.whisper_log_mel(x, 80, dtype=torch.float64, norm="per_call").numpy()
+    assert np.abs(emu_whisper3(emu, x.numpy(), 80, norm=1) - ref).max() <= 1e-4
+    t = np.arange(48000) / 16000.0
+    s = (0.5 * np.sin(2 * np.pi * 440 * t)).astype(np.float32)[None]
+    ref = oracle.whisper_log_mel(s, 80, dtype=torch.float64).numpy()
+    assert np.abs(emu_whisper3(emu, s, 80) - ref).max() <= 1e-4
+    z = emu_whisper3(emu, np.zeros((1, 16000), np.float32), 80)
+    assert np.abs(z + 1.5).max() < 1e-6
+    got = emu_whisper3(emu, x.numpy(), 80, lengths=[48000, 25003])
+    ref = oracle.whisper_log_mel(x[1, :25003], 80, dtype=torch.float64).numpy()
+    assert np.abs(got[1, :, :ref.shape[1]] - ref).max() <= 1e-4
+    assert not got[1, :, ref.shape[1]:].any()
+
+
+def test_whisper3_f16_output_is_the_rounded_f32_output(emu):
+    x = speech_like(torch.Generator().manual_seed(9), 2, 30000, 16000).numpy()
+    for nm in (80, 128):
+        f32 = emu_whisper3(emu, x, nm, lengths=[30000, 17001])
+        f16 = emu_whisper3(emu, x, nm, lengths=[30000, 17001], f16=True)
+        assert np.array_equal(f16, f32.astype(np.float16))

@@ -213,7 +213,7 @@ def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
     return "\n".join(out) + "\n"
 
 
-def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=None):
+def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=None, k0_scale=8):
     """tables for the rolled mel projection of the Whisper frame-pair kernel.  (The fully unrolled form does
     not fit the instruction cache next to the FFT codelets.)  Filters are sorted into classes by tap count
     (`caps`, ascending); a filter is zero-padded to the cap of its class, so each class is a branch-free loop:
@@ -263,7 +263,7 @@ def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=No
                 walign = 1 if cap == 1 else (2 if cap == 2 else 4)     # 32- / 64- / 128-bit weight loads
                 while len(wts) % walign:
                     wts.append(0.0)
-                desc += [8 * k0 | (m << 16), 4 * len(wts)]
+                desc += [k0_scale * k0 | (m << 16), 4 * len(wts)]
                 wts += w + [0.0] * ((-cap) % walign)
         ranges.append(len(desc) // 2)
     while len(wts) % 4:
@@ -372,6 +372,26 @@ def main():
         mel_share[w_] = 1.8
     tb.append(gen_melloop("fe_melloop_w80", w80, 12, (2, 3, 4, 6, 8, 11, 14), chunk_weight=mel_share))
     tb.append(gen_melloop("fe_melloop_w128", w128, 12, (1, 2, 3, 4, 6, 7, 9), chunk_weight=mel_share))
+    # Tensor-Memory Whisper kernel (fe_whisper3.cuh): per phase-A task i (sub-sequences n2 = 4 i + c, c = 0..3) 160 floats:
+    # window w[20 n1 + 4 i + c] as [n1][c], then W_400^(n2 k1), k1 = 1..10, as [k1][wr_c0 wr_c1 wi_c0 wi_c1 | wr_c2 wr_c3 wi_c2 wi_c3]
+    rows3 = np.zeros((5, 160), dtype=np.float64)
+    for i in range(5):
+        for n1 in range(20):
+            for c in range(4):
+                rows3[i, 4 * n1 + c] = w400[20 * n1 + 4 * i + c]
+        for k1 in range(1, 11):
+            for c in range(4):
+                wr, wi = tw[4 * i + c, k1]
+                base = 80 + 8 * (k1 - 1) + 4 * (c // 2)
+                rows3[i, base + (c % 2)] = wr
+                rows3[i, base + 2 + (c % 2)] = wi
+    tb.append("// Whisper (Tensor-Memory kernel) phase-A constants, see tools/gen_kernels.py")
+    tb.append(emit_array("fe_w3_tab", rows3).replace("FE_CONSTANT float fe_w3_tab", "FE_CONSTANT __attribute__((aligned(16))) float fe_w3_tab"))
+    # 16 mel chunks (chunk = warp = 4 * member + team): member 0 runs two phase-A tasks and no phase-B task, members 1, 2
+    # one A and two B tasks, member 3 one A, one B and the light row-0 task -- the mel shares level the totals
+    share3 = [w_ for w_ in (5.0, 1.4, 1.4, 4.2) for _ in range(4)]
+    tb.append(gen_melloop("fe_melloop3_w80", w80, 16, (2, 3, 4, 6, 8, 11, 14), chunk_weight=share3, k0_scale=1, emit_cost=22))
+    tb.append(gen_melloop("fe_melloop3_w128", w128, 16, (1, 2, 3, 4, 6, 7, 9), chunk_weight=share3, k0_scale=1, emit_cost=22))
     tb.append(gen_melrolled("fe_melroll_cosy", cz, 640))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
