@@ -301,18 +301,31 @@ __global__ void __launch_bounds__(256) fe_whisper2_fixup_kernel(const FeWhisper2
 // =====================================================================================================
 // Whisper, Tensor-Memory formulation (fe_whisper3.cuh)
 // =====================================================================================================
+#ifdef FE_W3_TRACE
+// debug build only (tools/trace_w3.py): clock64 stamps of CTA 0's warps at the phase boundaries
+#define FE_T3_UNITS 16
+#define FE_T3_EV 10
+__device__ long long fe_w3_trace_buf[FE_T3_UNITS * 16 * FE_T3_EV];
+#define FE_T3(iter, ev) do { if (blockIdx.x == 0 && (unsigned)(iter) < FE_T3_UNITS && lane == 0) \
+    fe_w3_trace_buf[((iter) * 16 + warp) * FE_T3_EV + (ev)] = clock64(); } while (0)
+#else
+#define FE_T3(iter, ev) do { } while (0)
+#endif
+
 static __device__ __forceinline__ void fe_tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 static __device__ __forceinline__ void fe_tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 // mbarrier wait that cannot hang the GPU: a protocol error traps (the launch fails) instead of spinning forever
 static __device__ __forceinline__ void fe_mbar_wait_bounded(unsigned addr, unsigned parity) {
     unsigned ok = 0;
 #pragma unroll 1
-    for (int spin = 0; spin < (1 << 22); ++spin) {
+    for (int spin = 0; spin < (1 << 20); ++spin) {
+        // the suspend-time hint lets the hardware park the warp instead of returning at once: without it the spin loops
+        // were 23 % of all executed instructions (profiles/r02_w3_v1)
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.b32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+            : "=r"(ok) : "r"(addr), "r"(parity), "r"(2000u) : "memory");
         if (ok) return;
     }
     __trap();
@@ -350,34 +363,42 @@ struct FeW3WaitPFree {     // phase B, before its first store into P of a unit: 
     }
 };
 
-// W[q] of unit `t`: 34 bulk copies of one row each (lanes 0..31 a row, lanes 0, 1 also rows 32, 33) that complete on the
-// team's mbarrier; edge units are filled element-wise by this warp; a dead team's phase is completed by a bare arrival
+// W[q] of unit `t`: the issuing warp first writes the edge rows element-wise, then lane 0 arms the team's mbarrier with
+// the byte count of the bulk rows and issues one 640-byte cp.async.bulk per row (they complete on that barrier); a dead
+// team's phase is completed by the bare arrival
 static __device__ __noinline__ void fe_w3_issue_w(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq,
                                                   unsigned mb_wfull, int lane) {
     typedef FeW3Cfg C;
-    const int mode = fe_w3_team_mode(p, t, q);
-    if (mode == 1) {
-        const float* src = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+    if (!fe_w3_team_live(t, q)) { fe_warp_arrive(mb_wfull, lane); return; }
+    const int64_t g0 = fe_w3_row0(t, q);
+    // the bulk rows are one contiguous run [r_lo, r_hi)
+    int r_lo = 0, r_hi = 0;
+    if (p.vec_ok & 1) {
+        const int64_t lo = g0 >= 0 ? 0 : (-g0 + C::HOP - 1) / C::HOP;
+        const int64_t hi = t.len - g0 < 0 ? 0 : (t.len - g0) / C::HOP;
+        r_lo = (int)(lo < C::ROWS ? lo : C::ROWS);
+        r_hi = (int)(hi < C::ROWS ? hi : C::ROWS);
+        if (r_hi < r_lo) r_hi = r_lo;
+    }
+    if (r_hi - r_lo < C::ROWS) fe_w3_fill_manual(p, t, q, wq, lane);
+    __syncwarp();
+    if (lane == 0) {
+        if (r_hi > r_lo) fe_mbar_expect_tx(mb_wfull, (unsigned)((r_hi - r_lo) * C::ROW_BYTES));
+        else fe_mbar_arrive(mb_wfull);
+        const float* src = p.wave + (int64_t)t.b * p.wave_stride + g0;
         const unsigned dst = (unsigned)__cvta_generic_to_shared(wq);
-        if (lane == 0) fe_mbar_expect_tx(mb_wfull, C::ROWS * C::ROW_BYTES);
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int r = lane + 32 * k;
-            if (r < C::ROWS)
-                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"(dst + (unsigned)(r * C::PITCH * 4)), "l"(src + r * C::HOP), "n"(C::ROW_BYTES), "r"(mb_wfull) : "memory");
-        }
-    } else {
-        if (mode == 2) fe_w3_fill_manual(p, t, q, wq, lane);
-        fe_warp_arrive(mb_wfull, lane);
+#pragma unroll 1
+        for (int r = r_lo; r < r_hi; ++r)
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(dst + (unsigned)(r * C::PITCH * 4)), "l"(src + r * C::HOP), "n"(C::ROW_BYTES), "r"(mb_wfull) : "memory");
     }
 }
 // the rows of the unit after next: into L2 now, so that the bulk copies issued one unit later hit there
 static __device__ __forceinline__ void fe_w3_prefetch_l2(const FeWhisper2Params& p, const FeW3Unit& t, int q, int lane) {
     typedef FeW3Cfg C;
-    if (lane == 0 && fe_w3_team_mode(p, t, q) == 1) {
-        const float* src = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+    const int64_t g0 = fe_w3_row0(t, q);
+    if (lane == 0 && fe_w3_team_live(t, q) && (p.vec_ok & 1) && g0 >= 0 && g0 + (int64_t)C::ROWS * C::HOP <= t.len) {
+        const float* src = p.wave + (int64_t)t.b * p.wave_stride + g0;
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "n"(C::ROWS * C::ROW_BYTES) : "memory");
     }
 }
@@ -430,42 +451,43 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
 
     const int u0 = blockIdx.x, du = gridDim.x;
     const int n_it = u0 < p.total_units ? (p.total_units - u0 + du - 1) / du : 0;
-    const int a1 = fe_w3_a_first(member), a2 = fe_w3_a_second(member);
-    const int b1 = fe_w3_b_first(member), b2 = fe_w3_b_second(member);
+    const int n_a = fe_w3_a_count(member), n_b = fe_w3_b_count(member);
     if (member == 1 && n_it > 0) {
         const FeW3Unit t = fe_w3_unit(p, u0);
         fe_w3_issue_w(p, t, team, wq, sy.wfull, lane);
         if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + du), team, lane);
     }
     FeW3Unit prev;
-    prev.b = 0; prev.t0 = 0; prev.T = 0; prev.len = 0; prev.lp = 0;
+    memset(&prev, 0, sizeof(prev));
 #pragma unroll 1
     for (int it = 0; it <= n_it; ++it) {
         const bool has = it < n_it;
         const unsigned par = (unsigned)(it & 1), ppar = par ^ 1u;
         FeW3Unit cur = prev;
         bool live = false;
+        FE_T3(it, 0);
         // ---- A(it)
         if (has) {
             cur = fe_w3_unit(p, u0 + it * du);
-            live = cur.t0 + C::FT * team < cur.T;
+            live = fe_w3_team_live(cur, team);
             fe_mbar_wait_bounded(sy.wfull, par);
+            FE_T3(it, 1);
             if (live) {
                 bool waited = false;
                 const FeW3WaitBLoaded pre{sy.bloaded, ppar, it > 0, &waited};
 #pragma unroll 1
-                for (int k = 0; k < 2; ++k) {           // one call site: the kernel is sensitive to its code size
-                    const int task = k == 0 ? a1 : a2;
-                    if (task >= 0) fe_w3_stage_a(wq, tm, lane, task, pre);
-                }
+                for (int k = 0; k < n_a; ++k)            // one call site: the kernel is sensitive to its code size
+                    fe_w3_stage_a(wq, tm, lane, fe_w3_a_hu(member, k), pre);
                 fe_tm_wait_st();
             }
             fe_tc_fence_before();
             fe_warp_arrive(sy.afull, lane);
         }
+        FE_T3(it, 2);
         // ---- M(it - 1)
         if (it > 0) {
             fe_mbar_wait_bounded(sy.pfull, ppar);
+            FE_T3(it, 3);
             if (prev.t0 < prev.T) {
                 const fe2 mm = fe_w3_phase_mel<NMELS, OUT16>(p, prev, sm, lane, warp);
                 int kmax = fe_float_key(mm.y), kmin = fe_float_key(-mm.x);
@@ -480,27 +502,26 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
             }
             if (has) fe_warp_arrive(sy.pfree, lane);
         }
+        FE_T3(it, 4);
         // ---- B(it)
         if (has) {
-            if (member > 0) {
-                fe_mbar_wait_bounded(sy.afull, par);
-                fe_tc_fence_after();
-                if (member == 1) {
-                    if (it + 1 < n_it) fe_w3_issue_w(p, fe_w3_unit(p, u0 + (it + 1) * du), team, wq, sy.wfull, lane);
-                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + (it + 2) * du), team, lane);
-                }
-                bool waited = false;
-                const FeW3WaitPFree pre{sy.pfree, ppar, it > 0, &waited};
-                if (live) {
+            fe_mbar_wait_bounded(sy.afull, par);
+            fe_tc_fence_after();
+            FE_T3(it, 5);
+            if (member == 1) {      // every A(it) task of the team has read W: refill it for the next unit
+                if (it + 1 < n_it) fe_w3_issue_w(p, fe_w3_unit(p, u0 + (it + 1) * du), team, wq, sy.wfull, lane);
+                if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + (it + 2) * du), team, lane);
+            }
+            bool waited = false;
+            const FeW3WaitPFree pre{sy.pfree, ppar, it > 0, &waited};
+            if (live) {
 #pragma unroll 1
-                    for (int k = 0; k < 2; ++k)
-                        fe_w3_stage_b(P, tm, lane, team, k == 0 ? b1 : b2, FeW3ArriveBLoaded{sy.bloaded, lane, k == 1}, pre);
-                } else {
-                    FeW3ArriveBLoaded{sy.bloaded, lane, true}();
+                for (int k = 0; k < n_b; ++k) {
+                    fe_w3_stage_b(P, tm, lane, team, fe_w3_b_task(member, k), FeW3ArriveBLoaded{sy.bloaded, lane, k == n_b - 1}, pre);
+                    FE_T3(it, 6 + k);
                 }
             } else {
-                fe_tc_fence_before();
-                fe_warp_arrive(sy.bloaded, lane);
+                FeW3ArriveBLoaded{sy.bloaded, lane, true}();
             }
             fe_warp_arrive(sy.pfull, lane);
         }
@@ -524,8 +545,8 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
         const int u = base + threadIdx.x;
         if (u < p.total_units) {
             const FeW3Unit t = fe_w3_unit(p, u);
-            const int n_in = (int)(p.T_out - t.t0 < C::UF ? p.T_out - t.t0 : C::UF);
-            const int n_live = t.T - t.t0;
+            const int n_in = t.n_in;
+            const int n_live = t.Ts - t.t0;
             const float umin = -fe_key_float(ukeys[u].y);
             const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
             if ((n_live > 0 && umin < thr) || n_live < n_in) list[atomicAdd(&count, 1)] = u;
@@ -535,9 +556,10 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
         for (int j = 0; j < n; ++j) {
             const int uu = list[j];
             const FeW3Unit t = fe_w3_unit(p, uu);
-            const int n_in = (int)(p.T_out - t.t0 < C::UF ? p.T_out - t.t0 : C::UF);
-            int n_live = t.T - t.t0;
-            n_live = n_live < 0 ? 0 : (n_live > C::UF ? C::UF : n_live);
+            const int n_in = t.n_in;
+            int n_live = t.Ts - t.t0;
+            n_live = n_live < 0 ? 0 : (n_live > n_in ? n_in : n_live);
+            const int64_t pitch = t.pitch;
             const float umin = -fe_key_float(ukeys[uu].y);
             const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
             const bool clampu = n_live > 0 && umin < thr;
@@ -545,41 +567,41 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
             const int c = threadIdx.x % C::UF, m0 = threadIdx.x / C::UF;
             if (c < n_in) {
                 if (OUT16) {
-                    __half* __restrict__ q0 = reinterpret_cast<__half*>(p.out) + (int64_t)t.b * p.out_batch_stride + t.t0 + c;
+                    __half* __restrict__ q0 = reinterpret_cast<__half*>(p.out) + t.o0 + c;
                     const __half thr_h = __ushort_as_half(fe_f2h_rn(thr));
                     if (c >= n_live) {
-                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = __ushort_as_half(0);
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * pitch] = __ushort_as_half(0);
                     } else if (clampu) {
                         for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
                             __half v[8];
 #pragma unroll
                             for (int k = 0; k < 8; ++k) {
                                 const int m = mb + k * RSTEP;
-                                v[k] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr_h;
+                                v[k] = m < NMELS ? q0[(int64_t)m * pitch] : thr_h;
                             }
 #pragma unroll
                             for (int k = 0; k < 8; ++k) {
                                 const int m = mb + k * RSTEP;
-                                if (m < NMELS && __half2float(v[k]) < __half2float(thr_h)) q0[(int64_t)m * p.T_out] = thr_h;
+                                if (m < NMELS && __half2float(v[k]) < __half2float(thr_h)) q0[(int64_t)m * pitch] = thr_h;
                             }
                         }
                     }
                 } else {
-                    float* __restrict__ q0 = reinterpret_cast<float*>(p.out) + (int64_t)t.b * p.out_batch_stride + t.t0 + c;
+                    float* __restrict__ q0 = reinterpret_cast<float*>(p.out) + t.o0 + c;
                     if (c >= n_live) {
-                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * p.T_out] = 0.0f;
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * pitch] = 0.0f;
                     } else if (clampu) {
                         for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
                             float v[8];
 #pragma unroll
                             for (int k = 0; k < 8; ++k) {
                                 const int m = mb + k * RSTEP;
-                                v[k] = m < NMELS ? q0[(int64_t)m * p.T_out] : thr;
+                                v[k] = m < NMELS ? q0[(int64_t)m * pitch] : thr;
                             }
 #pragma unroll
                             for (int k = 0; k < 8; ++k) {
                                 const int m = mb + k * RSTEP;
-                                if (m < NMELS && v[k] < thr) q0[(int64_t)m * p.T_out] = thr;
+                                if (m < NMELS && v[k] < thr) q0[(int64_t)m * pitch] = thr;
                             }
                         }
                     }
@@ -828,6 +850,11 @@ int b200feat_version(void) { return B200FEAT_VERSION; }
 const char* b200feat_last_error(void) { return g_err.c_str(); }
 int64_t b200feat_launch_count(void) { return g_launches.load(); }
 
+#ifdef FE_W3_TRACE
+int b200feat_debug_trace3(long long* host_out) {
+    return (int)cudaMemcpyFromSymbol(host_out, fe_w3_trace_buf, sizeof(long long) * FE_T3_UNITS * 16 * FE_T3_EV);
+}
+#endif
 #ifdef FE_W2_TRACE
 int b200feat_debug_trace(long long* host_out) {
     return (int)cudaMemcpyFromSymbol(host_out, fe_w2_trace_buf, sizeof(long long) * FE_TR_UNITS * 20 * FE_TR_EV);
@@ -929,10 +956,11 @@ static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* len
     p.units_per_clip = (int32_t)units;
     p.total_units = (int32_t)(B * units);
     p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
+    if (aligned16(out) && out_batch_stride % 4 == 0) p.vec_ok |= 2;     // 128-bit (float16: 64-bit) row stores possible
     p.max_keys = reinterpret_cast<int32_t*>(workspace);
     p.unit_minmax = reinterpret_cast<float2*>(reinterpret_cast<char*>(workspace) + keys_bytes);
     const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
-    const bool v3 = !in_s16 && p.vec_ok && whisper_kernel_choice() != 2;
+    const bool v3 = !in_s16 && (p.vec_ok & 1) && whisper_kernel_choice() != 2;
     if (v3) {
         // Tensor-Memory kernel: 128-frame units; their (max, -min) keys are accumulated with atomicMax, so the unit
         // table is initialised together with the per-clip keys

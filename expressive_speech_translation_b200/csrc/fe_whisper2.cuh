@@ -48,6 +48,10 @@ struct FeWhisper2Params {
     int32_t in_s16;            // 1: wave holds int16 PCM, the loader scales by 1/32768 (whisper.audio.load_audio's cast)
     int32_t* max_keys;         // (B) or (1): order-preserving keys of the running max of (x + 4) / 4
     float2* unit_minmax;       // (total_units): (min, max) of the unit's live outputs
+    // windowed output (Tensor-Memory kernel only; 0 = off): out is (B, n_windows, n_mels, win_frames), the encoder-ready
+    // segments whisper.transcribe cuts with mel[:, seek : seek + N_FRAMES] + pad_or_trim
+    int32_t win_frames;
+    int32_t n_windows;
 };
 
 struct FeW2Cfg {

@@ -79,6 +79,13 @@ FE_HD FE_INLINE void fe_tm_st4(const FeTm& tm, int col, float a, float b, float 
     tm.row[col] = a; tm.row[col + 1] = b; tm.row[col + 2] = c; tm.row[col + 3] = d;
 #endif
 }
+FE_HD FE_INLINE void fe_tm_st2(const FeTm& tm, int col, float a, float b) {
+#if defined(__CUDACC__)
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(tm.base + col), "f"(a), "f"(b) : "memory");
+#else
+    tm.row[col] = a; tm.row[col + 1] = b;
+#endif
+}
 FE_HD FE_INLINE void fe_tm_st8(const FeTm& tm, int col, fe2 a, fe2 b, fe2 c, fe2 d) {
 #if defined(__CUDACC__)
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
@@ -122,63 +129,104 @@ FE_HD FE_INLINE void fe_tm_tie(fe2& v) { fe_tm_tie(v.x); fe_tm_tie(v.y); }
 struct FeW3Unit {
     int b;          // clip
     int t0;         // first frame of the CTA unit
-    int T;          // frames of this clip (<= T_out)
+    int T;          // frames t0 <= f < T are computed and feed the clip's maximum
+    int Ts;         // frames f < Ts are stored (== T except for the tail unit of a windowed call)
+    int n_in;       // output columns the unit covers in `out` (0 for the tail unit)
+    int pitch;      // output row pitch in elements
+    int64_t o0;     // element offset in `out` of (mel row 0, frame t0)
     int64_t len;    // valid samples
     int64_t lp;     // len + padding
 };
 
+// Plain call: clip b has units_per_clip units of 128 frames, rows of T_out.  Windowed call (p.win_frames > 0): window w of
+// clip b is its own (n_mels, win_frames) block; a unit never straddles two windows (units per window =
+// ceil(win_frames / 128), the last one shorter), and one extra TAIL unit per clip computes the frames just behind the last
+// window without storing them: they can hold the clip's maximum (whisper takes the maximum over the whole padded mel).
 FE_HD FE_INLINE FeW3Unit fe_w3_unit(const FeWhisper2Params& p, int u) {
+    typedef FeW3Cfg C;
     FeW3Unit t;
     t.b = u / p.units_per_clip;
-    t.t0 = (u - t.b * p.units_per_clip) * FeW3Cfg::UF;
+    const int within = u - t.b * p.units_per_clip;
     t.len = fe_clip_len(p.lengths, t.b, p.L);
     t.lp = t.len + p.padding;
-    const int64_t T = t.lp / FeW3Cfg::HOP;
-    t.T = (int)(T < p.T_out ? T : p.T_out);
+    const int64_t Tc = t.lp / C::HOP;
+    if (p.win_frames > 0) {
+        const int W = p.win_frames, upw = (W + C::UF - 1) / C::UF;
+        if (within < p.n_windows * upw) {
+            const int w = within / upw, j = within - w * upw;
+            t.t0 = w * W + j * C::UF;
+            const int64_t wend = (int64_t)(w + 1) * W;
+            t.T = (int)(Tc < wend ? Tc : wend);
+            t.Ts = t.T;
+            t.n_in = W - j * C::UF < C::UF ? W - j * C::UF : C::UF;
+            t.pitch = W;
+            t.o0 = (int64_t)t.b * p.out_batch_stride + (int64_t)w * p.n_mels * W + j * C::UF;
+        } else {
+            t.t0 = p.n_windows * W;
+            const int64_t e = (int64_t)t.t0 + C::UF;
+            t.T = (int)(Tc < e ? Tc : e);
+            t.Ts = t.t0; t.n_in = 0; t.pitch = W; t.o0 = 0;
+        }
+        return t;
+    }
+    t.t0 = within * C::UF;
+    t.T = (int)(Tc < p.T_out ? Tc : p.T_out);
+    t.Ts = t.T;
+    t.n_in = (int)(p.T_out - t.t0 < C::UF ? p.T_out - t.t0 : C::UF);
+    t.pitch = (int)p.T_out;
+    t.o0 = (int64_t)t.b * p.out_batch_stride + t.t0;
     return t;
 }
 
-// how W[q] of a unit is filled: 0 nothing (no live frame), 1 bulk copies (every sample of the 34 rows lies inside the
-// clip and rows are 16-byte aligned in global memory), 2 element-wise (reflect / zero padding, ragged ends)
-FE_HD FE_INLINE int fe_w3_team_mode(const FeWhisper2Params& p, const FeW3Unit& t, int q) {
-    typedef FeW3Cfg C;
-    const int f0 = t.t0 + C::FT * q;
-    if (!(f0 < t.T)) return 0;
-    const int64_t g0 = (int64_t)f0 * C::HOP - C::PADL;
-    if (p.vec_ok && g0 >= 0 && g0 + (int64_t)C::ROWS * C::HOP <= t.len) return 1;
-    return 2;
+// How W[q] of a unit is filled, row by row: rows that lie completely inside the clip's samples (and are 16-byte
+// aligned in global memory) are bulk copies; the others -- reflect padding at the clip's edges, the zeros of `padding`
+// and of ragged ends -- are written element-wise by the issuing warp (2 + 3 rows of a 30-s clip's 3196).
+// fe_w3_team_live: the team has at least one frame to compute.
+FE_HD FE_INLINE bool fe_w3_team_live(const FeW3Unit& t, int q) { return t.t0 + FeW3Cfg::FT * q < t.T; }
+FE_HD FE_INLINE int64_t fe_w3_row0(const FeW3Unit& t, int q) {     // global sample index of row 0, column 0
+    return ((int64_t)t.t0 + FeW3Cfg::FT * q) * FeW3Cfg::HOP - FeW3Cfg::PADL;
+}
+FE_HD FE_INLINE bool fe_w3_row_bulk(const FeWhisper2Params& p, const FeW3Unit& t, int64_t g0, int r) {
+    const int64_t g = g0 + (int64_t)r * FeW3Cfg::HOP;
+    return (p.vec_ok & 1) && g >= 0 && g + FeW3Cfg::HOP <= t.len;
 }
 
-// element-wise fill of one team's rows by ONE warp (edge units only)
+// element-wise rows of one team, by ONE warp: four rows (20 independent loads per lane) in flight at a time
 FE_HD FE_INLINE void fe_w3_fill_manual(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq, int lane) {
     typedef FeW3Cfg C;
     const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
-    const int64_t g0 = ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
-    constexpr int NB = 4;      // rows per batch: 20 independent loads per lane in flight
+    const int64_t g0 = fe_w3_row0(t, q);
+    constexpr int NB = 4;
+    int rows[NB];
+    int n = 0;
 #pragma unroll 1
-    for (int r0 = 0; r0 < C::ROWS; r0 += NB) {
-        float v[NB][5];
+    for (int r = 0; r <= C::ROWS; ++r) {
+        if (r < C::ROWS && !fe_w3_row_bulk(p, t, g0, r)) rows[n++] = r;
+        if (n == NB || (r == C::ROWS && n > 0)) {
+            float v[NB][5];
 #pragma unroll
-        for (int k = 0; k < NB; ++k)
+            for (int k = 0; k < NB; ++k)
 #pragma unroll
-            for (int j = 0; j < 5; ++j) {
-                const int r = r0 + k;
-                v[k][j] = r < C::ROWS ? fe_fetch_reflect(x, g0 + (int64_t)r * C::HOP + lane + 32 * j, t.len, t.lp) : 0.0f;
-            }
+                for (int j = 0; j < 5; ++j)
+                    v[k][j] = k < n ? fe_fetch_reflect(x, g0 + (int64_t)rows[k] * C::HOP + lane + 32 * j, t.len, t.lp) : 0.0f;
 #pragma unroll
-        for (int k = 0; k < NB; ++k)
+            for (int k = 0; k < NB; ++k)
 #pragma unroll
-            for (int j = 0; j < 5; ++j)
-                if (r0 + k < C::ROWS) wq[(r0 + k) * C::PITCH + lane + 32 * j] = v[k][j];
+                for (int j = 0; j < 5; ++j)
+                    if (k < n) wq[rows[k] * C::PITCH + lane + 32 * j] = v[k][j];
+            n = 0;
+        }
     }
 }
 
 // host emulation of the bulk copies (the device issues cp.async.bulk, b200feat.cu)
 FE_HD FE_INLINE void fe_w3_fill_rows_host(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq) {
     typedef FeW3Cfg C;
-    const float* x = p.wave + (int64_t)t.b * p.wave_stride + ((int64_t)t.t0 + C::FT * q) * C::HOP - C::PADL;
+    const int64_t g0 = fe_w3_row0(t, q);
+    const float* x = p.wave + (int64_t)t.b * p.wave_stride;
     for (int r = 0; r < C::ROWS; ++r)
-        for (int c = 0; c < C::HOP; ++c) wq[r * C::PITCH + c] = x[r * C::HOP + c];
+        if (fe_w3_row_bulk(p, t, g0, r))
+            for (int c = 0; c < C::HOP; ++c) wq[r * C::PITCH + c] = x[g0 + (int64_t)r * C::HOP + c];
 }
 
 template <int NMELS>
@@ -194,75 +242,53 @@ FE_HD FE_INLINE void fe_w3_copy_tables(float* sm, int tid, int nthreads) {
 }
 
 // ---------------------------------------------------------------- task maps
-// member -> phase-A tasks (two for member 0), phase-B tasks (pairs p = 0..4 = rows (2p+1, 2p+2); 5 = row 0), and the
-// share of the mel projection (generated/fe_tables.h: fe_melloop3_*_ranges, chunk = warp)
-FE_HD FE_INLINE int fe_w3_a_first(int member) { return member == 0 ? 0 : member + 1; }     // 0, 2, 3, 4
-FE_HD FE_INLINE int fe_w3_a_second(int member) { return member == 0 ? 1 : -1; }
-FE_HD FE_INLINE int fe_w3_b_first(int member) { return member == 1 ? 0 : (member == 2 ? 2 : (member == 3 ? 4 : -1)); }
-FE_HD FE_INLINE int fe_w3_b_second(int member) { return member == 1 ? 1 : (member == 2 ? 3 : (member == 3 ? 5 : -1)); }
+// Phase A is cut into ten HALF-UNITS (hu = 0..9: sub-sequences n2 = 2 hu, 2 hu + 1, one packed real 20-point DFT);
+// phase B into six tasks (pairs p = 0..4 = rows (2p+1, 2p+2); 5 = row 0).  Members 0 and 1 run three half-units and
+// one light B task, members 2 and 3 two half-units and two pair tasks: A(u) is complete after 1.5 task times (not 2),
+// and the mel projection is shared equally (chunk = warp).
+FE_HD FE_INLINE int fe_w3_a_count(int member) { return member < 2 ? 3 : 2; }
+FE_HD FE_INLINE int fe_w3_a_hu(int member, int k) { return k < 2 ? 2 * member + k : 8 + member; }
+FE_HD FE_INLINE int fe_w3_b_count(int member) { return member < 2 ? 1 : 2; }
+FE_HD FE_INLINE int fe_w3_b_task(int member, int k) { return member == 0 ? 4 : (member == 1 ? 5 : 2 * (member - 2) + k); }
 
 // ---------------------------------------------------------------- phase A
-// fe_w3_tab: per task 160 floats = window w[20 n1 + 4 i + c] as [n1][c] (80), then for k1 = 1..10 the twiddles
-// W_400^((4 i + c) k1) as [k1][wr_c0, wr_c1, wi_c0, wi_c1, wr_c2, wr_c3, wi_c2, wi_c3] (80)
+// fe_w3_tab: per pair of half-units (i = hu / 2) 160 floats = window w[20 n1 + 4 i + c] as [n1][c] (80), then for
+// k1 = 1..10 the twiddles W_400^((4 i + c) k1) as [k1][wr_c0, wr_c1, wi_c0, wi_c1, wr_c2, wr_c3, wi_c2, wi_c3] (80);
+// half-unit hu uses c = 2 (hu % 2), 2 (hu % 2) + 1
 template <class PreStore>
-FE_HD FE_INLINE void fe_w3_stage_a(const float* wq, const FeTm& tm, int lane, int task, PreStore pre_store) {
+FE_HD FE_INLINE void fe_w3_stage_a(const float* wq, const FeTm& tm, int lane, int hu, PreStore pre_store) {
     typedef FeW3Cfg C;
-    // sample n = 20 n1 + 4 task + c of this lane's frame: row lane + n / 160, column n % 160; n / 160 == n1 / 8
-    const float4* __restrict__ s = reinterpret_cast<const float4*>(wq + C::PITCH * lane) + task;
-    const float4* __restrict__ tab = reinterpret_cast<const float4*>(fe_w3_tab + 160 * task);
-    fe2 x01[C::R], x23[C::R];
+    // sample n = 20 n1 + 2 hu + c of this lane's frame: row lane + n / 160, column n % 160; n / 160 == n1 / 8.
+    // 64-bit loads at lane stride 164 floats: two lanes per bank pair (the 16-byte row alignment the bulk copies need
+    // leaves no conflict-free pitch for them); same wavefronts as one conflict-free LDS.128 per two half-units
+    const fe2* __restrict__ s = reinterpret_cast<const fe2*>(wq + C::PITCH * lane) + hu;
+    const fe2* __restrict__ win = reinterpret_cast<const fe2*>(fe_w3_tab + 160 * (hu >> 1)) + (hu & 1);
+    const fe2* __restrict__ tw = reinterpret_cast<const fe2*>(fe_w3_tab + 160 * (hu >> 1)) + 40 + 2 * (hu & 1);
+    fe2 x[C::R];
 #pragma unroll
-    for (int n1 = 0; n1 < C::R; ++n1) {
-        const float4 v = s[5 * n1 + n1 / 8];
-        const float4 w = tab[n1];
-        x01[n1] = fe_mul(fe_mk2(w.x, w.y), fe_mk2(v.x, v.y));
-        x23[n1] = fe_mul(fe_mk2(w.z, w.w), fe_mk2(v.z, v.w));
-    }
-    const int col = C::ACOLS * task;
+    for (int n1 = 0; n1 < C::R; ++n1) x[n1] = fe_mul(win[2 * n1], s[10 * n1 + 2 * (n1 / 8)]);
     fe2 yr[11], yi[11];
-    fe_rdft20_h11(x01, yr, yi);
+    fe_rdft20_h11(x, yr, yi);
     pre_store();   // Tensor Memory may still be read by phase B of the previous unit
-    const fe2 y0 = yr[0];
-    {
-#pragma unroll
-        for (int j = 0; j < 5; ++j) {
-            fe2 re[2], im[2];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int k1 = 2 * j + 1 + h;
-                const float4 t = tab[20 + 2 * (k1 - 1)];
-                const fe2 wr = fe_mk2(t.x, t.y), wi = fe_mk2(t.z, t.w);
-                if (k1 < 10) {
-                    re[h] = fe_fma(fe_neg(wi), yi[k1], fe_mul(wr, yr[k1]));     // wr*yr - wi*yi
-                    im[h] = fe_fma(wi, yr[k1], fe_mul(wr, yi[k1]));             // wr*yi + wi*yr
-                } else {                                                        // k1 = 10: the real DFT's Nyquist row
-                    re[h] = fe_mul(wr, yr[10]);
-                    im[h] = fe_mul(wi, yr[10]);
-                }
-            }
-            fe_tm_st8(tm, col + 4 + 16 * j, re[0], im[0], re[1], im[1]);
-        }
-    }
-    fe_rdft20_h11(x23, yr, yi);
-    fe_tm_st4(tm, col, y0.x, y0.y, yr[0].x, yr[0].y);
+    const int col = C::ACOLS * (hu >> 1) + 8 * (hu & 1);
 #pragma unroll
     for (int j = 0; j < 5; ++j) {
         fe2 re[2], im[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int k1 = 2 * j + 1 + h;
-            const float4 t = tab[20 + 2 * (k1 - 1) + 1];
-            const fe2 wr = fe_mk2(t.x, t.y), wi = fe_mk2(t.z, t.w);
+            const fe2 wr = tw[4 * (k1 - 1)], wi = tw[4 * (k1 - 1) + 1];
             if (k1 < 10) {
-                re[h] = fe_fma(fe_neg(wi), yi[k1], fe_mul(wr, yr[k1]));
-                im[h] = fe_fma(wi, yr[k1], fe_mul(wr, yi[k1]));
-            } else {
+                re[h] = fe_fma(fe_neg(wi), yi[k1], fe_mul(wr, yr[k1]));     // wr*yr - wi*yi
+                im[h] = fe_fma(wi, yr[k1], fe_mul(wr, yi[k1]));             // wr*yi + wi*yr
+            } else {                                                        // k1 = 10: the real DFT's Nyquist row
                 re[h] = fe_mul(wr, yr[10]);
                 im[h] = fe_mul(wi, yr[10]);
             }
         }
-        fe_tm_st8(tm, col + 4 + 16 * j + 8, re[0], im[0], re[1], im[1]);
+        fe_tm_st8(tm, col + 4 + 16 * j, re[0], im[0], re[1], im[1]);
     }
+    fe_tm_st2(tm, C::ACOLS * (hu >> 1) + 2 * (hu & 1), yr[0].x, yr[0].y);
 }
 
 // Tensor Memory column of Y[n2][k1]: task n2 / 4, sub-sequence c = n2 % 4
@@ -273,9 +299,9 @@ FE_HD FE_INLINE constexpr int fe_w3_col_re(int n2, int k1) {
 FE_HD FE_INLINE constexpr int fe_w3_col_im(int n2, int k1) { return fe_w3_col_re(n2, k1) + 2; }
 
 // ---------------------------------------------------------------- phase B
-// P[bin][slot], slot = 4 * lane + (team ^ (lane >> 3)): 32 lanes of a warp hit 32 different banks, and the four teams'
-// values of one lane index share a 16-byte word (phase M reads it with one LDS.128)
-FE_HD FE_INLINE int fe_w3_p_slot(int lane, int team) { return 4 * lane + (team ^ (lane >> 3)); }
+// P[bin][frame of the unit], frame = 32 * team + lane: a warp's 32-bit stores are conflict-free, and phase M reads four
+// CONSECUTIVE frames with one LDS.128
+FE_HD FE_INLINE int fe_w3_p_slot(int lane, int team) { return FeW3Cfg::FT * team + lane; }
 
 // rows (k1a, k1b) = (2 pr + 1, 2 pr + 2): one packed complex 20-point DFT over n2
 template <class PostLoad, class PreStore>
@@ -344,25 +370,48 @@ FE_HD FE_INLINE void fe_w3_stage_b(float* P, const FeTm& tm, int lane, int team,
 }
 
 // ---------------------------------------------------------------- phase M
-// A lane handles the four frames t0 + 32 * (c ^ (lane >> 3)) + lane, c = 0..3 (component c of its 16-byte words of P).
+// A lane handles the four consecutive frames t0 + 4 * lane + c, c = 0..3 (one 16-byte word of every P row): one LDS.128
+// and two FFMA2 per tap, and -- when the whole unit is stored and rows are 16-byte aligned (VEC) -- ONE 128-bit store
+// per filter (a warp writes 512 contiguous bytes of the mel row).
 struct FeW3MelCtx {
     const char* Pl;      // P + 16 * lane bytes
     const char* wtab;    // padded weights (shared memory)
     const int2* desc;    // descriptors (shared memory)
-    char* ob[4];         // out + clip offset + the frame of component c
+    char* ob;            // out + offset of (mel row 0, frame t0 + 4 * lane)
     unsigned rs;         // output row pitch in bytes
     fe2 one01, one23;    // 1 for live frames, NaN for dead ones
-    bool lv[4];
+    bool lv[4];          // frame is stored (scalar path)
     float mn, mx;
 };
 
-template <int CAP, bool OUT16>
+template <int BYTE_OFF>
+FE_HD FE_INLINE void fe_stg_v4(char* q, fe2 a, fe2 b) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.v4.f32 [%0+%1], {%2, %3, %4, %5};" ::"l"(q), "n"(BYTE_OFF), "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+#else
+    float* o = reinterpret_cast<float*>(q + BYTE_OFF);
+    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+#endif
+}
+template <int BYTE_OFF>
+FE_HD FE_INLINE void fe_stg_h4(char* q, fe2 a, fe2 b) {
+    const unsigned lo = (unsigned)fe_f2h_rn(a.x) | ((unsigned)fe_f2h_rn(a.y) << 16);
+    const unsigned hi = (unsigned)fe_f2h_rn(b.x) | ((unsigned)fe_f2h_rn(b.y) << 16);
+#if defined(__CUDA_ARCH__)
+    asm volatile("st.global.v2.b32 [%0+%1], {%2, %3};" ::"l"(q), "n"(BYTE_OFF), "r"(lo), "r"(hi));
+#else
+    unsigned* o = reinterpret_cast<unsigned*>(q + BYTE_OFF);
+    o[0] = lo; o[1] = hi;
+#endif
+}
+
+template <int CAP, bool OUT16, bool VEC>
 FE_HD FE_INLINE void fe_w3_mel_class(FeW3MelCtx& c, int i0, int i1) {
     typedef FeW3Cfg C;
 #pragma unroll(CAP <= 2 ? 2 : 1)
     for (int i = i0; i < i1; ++i) {
-        const int2 d = c.desc[i];
-        const float4* __restrict__ P = reinterpret_cast<const float4*>(c.Pl + (size_t)(d.x & 0xffff) * (C::UF * 4));
+        const int2 d = c.desc[i];      // d.x = 512 * k0 | mel row, d.y = byte offset of the weights
+        const float4* __restrict__ P = reinterpret_cast<const float4*>(c.Pl + (d.x & ~0x1ff));
         float w[(CAP + 3) / 4 * 4];
         if (CAP == 1) {
             w[0] = *reinterpret_cast<const float*>(c.wtab + d.y);
@@ -387,17 +436,20 @@ FE_HD FE_INLINE void fe_w3_mel_class(FeW3MelCtx& c, int i0, int i1) {
         }
         const fe2 y01 = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(a01.x), fe_w2_lg2(a01.y)), c.one01);   // (log10(v) + 4) / 4
         const fe2 y23 = fe_fmac(C::LOG_SCALE, fe_mk2(fe_w2_lg2(a23.x), fe_w2_lg2(a23.y)), c.one23);
-        const unsigned m = (unsigned)d.x >> 16;
-        if (OUT16) {   // min / max stay on the unrounded values: the fix-up decides in float32 like the reference
-            if (c.lv[0]) fe_stg_h<0>(fe_row_ptr(c.ob[0], c.rs, m), y01.x);
-            if (c.lv[1]) fe_stg_h<0>(fe_row_ptr(c.ob[1], c.rs, m), y01.y);
-            if (c.lv[2]) fe_stg_h<0>(fe_row_ptr(c.ob[2], c.rs, m), y23.x);
-            if (c.lv[3]) fe_stg_h<0>(fe_row_ptr(c.ob[3], c.rs, m), y23.y);
+        char* o = fe_row_ptr(c.ob, c.rs, (unsigned)d.x & 0x1ffu);
+        if (VEC) {     // min / max below stay on the unrounded values: the fix-up decides in float32 like the reference
+            if (OUT16) fe_stg_h4<0>(o, y01, y23);
+            else fe_stg_v4<0>(o, y01, y23);
+        } else if (OUT16) {
+            if (c.lv[0]) fe_stg_h<0>(o, y01.x);
+            if (c.lv[1]) fe_stg_h<2>(o, y01.y);
+            if (c.lv[2]) fe_stg_h<4>(o, y23.x);
+            if (c.lv[3]) fe_stg_h<6>(o, y23.y);
         } else {
-            if (c.lv[0]) fe_stg<0>(fe_row_ptr(c.ob[0], c.rs, m), y01.x);
-            if (c.lv[1]) fe_stg<0>(fe_row_ptr(c.ob[1], c.rs, m), y01.y);
-            if (c.lv[2]) fe_stg<0>(fe_row_ptr(c.ob[2], c.rs, m), y23.x);
-            if (c.lv[3]) fe_stg<0>(fe_row_ptr(c.ob[3], c.rs, m), y23.y);
+            if (c.lv[0]) fe_stg<0>(o, y01.x);
+            if (c.lv[1]) fe_stg<4>(o, y01.y);
+            if (c.lv[2]) fe_stg<8>(o, y23.x);
+            if (c.lv[3]) fe_stg<12>(o, y23.y);
         }
         c.mx = fe_max3(c.mx, y01.x, y01.y); c.mx = fe_max3(c.mx, y23.x, y23.y);
         c.mn = fe_min3(c.mn, y01.x, y01.y); c.mn = fe_min3(c.mn, y23.x, y23.y);
@@ -413,15 +465,15 @@ template <> struct FeW3MelCaps<128> {
     static constexpr int N = FE_MELLOOP3_W128_NCLS;
     static FE_HD constexpr int cap(int k) { constexpr int c[N] = {FE_MELLOOP3_W128_CAPS}; return c[k]; }
 };
-template <int NMELS, bool OUT16, int K, bool END = (K == FeW3MelCaps<NMELS>::N)>
+template <int NMELS, bool OUT16, bool VEC, int K, bool END = (K == FeW3MelCaps<NMELS>::N)>
 struct FeW3MelRun {
     static FE_HD FE_INLINE void run(FeW3MelCtx& c, const int* r) {
-        fe_w3_mel_class<FeW3MelCaps<NMELS>::cap(K), OUT16>(c, r[K], r[K + 1]);
-        FeW3MelRun<NMELS, OUT16, K + 1>::run(c, r);
+        fe_w3_mel_class<FeW3MelCaps<NMELS>::cap(K), OUT16, VEC>(c, r[K], r[K + 1]);
+        FeW3MelRun<NMELS, OUT16, VEC, K + 1>::run(c, r);
     }
 };
-template <int NMELS, bool OUT16, int K>
-struct FeW3MelRun<NMELS, OUT16, K, true> {
+template <int NMELS, bool OUT16, bool VEC, int K>
+struct FeW3MelRun<NMELS, OUT16, VEC, K, true> {
     static FE_HD FE_INLINE void run(FeW3MelCtx&, const int*) {}
 };
 
@@ -436,22 +488,25 @@ FE_HD FE_INLINE fe2 fe_w3_phase_mel(const FeWhisper2Params& p, const FeW3Unit& t
     c.wtab = reinterpret_cast<const char*>(sm + C::OFF_MW);
     c.desc = reinterpret_cast<const int2*>(sm + C::OFF_MDESC);
     constexpr int ESZ = OUT16 ? 2 : 4;
-    c.rs = (unsigned)p.T_out * (unsigned)ESZ;     // row pitch in bytes; the host guarantees T_out < 2^24
+    c.rs = (unsigned)t.pitch * (unsigned)ESZ;     // row pitch in bytes; the host guarantees pitch < 2^24
     union { unsigned u; float f; } qnan;
     qnan.u = 0x7fc00000u;
     float one[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const int f = t.t0 + C::FT * (k ^ (lane >> 3)) + lane;
-        c.lv[k] = f < t.T;
-        c.ob[k] = reinterpret_cast<char*>(p.out) + ((int64_t)t.b * p.out_batch_stride + f) * ESZ;
-        one[k] = c.lv[k] ? 1.0f : qnan.f;
+        const int f = t.t0 + 4 * lane + k;
+        c.lv[k] = f < t.Ts;
+        one[k] = f < t.T ? 1.0f : qnan.f;      // dead frames carry NaN through min / max
     }
+    c.ob = reinterpret_cast<char*>(p.out) + (t.o0 + 4 * lane) * ESZ;
     c.one01 = fe_mk2(one[0], one[1]); c.one23 = fe_mk2(one[2], one[3]);
     c.mn = 3.0e38f; c.mx = -3.0e38f;
     int r[NCLS + 1];
 #pragma unroll
     for (int k = 0; k <= NCLS; ++k) r[k] = ranges[k];
-    FeW3MelRun<NMELS, OUT16, 0>::run(c, r);
+    // whole unit stored and 16-byte (float16: 8-byte) aligned rows: one vector store per filter
+    const bool vec = t.Ts - t.t0 >= C::UF && (p.vec_ok & 2) != 0 && (t.pitch & 3) == 0 && (t.o0 & 3) == 0;
+    if (vec) FeW3MelRun<NMELS, OUT16, true, 0>::run(c, r);
+    else FeW3MelRun<NMELS, OUT16, false, 0>::run(c, r);
     return fe_mk2(c.mn, c.mx);
 }

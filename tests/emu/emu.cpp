@@ -61,27 +61,21 @@ static void run_whisper3(const FeWhisper2Params& p) {
         if (t.t0 < t.T) {
             for (int q = 0; q < C::TEAMS; ++q) {
                 float* wq = sm.data() + C::OFF_W + q * C::WT;
-                const int mode = fe_w3_team_mode(p, t, q);
-                if (mode == 1) fe_w3_fill_rows_host(p, t, q, wq);
-                else if (mode == 2) for (int l = 0; l < 32; ++l) fe_w3_fill_manual(p, t, q, wq, l);
-                if (mode == 0) continue;
+                if (!fe_w3_team_live(t, q)) continue;
+                fe_w3_fill_rows_host(p, t, q, wq);
+                for (int l = 0; l < 32; ++l) fe_w3_fill_manual(p, t, q, wq, l);
                 for (int member = 0; member < C::MEMBERS; ++member)
-                    for (int k = 0; k < 2; ++k) {
-                        const int task = k == 0 ? fe_w3_a_first(member) : fe_w3_a_second(member);
-                        if (task < 0) continue;
+                    for (int k = 0; k < fe_w3_a_count(member); ++k)
                         for (int l = 0; l < 32; ++l) {
                             FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
-                            fe_w3_stage_a(wq, tm, l, task, FeNoHook());
+                            fe_w3_stage_a(wq, tm, l, fe_w3_a_hu(member, k), FeNoHook());
                         }
-                    }
-                for (int member = 1; member < C::MEMBERS; ++member)
-                    for (int k = 0; k < 2; ++k) {
-                        const int task = k == 0 ? fe_w3_b_first(member) : fe_w3_b_second(member);
+                for (int member = 0; member < C::MEMBERS; ++member)
+                    for (int k = 0; k < fe_w3_b_count(member); ++k)
                         for (int l = 0; l < 32; ++l) {
                             FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
-                            fe_w3_stage_b(P, tm, l, q, task, FeNoHook(), FeNoHook());
+                            fe_w3_stage_b(P, tm, l, q, fe_w3_b_task(member, k), FeNoHook(), FeNoHook());
                         }
-                    }
             }
             for (int w = 0; w < C::NW; ++w) for (int l = 0; l < 32; ++l) {
                 const fe2 mm = fe_w3_phase_mel<NMELS, OUT16>(p, t, sm.data(), l, w);
@@ -124,7 +118,8 @@ static int emu_whisper_any(const void* wave, bool in_s16, const int64_t* lengths
     p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B; p.padding = padding;
     p.n_mels = n_mels; p.norm_mode = norm_mode; p.out = out; p.out_batch_stride = (int64_t)n_mels * T_out;
     p.T_out = T_out; p.units_per_clip = (int)((T_out + C::FT - 1) / C::FT); p.total_units = B * p.units_per_clip;
-    p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
+    p.vec_ok = ((((uintptr_t)wave & 15) == 0) && (stride % 4 == 0)) ? 1 : 0;
+    if ((((uintptr_t)out & 15) == 0) && (p.out_batch_stride % 4 == 0)) p.vec_ok |= 2;
     std::vector<float2> mm((size_t)std::max(p.total_units, 1));
     p.max_keys = keys.data(); p.unit_minmax = mm.data();
     if (version == 3) {

@@ -263,7 +263,7 @@ def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=No
                 walign = 1 if cap == 1 else (2 if cap == 2 else 4)     # 32- / 64- / 128-bit weight loads
                 while len(wts) % walign:
                     wts.append(0.0)
-                desc += [k0_scale * k0 | (m << 16), 4 * len(wts)]
+                desc += [(k0_scale * k0 | (m << 16)) if k0_scale != 512 else (512 * k0 | m), 4 * len(wts)]
                 wts += w + [0.0] * ((-cap) % walign)
         ranges.append(len(desc) // 2)
     while len(wts) % 4:
@@ -387,11 +387,11 @@ def main():
                 rows3[i, base + 2 + (c % 2)] = wi
     tb.append("// Whisper (Tensor-Memory kernel) phase-A constants, see tools/gen_kernels.py")
     tb.append(emit_array("fe_w3_tab", rows3).replace("FE_CONSTANT float fe_w3_tab", "FE_CONSTANT __attribute__((aligned(16))) float fe_w3_tab"))
-    # 16 mel chunks (chunk = warp = 4 * member + team): member 0 runs two phase-A tasks and no phase-B task, members 1, 2
-    # one A and two B tasks, member 3 one A, one B and the light row-0 task -- the mel shares level the totals
-    share3 = [w_ for w_ in (5.0, 1.4, 1.4, 4.2) for _ in range(4)]
-    tb.append(gen_melloop("fe_melloop3_w80", w80, 16, (2, 3, 4, 6, 8, 11, 14), chunk_weight=share3, k0_scale=1, emit_cost=22))
-    tb.append(gen_melloop("fe_melloop3_w128", w128, 16, (1, 2, 3, 4, 6, 7, 9), chunk_weight=share3, k0_scale=1, emit_cost=22))
+    # 16 mel chunks (chunk = warp = 4 * member + team), equal shares: the phase-A / phase-B task map (fe_w3_a_hu,
+    # fe_w3_b_task) already levels the members' totals
+    share3 = [1.0] * 16
+    tb.append(gen_melloop("fe_melloop3_w80", w80, 16, (2, 3, 4, 6, 8, 11, 14), chunk_weight=share3, k0_scale=512, emit_cost=22))
+    tb.append(gen_melloop("fe_melloop3_w128", w128, 16, (1, 2, 3, 4, 6, 7, 9), chunk_weight=share3, k0_scale=512, emit_cost=22))
     tb.append(gen_melrolled("fe_melroll_cosy", cz, 640))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
