@@ -1,6 +1,7 @@
 // libb200feat.so -- kernels, launch logic and the C ABI declared in include/b200feat.h.
 // Build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC -shared
 // (see expressive_speech_translation_b200/build.py).  sm_100a only; no other architecture, no CPU path.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <atomic>
@@ -325,7 +326,7 @@ static __device__ __forceinline__ void fe_mbar_wait_bounded(unsigned addr, unsig
             "{\n\t.reg .pred p;\n\t"
             "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.b32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok) : "r"(addr), "r"(parity), "r"(2000u) : "memory");
+            : "=r"(ok) : "r"(addr), "r"(parity), "r"(200u) : "memory");
         if (ok) return;
     }
     __trap();
@@ -366,32 +367,60 @@ struct FeW3WaitPFree {     // phase B, before its first store into P of a unit: 
 // W[q] of unit `t`: the issuing warp first writes the edge rows element-wise, then lane 0 arms the team's mbarrier with
 // the byte count of the bulk rows and issues one 640-byte cp.async.bulk per row (they complete on that barrier); a dead
 // team's phase is completed by the bare arrival
-static __device__ __noinline__ void fe_w3_issue_w(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq,
-                                                  unsigned mb_wfull, int lane) {
+struct FeW3Issue {      // what the copy issuer needs of the launch parameters, by value: passing the parameter block by
+    const float* wave;  // reference to a non-inlined function moves it to local memory for the WHOLE kernel
+    int64_t wave_stride;
+    int32_t vec_ok, use_tmap, tmap_rows;
+};
+static __device__ __noinline__ void fe_w3_issue_w(const FeW3Issue p, const CUtensorMap* tmap, int b, int f0, int64_t len, int64_t lp,
+                                                  float* wq, unsigned mb_wfull, int lane) {
     typedef FeW3Cfg C;
-    if (!fe_w3_team_live(t, q)) { fe_warp_arrive(mb_wfull, lane); return; }
-    const int64_t g0 = fe_w3_row0(t, q);
-    // the bulk rows are one contiguous run [r_lo, r_hi)
+    const int64_t g0 = (int64_t)f0 * C::HOP - C::PADL;
+    // interior units: ONE tensor copy of the whole (34 rows x 164 floats) box.  The tensor map describes clip b as rows of
+    // 164 floats that start every 160 floats (overlapping rows: the four extra floats per row are the pitch padding), so
+    // the box lands in shared memory exactly in the W[q] layout.
+    if (p.use_tmap) {
+        const int row = f0 - C::TMAP_ROW0;        // row 0 of the map = frame TMAP_ROW0 of the clip
+        if (row >= 0 && row + C::ROWS <= p.tmap_rows && g0 + (int64_t)C::ROWS * C::HOP + (C::PITCH - C::HOP) <= len) {
+            if (lane == 0) {
+                fe_mbar_expect_tx(mb_wfull, C::ROWS * C::PITCH * 4);
+                asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                             ::"r"((unsigned)__cvta_generic_to_shared(wq)), "l"(tmap), "r"(0), "r"(row), "r"(b), "r"(mb_wfull) : "memory");
+            }
+            return;
+        }
+    }
+    // edge units: the issuing warp first writes the edge rows element-wise, then lane 0 arms the team's mbarrier with the
+    // byte count of the bulk rows (one contiguous run [r_lo, r_hi)) and issues one 640-byte cp.async.bulk per row
     int r_lo = 0, r_hi = 0;
     if (p.vec_ok & 1) {
         const int64_t lo = g0 >= 0 ? 0 : (-g0 + C::HOP - 1) / C::HOP;
-        const int64_t hi = t.len - g0 < 0 ? 0 : (t.len - g0) / C::HOP;
+        const int64_t hi = len - g0 < 0 ? 0 : (len - g0) / C::HOP;
         r_lo = (int)(lo < C::ROWS ? lo : C::ROWS);
         r_hi = (int)(hi < C::ROWS ? hi : C::ROWS);
         if (r_hi < r_lo) r_hi = r_lo;
     }
-    if (r_hi - r_lo < C::ROWS) fe_w3_fill_manual(p, t, q, wq, lane);
+    const float* __restrict__ x = p.wave + (int64_t)b * p.wave_stride;
+    if (r_hi - r_lo < C::ROWS) fe_w3_fill_rows_manual(x, g0, len, lp, r_lo, r_hi, wq, lane);
     __syncwarp();
     if (lane == 0) {
         if (r_hi > r_lo) fe_mbar_expect_tx(mb_wfull, (unsigned)((r_hi - r_lo) * C::ROW_BYTES));
         else fe_mbar_arrive(mb_wfull);
-        const float* src = p.wave + (int64_t)t.b * p.wave_stride + g0;
+        const float* src = x + g0;
         const unsigned dst = (unsigned)__cvta_generic_to_shared(wq);
-#pragma unroll 1
+#pragma unroll 4
         for (int r = r_lo; r < r_hi; ++r)
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                          ::"r"(dst + (unsigned)(r * C::PITCH * 4)), "l"(src + r * C::HOP), "n"(C::ROW_BYTES), "r"(mb_wfull) : "memory");
     }
+}
+// W[q] of unit `t` (inlined part: a dead team's phase is completed by a bare arrival)
+static __device__ __forceinline__ void fe_w3_request_w(const FeWhisper2Params& p, const CUtensorMap* tmap, const FeW3Unit& t, int q,
+                                                       float* wq, unsigned mb_wfull, int lane) {
+    if (!fe_w3_team_live(t, q)) { fe_warp_arrive(mb_wfull, lane); return; }
+    FeW3Issue a;
+    a.wave = p.wave; a.wave_stride = p.wave_stride; a.vec_ok = p.vec_ok; a.use_tmap = p.use_tmap; a.tmap_rows = p.tmap_rows;
+    fe_w3_issue_w(a, tmap, t.b, t.t0 + FeW3Cfg::FT * q, t.len, t.lp, wq, mb_wfull, lane);
 }
 // the rows of the unit after next: into L2 now, so that the bulk copies issued one unit later hit there
 static __device__ __forceinline__ void fe_w3_prefetch_l2(const FeWhisper2Params& p, const FeW3Unit& t, int q, int lane) {
@@ -412,9 +441,10 @@ static __device__ __forceinline__ void fe_w3_prefetch_l2(const FeWhisper2Params&
 // A warp arrives on phase k of a barrier only after it has waited for phase k-1 of it (where it waits at all), so no
 // barrier can run two phases ahead of a waiter (parity waits would alias).
 template <int NMELS, bool OUT16>
-__global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhisper2Params p) {
+__global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhisper2Params p, const __grid_constant__ CUtensorMap tmap) {
     typedef FeW3Cfg C;
-    extern __shared__ __align__(16) float sm[];
+    extern __shared__ __align__(1024) float sm3[];
+    float* const sm = sm3;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -426,6 +456,8 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
     sy.wfull = mb0 + 8u * team; sy.afull = mb0 + 8u * (4 + team); sy.bloaded = mb0 + 8u * (8 + team);
     sy.pfull = mb0 + 8u * 12; sy.pfree = mb0 + 8u * 13;
     unsigned* const tm_slot = reinterpret_cast<unsigned*>(sm + C::OFF_MBAR + 2 * C::NMBAR);
+    int* const issued = reinterpret_cast<int*>(sm + C::OFF_MBAR + 2 * C::NMBAR + 4);    // per team: members that finished phase A, all units
+    if (tid < 4) issued[tid] = 0;
     if (tid == 0) {
         for (int q = 0; q < 4; ++q) {
             fe_mbar_init(mb0 + 8u * q, 1);
@@ -454,7 +486,7 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
     const int n_a = fe_w3_a_count(member), n_b = fe_w3_b_count(member);
     if (member == 1 && n_it > 0) {
         const FeW3Unit t = fe_w3_unit(p, u0);
-        fe_w3_issue_w(p, t, team, wq, sy.wfull, lane);
+        fe_w3_request_w(p, &tmap, t, team, wq, sy.wfull, lane);
         if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + du), team, lane);
     }
     FeW3Unit prev;
@@ -482,6 +514,20 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
             }
             fe_tc_fence_before();
             fe_warp_arrive(sy.afull, lane);
+            {   // the member that finishes A(it) LAST refills W for the next unit at once (every A(it) task has read W by
+                // then): the copy then has the whole of M(it-1) and B(it) to land
+                int last = 0;
+                if (lane == 0) {
+                    __threadfence_block();
+                    last = atomicAdd(issued + team, 1) == 4 * it + 3;
+                    __threadfence_block();
+                }
+                last = __shfl_sync(0xffffffffu, last, 0);
+                if (last) {
+                    if (it + 1 < n_it) fe_w3_request_w(p, &tmap, fe_w3_unit(p, u0 + (it + 1) * du), team, wq, sy.wfull, lane);
+                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + (it + 2) * du), team, lane);
+                }
+            }
         }
         FE_T3(it, 2);
         // ---- M(it - 1)
@@ -508,10 +554,6 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
             fe_mbar_wait_bounded(sy.afull, par);
             fe_tc_fence_after();
             FE_T3(it, 5);
-            if (member == 1) {      // every A(it) task of the team has read W: refill it for the next unit
-                if (it + 1 < n_it) fe_w3_issue_w(p, fe_w3_unit(p, u0 + (it + 1) * du), team, wq, sy.wfull, lane);
-                if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + (it + 2) * du), team, lane);
-            }
             bool waited = false;
             const FeW3WaitPFree pre{sy.pfree, ppar, it > 0, &waited};
             if (live) {
@@ -722,6 +764,7 @@ static void launch_whisper2(int n_mels, bool out16, bool in16, unsigned grid, cu
 }
 
 // the Tensor-Memory kernel: four instantiations (mel bins x output dtype); float32 input only
+typedef void (*FeW3Kernel)(const FeWhisper2Params, const CUtensorMap);
 template <class F>
 static int whisper3_for_each(F f) {
     if (int rc = f(fe_whisper3_kernel<80, false>, 0)) return rc;
@@ -731,16 +774,48 @@ static int whisper3_for_each(F f) {
     return 0;
 }
 static int whisper3_smem_attr() {
-    return whisper3_for_each([](void (*k)(const FeWhisper2Params), int) {
+    return whisper3_for_each([](FeW3Kernel k, int) {
         return cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FeW3Cfg::SMEM_BYTES) == cudaSuccess ? 0 : 1;
     });
 }
-static void launch_whisper3(int n_mels, bool out16, unsigned grid, cudaStream_t st, const FeWhisper2Params& p) {
+static void launch_whisper3(int n_mels, bool out16, unsigned grid, cudaStream_t st, const FeWhisper2Params& p, const CUtensorMap& tmap) {
     const int want = (n_mels == 128 ? 2 : 0) + (out16 ? 1 : 0);
-    whisper3_for_each([&](void (*k)(const FeWhisper2Params), int id) {
-        if (id == want) k<<<grid, FeW3Cfg::NT, FeW3Cfg::SMEM_BYTES, st>>>(p);
+    whisper3_for_each([&](FeW3Kernel k, int id) {
+        if (id == want) k<<<grid, FeW3Cfg::NT, FeW3Cfg::SMEM_BYTES, st>>>(p, tmap);
         return 0;
     });
+}
+// Tensor map of the waveform batch for the kernel's box copies: clip b = rows of PITCH floats starting every HOP floats
+// (dimension 1) from sample TMAP_ROW0 * HOP - PADL of the clip, clips `wave_stride` floats apart (dimension 2).  The driver entry
+// point is resolved at run time (no link against libcuda).  Returns false when the map cannot be built: the kernel then
+// falls back to its row-by-row copies.
+static bool whisper3_make_tmap(const float* wave, int64_t wave_stride, int64_t L, int32_t B, CUtensorMap* map, int32_t* rows_out) {
+    typedef FeW3Cfg C;
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) fn = nullptr;
+        return reinterpret_cast<EncodeFn>(fn);
+    }();
+    memset(map, 0, sizeof(*map));
+    *rows_out = 0;
+    if (!encode || getenv("B200FEAT_NO_TMAP")) return false;
+    const int64_t first = (int64_t)C::TMAP_ROW0 * C::HOP - C::PADL;           // clip sample of (row 0, column 0)
+    const int64_t rows = L - first - C::PITCH < 0 ? 0 : (L - first - C::PITCH) / C::HOP + 1;   // rows that lie inside the clip
+    if (rows < C::ROWS || rows > 0x7fffffff || B < 1) return false;
+    cuuint64_t gdim[3] = {(cuuint64_t)C::PITCH, (cuuint64_t)rows, (cuuint64_t)B};
+    cuuint64_t gstr[2] = {(cuuint64_t)C::HOP * 4, (cuuint64_t)wave_stride * 4};
+    cuuint32_t box[3] = {(cuuint32_t)C::PITCH, (cuuint32_t)C::ROWS, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult rc = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(wave + first), gdim, gstr, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) return false;
+    *rows_out = (int32_t)rows;
+    return true;
 }
 // B200FEAT_WHISPER_KERNEL=2 forces the shared-memory frame-pair kernel (A/B timing, profiles/); default: the
 // Tensor-Memory kernel wherever it applies (float32 input, 16-byte aligned rows)
@@ -970,8 +1045,10 @@ static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* len
         FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)(keys_bytes + (int64_t)B * units3 * 8), st));
         {
             const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
+            CUtensorMap tmap;
+            p.use_tmap = whisper3_make_tmap(p.wave, wave_stride, L, B, &tmap, &p.tmap_rows) ? 1 : 0;
             ProfScope ps(st, 0);
-            launch_whisper3(n_mels, out16, grid, st, p);
+            launch_whisper3(n_mels, out16, grid, st, p, tmap);
             g_launches++;
         }
         {

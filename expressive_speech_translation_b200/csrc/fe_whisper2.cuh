@@ -52,6 +52,8 @@ struct FeWhisper2Params {
     // segments whisper.transcribe cuts with mel[:, seek : seek + N_FRAMES] + pad_or_trim
     int32_t win_frames;
     int32_t n_windows;
+    int32_t use_tmap;          // Tensor-Memory kernel: the launch carries a tensor map of the waveform (box copies)
+    int32_t tmap_rows;         // rows per clip in that map
 };
 
 struct FeW2Cfg {

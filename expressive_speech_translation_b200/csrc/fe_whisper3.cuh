@@ -41,8 +41,9 @@ struct FeW3Cfg {
     static constexpr int FT = 32;                        // frames per team and unit
     static constexpr int UF = TEAMS * FT;                // frames per CTA unit (128)
     static constexpr int ROWS = 34, PITCH = 164;         // W[q]: rows of HOP samples, pitch in floats
-    static constexpr int WT = ROWS * PITCH;              // floats per team
+    static constexpr int WT = (ROWS * PITCH + 31) / 32 * 32;   // floats per team, padded: every W[q] is 128-byte aligned (tensor copies)
     static constexpr int ROW_BYTES = HOP * 4;
+    static constexpr int TMAP_ROW0 = 2;                  // first frame whose row lies inside the clip (160 * 2 - 200 >= 0)
     static constexpr int NBINS = 200;
     static constexpr int ATASKS = 5, ACOLS = 84;         // Tensor Memory columns per phase-A task
     static constexpr int TMEM_COLS = 512;                // allocation (power of two >= ATASKS * ACOLS = 420)
@@ -50,13 +51,13 @@ struct FeW3Cfg {
     static constexpr int OFF_P = OFF_W + TEAMS * WT;                 // P[bin][UF]
     static constexpr int OFF_MBAR = OFF_P + NBINS * UF;              // 14 mbarriers (8 bytes each) + the TMEM base slot
     static constexpr int NMBAR = 14;
-    static constexpr int OFF_MDESC = OFF_MBAR + 2 * NMBAR + 4;       // mel descriptors (2 ints per filter, <= 128 filters)
+    static constexpr int OFF_MDESC = OFF_MBAR + 2 * NMBAR + 8;       // (+ TMEM base slot, pad, four W-request counters)       // mel descriptors (2 ints per filter, <= 128 filters)
     static constexpr int OFF_MW = OFF_MDESC + 256;                   // padded taps
     static constexpr int MW_MAX = 576;
     static constexpr int SMEM_FLOATS = OFF_MW + MW_MAX;
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
     static_assert(OFF_P % 4 == 0 && OFF_MBAR % 2 == 0 && OFF_MDESC % 4 == 0 && OFF_MW % 4 == 0, "alignment of the carve-up");
-    static_assert(WT % 4 == 0 && PITCH % 4 == 0, "cp.async.bulk needs 16-byte aligned rows");
+    static_assert(WT % 32 == 0 && PITCH % 4 == 0, "cp.async.bulk needs 16-byte aligned rows, cp.async.bulk.tensor a 128-byte aligned box");
     static_assert(SMEM_BYTES <= 232448, "more than 227 KB of shared memory");
     static constexpr float LOG_SCALE = FeW2Cfg::LOG_SCALE;
 };
@@ -191,24 +192,24 @@ FE_HD FE_INLINE bool fe_w3_row_bulk(const FeWhisper2Params& p, const FeW3Unit& t
     return (p.vec_ok & 1) && g >= 0 && g + FeW3Cfg::HOP <= t.len;
 }
 
-// element-wise rows of one team, by ONE warp: four rows (20 independent loads per lane) in flight at a time
-FE_HD FE_INLINE void fe_w3_fill_manual(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq, int lane) {
+// element-wise rows of one team, by ONE warp: every row outside [r_lo, r_hi), four rows (20 independent loads per lane)
+// in flight at a time
+FE_HD FE_INLINE void fe_w3_fill_rows_manual(const float* __restrict__ x, int64_t g0, int64_t len, int64_t lp, int r_lo, int r_hi,
+                                            float* wq, int lane) {
     typedef FeW3Cfg C;
-    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
-    const int64_t g0 = fe_w3_row0(t, q);
     constexpr int NB = 4;
     int rows[NB];
     int n = 0;
 #pragma unroll 1
     for (int r = 0; r <= C::ROWS; ++r) {
-        if (r < C::ROWS && !fe_w3_row_bulk(p, t, g0, r)) rows[n++] = r;
+        if (r < C::ROWS && !(r >= r_lo && r < r_hi)) rows[n++] = r;
         if (n == NB || (r == C::ROWS && n > 0)) {
             float v[NB][5];
 #pragma unroll
             for (int k = 0; k < NB; ++k)
 #pragma unroll
                 for (int j = 0; j < 5; ++j)
-                    v[k][j] = k < n ? fe_fetch_reflect(x, g0 + (int64_t)rows[k] * C::HOP + lane + 32 * j, t.len, t.lp) : 0.0f;
+                    v[k][j] = k < n ? fe_fetch_reflect(x, g0 + (int64_t)rows[k] * C::HOP + lane + 32 * j, len, lp) : 0.0f;
 #pragma unroll
             for (int k = 0; k < NB; ++k)
 #pragma unroll
@@ -217,6 +218,15 @@ FE_HD FE_INLINE void fe_w3_fill_manual(const FeWhisper2Params& p, const FeW3Unit
             n = 0;
         }
     }
+}
+// host emulation: the same split into bulk rows and element-wise rows as fe_w3_issue_w (b200feat.cu)
+FE_HD FE_INLINE void fe_w3_fill_manual(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq, int lane) {
+    typedef FeW3Cfg C;
+    const int64_t g0 = fe_w3_row0(t, q);
+    int r_lo = 0, r_hi = 0;
+    for (int r = 0; r < C::ROWS; ++r)
+        if (fe_w3_row_bulk(p, t, g0, r)) { if (r_hi == r_lo) r_lo = r; r_hi = r + 1; }
+    fe_w3_fill_rows_manual(p.wave + (int64_t)t.b * p.wave_stride, g0, t.len, t.lp, r_lo, r_hi, wq, lane);
 }
 
 // host emulation of the bulk copies (the device issues cp.async.bulk, b200feat.cu)
@@ -408,7 +418,9 @@ FE_HD FE_INLINE void fe_stg_h4(char* q, fe2 a, fe2 b) {
 template <int CAP, bool OUT16, bool VEC>
 FE_HD FE_INLINE void fe_w3_mel_class(FeW3MelCtx& c, int i0, int i1) {
     typedef FeW3Cfg C;
-#pragma unroll(CAP <= 2 ? 2 : 1)
+    // two filters in flight (four for the short classes): one filter is a dependent chain descriptor -> taps -> FFMA2
+    // -> lg2 -> store of ~300 cycles, and a warp has only eight of them per unit
+#pragma unroll(!VEC ? 1 : (CAP <= 3 ? 4 : 2))
     for (int i = i0; i < i1; ++i) {
         const int2 d = c.desc[i];      // d.x = 512 * k0 | mel row, d.y = byte offset of the weights
         const float4* __restrict__ P = reinterpret_cast<const float4*>(c.Pl + (d.x & ~0x1ff));

@@ -213,7 +213,7 @@ def gen_melproj(name, filt, nch, max_bin, epi_cost=6):
     return "\n".join(out) + "\n"
 
 
-def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=None, k0_scale=8):
+def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=None, k0_scale=8, by_class=False):
     """tables for the rolled mel projection of the Whisper frame-pair kernel.  (The fully unrolled form does
     not fit the instruction cache next to the FFT codelets.)  Filters are sorted into classes by tap count
     (`caps`, ascending); a filter is zero-padded to the cap of its class, so each class is a branch-free loop:
@@ -248,10 +248,17 @@ def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=No
     assert len(cw) == nch
     load = [0.0] * nch
     chunks = [[] for _ in range(nch)]
-    for it in sorted(info, key=lambda t: -(2 * t[2] + emit_cost)):
-        c = min(range(nch), key=lambda q: (load[q] + 2 * it[2] + emit_cost) / cw[q])
-        chunks[c].append(it)
-        load[c] += 2 * it[2] + emit_cost
+    if by_class:
+        # a chunk = a contiguous run of the class-sorted filter list (equal cost per chunk): a warp then sees one or
+        # two classes with several filters each, so its class loops can keep several independent filters in flight
+        order = sorted(info, key=lambda t: (t[1], t[0]))
+        for c, (a, b) in enumerate(partition([3 * t[2] + emit_cost for t in order], nch)):
+            chunks[c] = order[a:b]
+    else:
+        for it in sorted(info, key=lambda t: -(2 * t[2] + emit_cost)):
+            c = min(range(nch), key=lambda q: (load[q] + 2 * it[2] + emit_cost) / cw[q])
+            chunks[c].append(it)
+            load[c] += 2 * it[2] + emit_cost
     desc, wts, ranges = [], [], []
     for c in range(nch):
         chunks[c].sort(key=lambda t: t[0])
@@ -390,8 +397,8 @@ def main():
     # 16 mel chunks (chunk = warp = 4 * member + team), equal shares: the phase-A / phase-B task map (fe_w3_a_hu,
     # fe_w3_b_task) already levels the members' totals
     share3 = [1.0] * 16
-    tb.append(gen_melloop("fe_melloop3_w80", w80, 16, (2, 3, 4, 6, 8, 11, 14), chunk_weight=share3, k0_scale=512, emit_cost=22))
-    tb.append(gen_melloop("fe_melloop3_w128", w128, 16, (1, 2, 3, 4, 6, 7, 9), chunk_weight=share3, k0_scale=512, emit_cost=22))
+    tb.append(gen_melloop("fe_melloop3_w80", w80, 16, (2, 3, 4, 6, 8, 11, 14), chunk_weight=share3, k0_scale=512, emit_cost=22, by_class=True))
+    tb.append(gen_melloop("fe_melloop3_w128", w128, 16, (1, 2, 3, 4, 6, 7, 9), chunk_weight=share3, k0_scale=512, emit_cost=22, by_class=True))
     tb.append(gen_melrolled("fe_melroll_cosy", cz, 640))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
