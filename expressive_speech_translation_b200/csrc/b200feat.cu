@@ -379,19 +379,16 @@ static __device__ __noinline__ void fe_w3_issue_w(const FeW3Issue p, const CUten
     // interior units: ONE tensor copy of the whole (34 rows x 164 floats) box.  The tensor map describes clip b as rows of
     // 164 floats that start every 160 floats (overlapping rows: the four extra floats per row are the pitch padding), so
     // the box lands in shared memory exactly in the W[q] layout.
-    if (p.use_tmap) {
-        const int row = f0 - C::TMAP_ROW0;        // row 0 of the map = frame TMAP_ROW0 of the clip
-        if (row >= 0 && row + C::ROWS <= p.tmap_rows && g0 + (int64_t)C::ROWS * C::HOP + (C::PITCH - C::HOP) <= len) {
-            if (lane == 0) {
-                fe_mbar_expect_tx(mb_wfull, C::ROWS * C::PITCH * 4);
-                asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                             ::"r"((unsigned)__cvta_generic_to_shared(wq)), "l"(tmap), "r"(0), "r"(row), "r"(b), "r"(mb_wfull) : "memory");
-            }
-            return;
+    if (p.use_tmap) {      // always the whole box; rows outside the map arrive as zeros, the team patches what is not right
+        if (lane == 0) {
+            fe_mbar_expect_tx(mb_wfull, C::ROWS * C::PITCH * 4);
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                         ::"r"((unsigned)__cvta_generic_to_shared(wq)), "l"(tmap), "r"(0), "r"(f0 - C::TMAP_ROW0), "r"(b), "r"(mb_wfull) : "memory");
         }
+        return;
     }
-    // edge units: the issuing warp first writes the edge rows element-wise, then lane 0 arms the team's mbarrier with the
-    // byte count of the bulk rows (one contiguous run [r_lo, r_hi)) and issues one 640-byte cp.async.bulk per row
+    // launches without a tensor map: the issuing warp first writes the edge rows element-wise, then lane 0 arms the team's
+    // mbarrier with the byte count of the bulk rows (one contiguous run [r_lo, r_hi)) and issues one 640-byte copy per row
     int r_lo = 0, r_hi = 0;
     if (p.vec_ok & 1) {
         const int64_t lo = g0 >= 0 ? 0 : (-g0 + C::HOP - 1) / C::HOP;
@@ -484,10 +481,12 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
     const int u0 = blockIdx.x, du = gridDim.x;
     const int n_it = u0 < p.total_units ? (p.total_units - u0 + du - 1) / du : 0;
     const int n_a = fe_w3_a_count(member), n_b = fe_w3_b_count(member);
+    FeW3Pos pos;
+    pos.within = u0 / p.B; pos.b = u0 - pos.within * p.B;      // the one division of the kernel
     if (member == 1 && n_it > 0) {
-        const FeW3Unit t = fe_w3_unit(p, u0);
-        fe_w3_request_w(p, &tmap, t, team, wq, sy.wfull, lane);
-        if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + du), team, lane);
+        fe_w3_request_w(p, &tmap, fe_w3_unit_at(p, pos.b, pos.within), team, wq, sy.wfull, lane);
+        const FeW3Pos p1 = fe_w3_pos_next(p, pos);
+        if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit_at(p, p1.b, p1.within), team, lane);
     }
     FeW3Unit prev;
     memset(&prev, 0, sizeof(prev));
@@ -500,11 +499,15 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
         FE_T3(it, 0);
         // ---- A(it)
         if (has) {
-            cur = fe_w3_unit(p, u0 + it * du);
+            cur = fe_w3_unit_at(p, pos.b, pos.within);
             live = fe_w3_team_live(cur, team);
             fe_mbar_wait_bounded(sy.wfull, par);
             FE_T3(it, 1);
             if (live) {
+                if (p.use_tmap && !fe_w3_box_complete(p, cur, team)) {     // clip edges, ragged ends: patch rows, team barrier
+                    fe_w3_patch_rows(p, cur, team, wq, member, lane);
+                    fe_bar_sync(1 + team, C::MEMBERS * 32);
+                }
                 bool waited = false;
                 const FeW3WaitBLoaded pre{sy.bloaded, ppar, it > 0, &waited};
 #pragma unroll 1
@@ -524,8 +527,9 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
                 }
                 last = __shfl_sync(0xffffffffu, last, 0);
                 if (last) {
-                    if (it + 1 < n_it) fe_w3_request_w(p, &tmap, fe_w3_unit(p, u0 + (it + 1) * du), team, wq, sy.wfull, lane);
-                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit(p, u0 + (it + 2) * du), team, lane);
+                    const FeW3Pos p1 = fe_w3_pos_next(p, pos), p2 = fe_w3_pos_next(p, p1);
+                    if (it + 1 < n_it) fe_w3_request_w(p, &tmap, fe_w3_unit_at(p, p1.b, p1.within), team, wq, sy.wfull, lane);
+                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit_at(p, p2.b, p2.within), team, lane);
                 }
             }
         }
@@ -568,6 +572,7 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
             fe_warp_arrive(sy.pfull, lane);
         }
         prev = cur;
+        pos = fe_w3_pos_next(p, pos);
     }
     fe_tc_fence_before();
     __syncthreads();
@@ -1045,6 +1050,7 @@ static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* len
         FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)(keys_bytes + (int64_t)B * units3 * 8), st));
         {
             const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
+            p.step_w = (int32_t)(grid / (unsigned)B); p.step_b = (int32_t)(grid % (unsigned)B);
             CUtensorMap tmap;
             p.use_tmap = whisper3_make_tmap(p.wave, wave_stride, L, B, &tmap, &p.tmap_rows) ? 1 : 0;
             ProfScope ps(st, 0);

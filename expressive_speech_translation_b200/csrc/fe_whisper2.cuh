@@ -54,6 +54,7 @@ struct FeWhisper2Params {
     int32_t n_windows;
     int32_t use_tmap;          // Tensor-Memory kernel: the launch carries a tensor map of the waveform (box copies)
     int32_t tmap_rows;         // rows per clip in that map
+    int32_t step_b, step_w;    // Tensor-Memory kernel: gridDim.x units = step_w unit positions + step_b clips
 };
 
 struct FeW2Cfg {

@@ -143,14 +143,16 @@ struct FeW3Unit {
 // clip b is its own (n_mels, win_frames) block; a unit never straddles two windows (units per window =
 // ceil(win_frames / 128), the last one shorter), and one extra TAIL unit per clip computes the frames just behind the last
 // window without storing them: they can hold the clip's maximum (whisper takes the maximum over the whole padded mel).
-FE_HD FE_INLINE FeW3Unit fe_w3_unit(const FeWhisper2Params& p, int u) {
+// the decode proper, from (clip, unit within the clip): no division by a run-time value on the plain path -- the
+// kernel advances (clip, within) incrementally (FeW3Pos), because a full decode per warp and unit was 7 % of the
+// kernel's time (profiles/r02_w3_trace_v7.txt: 850 cycles of every 12.6 k-cycle unit)
+FE_HD FE_INLINE FeW3Unit fe_w3_unit_at(const FeWhisper2Params& p, int b, int within) {
     typedef FeW3Cfg C;
     FeW3Unit t;
-    t.b = u / p.units_per_clip;
-    const int within = u - t.b * p.units_per_clip;
+    t.b = b;
     t.len = fe_clip_len(p.lengths, t.b, p.L);
     t.lp = t.len + p.padding;
-    const int64_t Tc = t.lp / C::HOP;
+    const int64_t Tc = t.lp < ((int64_t)1 << 32) ? (int64_t)((uint32_t)t.lp / (uint32_t)C::HOP) : t.lp / C::HOP;
     if (p.win_frames > 0) {
         const int W = p.win_frames, upw = (W + C::UF - 1) / C::UF;
         if (within < p.n_windows * upw) {
@@ -177,6 +179,20 @@ FE_HD FE_INLINE FeW3Unit fe_w3_unit(const FeWhisper2Params& p, int u) {
     t.pitch = (int)p.T_out;
     t.o0 = (int64_t)t.b * p.out_batch_stride + t.t0;
     return t;
+}
+// Unit order: POSITION-major, u = within * B + clip.  With clip-major order and gridDim.x = 148, a CTA would only ever
+// see 6 of a 30-s clip's 24 unit positions (gcd(148, 24) = 4), and the CTAs that keep drawing a clip's first / last unit
+// (edge rows, a 56-frame unit) finish 10 % apart (profiles/r02_w3_v8: 12 % of the SM cycles idle at the end).
+FE_HD FE_INLINE FeW3Unit fe_w3_unit(const FeWhisper2Params& p, int u) {
+    const int within = u / p.B;
+    return fe_w3_unit_at(p, u - within * p.B, within);
+}
+// position of a CTA's current unit; one step = gridDim.x units = (step_w positions, step_b clips) with a carry
+struct FeW3Pos { int b, within; };
+FE_HD FE_INLINE FeW3Pos fe_w3_pos_next(const FeWhisper2Params& p, FeW3Pos q) {
+    q.b += p.step_b; q.within += p.step_w;
+    if (q.b >= p.B) { q.b -= p.B; q.within += 1; }
+    return q;
 }
 
 // How W[q] of a unit is filled, row by row: rows that lie completely inside the clip's samples (and are 16-byte
@@ -219,6 +235,56 @@ FE_HD FE_INLINE void fe_w3_fill_rows_manual(const float* __restrict__ x, int64_t
         }
     }
 }
+// Tensor-map launches: the box copy is issued for EVERY live team (rows outside the map are zero-filled by the TMA), and
+// the rows it cannot get right are patched by the team's own four warps after the copy has landed: a row is right when
+// it lies inside the map and inside the clip's valid samples, or outside the map and inside the clip's zero padding.
+FE_HD FE_INLINE bool fe_w3_row_from_box(const FeWhisper2Params& p, const FeW3Unit& t, int f0, int r) {
+    typedef FeW3Cfg C;
+    const int64_t g = ((int64_t)f0 + r) * C::HOP - C::PADL;
+    const int ri = f0 - C::TMAP_ROW0 + r;
+    const bool inb = ri >= 0 && ri < p.tmap_rows;
+    if (inb) return g >= 0 && g + C::HOP <= t.len;
+    return ri >= p.tmap_rows && g >= t.len && g + C::HOP <= t.lp;
+}
+// rows [0, ROWS) of a box are right from row r_lo on and up to r_hi, or (zero padding) all the way: returns true when
+// every row is right (the common case, decided from the first and the last row)
+FE_HD FE_INLINE bool fe_w3_box_complete(const FeWhisper2Params& p, const FeW3Unit& t, int q) {
+    typedef FeW3Cfg C;
+    const int f0 = t.t0 + C::FT * q;
+    const int64_t g0 = (int64_t)f0 * C::HOP - C::PADL, g1 = g0 + (int64_t)C::ROWS * C::HOP;
+    const int r0 = f0 - C::TMAP_ROW0;
+    if (r0 >= 0 && r0 + C::ROWS <= p.tmap_rows && g1 <= t.len) return true;          // inside the map and the clip
+    if (r0 >= p.tmap_rows && g0 >= t.len && g1 <= t.lp) return true;                 // all zero padding
+    return false;
+}
+// member `member` patches rows member, member + 4, ...; a team barrier must follow
+FE_HD FE_INLINE void fe_w3_patch_rows(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq, int member, int lane) {
+    typedef FeW3Cfg C;
+    const int f0 = t.t0 + C::FT * q;
+    const float* __restrict__ x = p.wave + (int64_t)t.b * p.wave_stride;
+    const int64_t g0 = (int64_t)f0 * C::HOP - C::PADL;
+#pragma unroll 1
+    for (int r = member; r < C::ROWS; r += C::MEMBERS) {
+        if (fe_w3_row_from_box(p, t, f0, r)) continue;
+        float v[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) v[j] = fe_fetch_reflect(x, g0 + (int64_t)r * C::HOP + lane + 32 * j, t.len, t.lp);
+#pragma unroll
+        for (int j = 0; j < 5; ++j) wq[r * C::PITCH + lane + 32 * j] = v[j];
+    }
+}
+// host emulation of the box copy: rows inside the map are copied (PITCH floats each), the others zero-filled
+FE_HD FE_INLINE void fe_w3_box_host(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq) {
+    typedef FeW3Cfg C;
+    const int f0 = t.t0 + C::FT * q;
+    const float* x = p.wave + (int64_t)t.b * p.wave_stride;
+    for (int r = 0; r < C::ROWS; ++r) {
+        const int ri = f0 - C::TMAP_ROW0 + r;
+        const int64_t g = ((int64_t)f0 + r) * C::HOP - C::PADL;
+        for (int c = 0; c < C::PITCH; ++c) wq[r * C::PITCH + c] = (ri >= 0 && ri < p.tmap_rows) ? x[g + c] : 0.0f;
+    }
+}
+
 // host emulation: the same split into bulk rows and element-wise rows as fe_w3_issue_w (b200feat.cu)
 FE_HD FE_INLINE void fe_w3_fill_manual(const FeWhisper2Params& p, const FeW3Unit& t, int q, float* wq, int lane) {
     typedef FeW3Cfg C;

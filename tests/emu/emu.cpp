@@ -2,6 +2,7 @@
 // Compiles the very same phase functions the CUDA kernels call, with g++, and runs them thread after
 // thread over a plain array standing in for shared memory.  Built by tests/emu/build.py.
 #include <vector>
+#include <cstdlib>
 #include <cstring>
 #include <algorithm>
 #include "fe_common.h"
@@ -45,6 +46,7 @@ static void run_whisper(const FeWhisper2Params& p) {
     }
 }
 
+static bool use_tmap_env() { const char* e = getenv("EMU_NO_TMAP"); return !(e && e[0] == '1'); }
 // Tensor-Memory kernel (fe_whisper3.cuh): Tensor Memory is a plain [team][lane][512] array here; per CTA unit the teams'
 // rows are filled (bulk-copy path or element-wise path, as the kernel picks them), then phases A, B and M run in the
 // order the mbarriers enforce on the GPU.  unit_minmax holds (max key, -min key) like the kernel's atomics.
@@ -62,8 +64,15 @@ static void run_whisper3(const FeWhisper2Params& p) {
             for (int q = 0; q < C::TEAMS; ++q) {
                 float* wq = sm.data() + C::OFF_W + q * C::WT;
                 if (!fe_w3_team_live(t, q)) continue;
-                fe_w3_fill_rows_host(p, t, q, wq);
-                for (int l = 0; l < 32; ++l) fe_w3_fill_manual(p, t, q, wq, l);
+                if (p.use_tmap) {       // box copy, then the team's patch of the rows the copy cannot get right
+                    fe_w3_box_host(p, t, q, wq);
+                    if (!fe_w3_box_complete(p, t, q))
+                        for (int member = 0; member < C::MEMBERS; ++member)
+                            for (int l = 0; l < 32; ++l) fe_w3_patch_rows(p, t, q, wq, member, l);
+                } else {
+                    fe_w3_fill_rows_host(p, t, q, wq);
+                    for (int l = 0; l < 32; ++l) fe_w3_fill_manual(p, t, q, wq, l);
+                }
                 for (int member = 0; member < C::MEMBERS; ++member)
                     for (int k = 0; k < fe_w3_a_count(member); ++k)
                         for (int l = 0; l < 32; ++l) {
@@ -125,6 +134,12 @@ static int emu_whisper_any(const void* wave, bool in_s16, const int64_t* lengths
     if (version == 3) {
         if (in_s16) return -2;
         p.units_per_clip = (int)((T_out + FeW3Cfg::UF - 1) / FeW3Cfg::UF); p.total_units = B * p.units_per_clip;
+        {   // the tensor map the library would build (whisper3_make_tmap in b200feat.cu)
+            const int64_t first = (int64_t)FeW3Cfg::TMAP_ROW0 * 160 - 200;
+            const int64_t rows = L - first - FeW3Cfg::PITCH < 0 ? 0 : (L - first - FeW3Cfg::PITCH) / 160 + 1;
+            p.use_tmap = ((p.vec_ok & 1) && rows >= FeW3Cfg::ROWS && use_tmap_env()) ? 1 : 0;
+            p.tmap_rows = p.use_tmap ? (int)rows : 0;
+        }
         if (n_mels == 80 && !out16) run_whisper3<80, false>(p);
         else if (n_mels == 80) run_whisper3<80, true>(p);
         else if (n_mels == 128 && !out16) run_whisper3<128, false>(p);
