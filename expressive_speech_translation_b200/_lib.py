@@ -29,6 +29,10 @@ SYMBOLS = {
     "b200feat_whisper_logmel_ex": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                               _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32, _c.c_int64,
                                               _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
+    "b200feat_noalloc_workspace_max": (_c.c_int64, []),
+    "b200feat_whisper_logmel_noalloc": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
+                                                   _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int64,
+                                                   _c.c_int64, _c.c_void_p]),
     "b200feat_cosy_mel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
                                      _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64,
                                      _c.c_void_p]),

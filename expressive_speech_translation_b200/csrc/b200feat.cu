@@ -1117,6 +1117,58 @@ int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64
                                out_dtype == B200FEAT_F16, out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
 }
 
+// ------------------------------------------------------------------------------------------ Whisper, no allocation
+// The workspace of b200feat_whisper_logmel (per-clip maximum keys + per-unit (max, -min) keys) as a file-scope device
+// array, for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every
+// GPU that loads the library holds these bytes until exit.  In HOST code the name below is only a stand-in for the
+// symbol: the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+#define FE_NOALLOC_WS_BYTES (1 << 20)
+static __device__ __align__(256) unsigned char fe_noalloc_ws[FE_NOALLOC_WS_BYTES];
+
+static int noalloc_ws_ptr(void** out) {
+    static std::mutex mu;
+    static void* ptrs[64];
+    int dev = 0;
+    FE_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(B200FEAT_EINVAL, "whisper_logmel_noalloc: device index %d not supported (< 64)", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (ptrs[dev] == nullptr) {
+        void* q = nullptr;
+        FE_CUDA(cudaGetSymbolAddress(&q, fe_noalloc_ws));      // `dev` is current: the address is this device's copy
+        if (q == nullptr) return fail(B200FEAT_ECUDA, "whisper_logmel_noalloc: cudaGetSymbolAddress returned a null address");
+        ptrs[dev] = q;
+    }
+    *out = ptrs[dev];
+    return 0;
+}
+
+int64_t b200feat_noalloc_workspace_max(void) { return FE_NOALLOC_WS_BYTES; }
+
+int b200feat_whisper_logmel_noalloc(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                                    int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                                    float* out, int64_t out_batch_stride, int64_t T_out, void* cuda_stream) {
+    if (B < 0 || L < 0 || padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel_noalloc: negative B, L or padding");
+    const int64_t need = b200feat_workspace_bytes(B200FEAT_KIND_WHISPER, B, (T_out > 0 ? T_out : 0) * FeW2Cfg::HOP);
+    const int64_t need_l = b200feat_workspace_bytes(B200FEAT_KIND_WHISPER, B, L + padding);
+    const int64_t want = need > need_l ? need : need_l;
+    if (want < 0 || want > FE_NOALLOC_WS_BYTES)
+        return fail(B200FEAT_EWORKSPACE, "whisper_logmel_noalloc: this call needs %lld bytes of scratch, the built-in array holds %d "
+                    "(B x ceil(frames / 64) x 8 + 4 x B + 32 <= %d); split the batch or use b200feat_whisper_logmel with a "
+                    "caller-owned workspace", (long long)want, FE_NOALLOC_WS_BYTES, FE_NOALLOC_WS_BYTES);
+    void* ws = nullptr;
+    if (B > 0 && T_out > 0) {
+        if (int rc = check_device_arch()) return rc;
+        if (int rc = noalloc_ws_ptr(&ws)) return rc;
+    } else {
+        static unsigned char dummy;      // nothing is launched for an empty call; the shared path only checks non-null
+        ws = &dummy;
+    }
+    // the shared path clears the part of the array it uses (cudaMemsetAsync on cuda_stream) before the kernels run, so
+    // the previous call's contents never leak into this one; it allocates nothing
+    return whisper_logmel_impl(wave, false, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out, false,
+                               out_batch_stride, T_out, ws, FE_NOALLOC_WS_BYTES, cuda_stream);
+}
+
 // ------------------------------------------------------------------------------------------ CosyVoice
 static int cosy_mel_impl(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
                          int64_t wave_stride, float* out, bool frame_major, int64_t out_batch_stride, int64_t T_out,

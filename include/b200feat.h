@@ -87,6 +87,24 @@ int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64
                                void* out, int32_t out_dtype, int64_t out_batch_stride, int64_t T_out,
                                void* workspace, int64_t workspace_bytes, void* cuda_stream);
 
+/* Whisper log-mel WITHOUT any allocation and without a caller workspace.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arithmetic, kernels and result as b200feat_whisper_logmel (float32 in / out);
+ * the scratch the kernels need (per-clip maximum keys, per-unit minimum / maximum) lives in ONE library-owned static
+ * device array of b200feat_noalloc_workspace_max() = 1 MiB per GPU (held by every GPU that loads the library until exit).
+ *   limit    a call needs 32 + 4 * B + 8 * B * ceil(max(T_out, (L + padding) / 160 + 1) / 64) bytes (e.g. 1024 clips of
+ *            30 s: 380 KiB; 2048: 760 KiB); larger calls are rejected with B200FEAT_EWORKSPACE and a message -- split
+ *            the batch, or use b200feat_whisper_logmel with your own workspace.
+ *   sharing  every call on a device uses the same array.  The part a call uses is cleared on cuda_stream before its
+ *            kernels run, so calls that are ordered on the GPU (same stream, or ordered by events) are independent of
+ *            each other; calls that OVERLAP on the GPU (different streams, no ordering) race on it and give wrong
+ *            results -- serialise them or use the workspace entry point.
+ *   The entry point calls no cudaMalloc / cudaFree / allocating library routine; its launches are asynchronous. */
+int64_t b200feat_noalloc_workspace_max(void);
+int b200feat_whisper_logmel_noalloc(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
+                                    int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                                    float* out, int64_t out_batch_stride, int64_t T_out, void* cuda_stream);
+
 /* CosyVoice 24 kHz mel (n_fft 1920, hop 480, 80 mels, ln, no normalisation).
  * out: (B, 80, T_out) fp32. */
 int b200feat_cosy_mel(const float* wave, const int64_t* lengths, int32_t B, int64_t L,
