@@ -480,7 +480,7 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
 
     const int u0 = blockIdx.x, du = gridDim.x;
     const int n_it = u0 < p.total_units ? (p.total_units - u0 + du - 1) / du : 0;
-    const int n_a = fe_w3_a_count(member), n_b = fe_w3_b_count(member);
+    const int a_single = fe_w3_a_single(member), n_b = fe_w3_b_count(member);
     FeW3Pos pos;
     pos.within = u0 / p.B; pos.b = u0 - pos.within * p.B;      // the one division of the kernel
     if (member == 1 && n_it > 0) {
@@ -510,9 +510,16 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
                 }
                 bool waited = false;
                 const FeW3WaitBLoaded pre{sy.bloaded, ppar, it > 0, &waited};
+#ifdef FE_W3_PAIR         // A/B build only: conflict-free LDS.128 for the member's first two half-units.  Measured on one
+                          // B200, same box: 1.046 ms against 1.028 ms for the form below -- the kernel is bound by instruction
+                          // issue, not by the shared-memory pipe, and the pair form costs code size and registers.
+                fe_w3_stage_a_pair(wq, tm, lane, member, pre);
+                if (a_single >= 0) fe_w3_stage_a(wq, tm, lane, a_single, pre);
+#else
 #pragma unroll 1
-                for (int k = 0; k < n_a; ++k)            // one call site: the kernel is sensitive to its code size
-                    fe_w3_stage_a(wq, tm, lane, fe_w3_a_hu(member, k), pre);
+                for (int k = 0; k < (a_single >= 0 ? 3 : 2); ++k)      // one call site: the kernel is sensitive to code size
+                    fe_w3_stage_a(wq, tm, lane, k < 2 ? 2 * member + k : a_single, pre);
+#endif
                 fe_tm_wait_st();
             }
             fe_tc_fence_before();
@@ -586,10 +593,14 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
     __shared__ int list[256];
     __shared__ int count;
     const int2* __restrict__ ukeys = reinterpret_cast<const int2*>(p.unit_minmax);
-    for (int base = blockIdx.x * blockDim.x; base < p.total_units; base += gridDim.x * blockDim.x) {
+    // unit u is checked by CTA u % gridDim.x: neighbouring units (the same position of neighbouring clips, which tend to
+    // need the clamp together -- clip starts, silent stretches) go to DIFFERENT CTAs, so the rewrites spread over the
+    // whole GPU.  (With contiguous blocks of units per CTA the 37 flagged units of the noise bench sat in a few CTAs
+    // that rewrote them one after the other: 57 us with the SMs 95 % idle, profiles/r02_whisper3_ncu_summary.txt.)
+    for (int base = 0; base < p.total_units; base += gridDim.x * blockDim.x) {
         if (threadIdx.x == 0) count = 0;
         __syncthreads();
-        const int u = base + threadIdx.x;
+        const int u = base + (int)threadIdx.x * (int)gridDim.x + (int)blockIdx.x;
         if (u < p.total_units) {
             const FeW3Unit t = fe_w3_unit(p, u);
             const int n_in = t.n_in;
@@ -1058,8 +1069,8 @@ static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* len
             g_launches++;
         }
         {
-            const int need = (p.total_units + 255) / 256;
-            const unsigned grid = (unsigned)(need < sms * 8 ? need : sms * 8);
+            const int want = sms * 4;
+            const unsigned grid = (unsigned)(p.total_units < want ? p.total_units : want);
             ProfScope ps(st, 1);
             if (n_mels == 80 && !out16) fe_whisper3_fixup_kernel<80, false><<<grid, 256, 0, st>>>(p);
             else if (n_mels == 80) fe_whisper3_fixup_kernel<80, true><<<grid, 256, 0, st>>>(p);

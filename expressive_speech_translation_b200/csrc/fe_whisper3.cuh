@@ -322,8 +322,7 @@ FE_HD FE_INLINE void fe_w3_copy_tables(float* sm, int tid, int nthreads) {
 // phase B into six tasks (pairs p = 0..4 = rows (2p+1, 2p+2); 5 = row 0).  Members 0 and 1 run three half-units and
 // one light B task, members 2 and 3 two half-units and two pair tasks: A(u) is complete after 1.5 task times (not 2),
 // and the mel projection is shared equally (chunk = warp).
-FE_HD FE_INLINE int fe_w3_a_count(int member) { return member < 2 ? 3 : 2; }
-FE_HD FE_INLINE int fe_w3_a_hu(int member, int k) { return k < 2 ? 2 * member + k : 8 + member; }
+FE_HD FE_INLINE int fe_w3_a_single(int member) { return member < 2 ? 8 + member : -1; }     // besides the pair i = member
 FE_HD FE_INLINE int fe_w3_b_count(int member) { return member < 2 ? 1 : 2; }
 FE_HD FE_INLINE int fe_w3_b_task(int member, int k) { return member == 0 ? 4 : (member == 1 ? 5 : 2 * (member - 2) + k); }
 
@@ -331,18 +330,11 @@ FE_HD FE_INLINE int fe_w3_b_task(int member, int k) { return member == 0 ? 4 : (
 // fe_w3_tab: per pair of half-units (i = hu / 2) 160 floats = window w[20 n1 + 4 i + c] as [n1][c] (80), then for
 // k1 = 1..10 the twiddles W_400^((4 i + c) k1) as [k1][wr_c0, wr_c1, wi_c0, wi_c1, wr_c2, wr_c3, wi_c2, wi_c3] (80);
 // half-unit hu uses c = 2 (hu % 2), 2 (hu % 2) + 1
+// the part after the windowed loads: real 20-point DFT of the packed pair of sub-sequences, twiddles, Tensor Memory stores
 template <class PreStore>
-FE_HD FE_INLINE void fe_w3_stage_a(const float* wq, const FeTm& tm, int lane, int hu, PreStore pre_store) {
+FE_HD FE_INLINE void fe_w3_a_core(const fe2* x, const FeTm& tm, int hu, PreStore pre_store) {
     typedef FeW3Cfg C;
-    // sample n = 20 n1 + 2 hu + c of this lane's frame: row lane + n / 160, column n % 160; n / 160 == n1 / 8.
-    // 64-bit loads at lane stride 164 floats: two lanes per bank pair (the 16-byte row alignment the bulk copies need
-    // leaves no conflict-free pitch for them); same wavefronts as one conflict-free LDS.128 per two half-units
-    const fe2* __restrict__ s = reinterpret_cast<const fe2*>(wq + C::PITCH * lane) + hu;
-    const fe2* __restrict__ win = reinterpret_cast<const fe2*>(fe_w3_tab + 160 * (hu >> 1)) + (hu & 1);
     const fe2* __restrict__ tw = reinterpret_cast<const fe2*>(fe_w3_tab + 160 * (hu >> 1)) + 40 + 2 * (hu & 1);
-    fe2 x[C::R];
-#pragma unroll
-    for (int n1 = 0; n1 < C::R; ++n1) x[n1] = fe_mul(win[2 * n1], s[10 * n1 + 2 * (n1 / 8)]);
     fe2 yr[11], yi[11];
     fe_rdft20_h11(x, yr, yi);
     pre_store();   // Tensor Memory may still be read by phase B of the previous unit
@@ -365,6 +357,40 @@ FE_HD FE_INLINE void fe_w3_stage_a(const float* wq, const FeTm& tm, int lane, in
         fe_tm_st8(tm, col + 4 + 16 * j, re[0], im[0], re[1], im[1]);
     }
     fe_tm_st2(tm, C::ACOLS * (hu >> 1) + 2 * (hu & 1), yr[0].x, yr[0].y);
+}
+
+// ONE half-unit: 64-bit loads at lane stride 164 floats hit every bank pair twice (the 16-byte row alignment the tensor
+// copy needs leaves no conflict-free pitch for them): used for half-units 8 and 9 only
+template <class PreStore>
+FE_HD FE_INLINE void fe_w3_stage_a(const float* wq, const FeTm& tm, int lane, int hu, PreStore pre_store) {
+    typedef FeW3Cfg C;
+    // sample n = 20 n1 + 2 hu + c of this lane's frame: row lane + n / 160, column n % 160; n / 160 == n1 / 8
+    const fe2* __restrict__ s = reinterpret_cast<const fe2*>(wq + C::PITCH * lane) + hu;
+    const fe2* __restrict__ win = reinterpret_cast<const fe2*>(fe_w3_tab + 160 * (hu >> 1)) + (hu & 1);
+    fe2 x[C::R];
+#pragma unroll
+    for (int n1 = 0; n1 < C::R; ++n1) x[n1] = fe_mul(win[2 * n1], s[10 * n1 + 2 * (n1 / 8)]);
+    fe_w3_a_core(x, tm, hu, pre_store);
+}
+
+// the PAIR of half-units (2 i, 2 i + 1): their samples 20 n1 + 4 i .. + 3 are one 16-byte word per n1, and 128-bit loads
+// at lane stride 164 floats (= 4 x 41) are conflict-free -- half the shared-memory wavefronts of two single half-units
+// (profiles/r02_whisper3_ncu_summary.txt: 31 % of the kernel's wavefronts were these conflicts)
+template <class PreStore>
+FE_HD FE_INLINE void fe_w3_stage_a_pair(const float* wq, const FeTm& tm, int lane, int i, PreStore pre_store) {
+    typedef FeW3Cfg C;
+    const float4* __restrict__ s = reinterpret_cast<const float4*>(wq + C::PITCH * lane) + i;
+    const float4* __restrict__ win = reinterpret_cast<const float4*>(fe_w3_tab + 160 * i);
+    fe2 xa[C::R], xb[C::R];
+#pragma unroll
+    for (int n1 = 0; n1 < C::R; ++n1) {
+        const float4 v = s[5 * n1 + n1 / 8];
+        const float4 w = win[n1];
+        xa[n1] = fe_mul(fe_mk2(w.x, w.y), fe_mk2(v.x, v.y));
+        xb[n1] = fe_mul(fe_mk2(w.z, w.w), fe_mk2(v.z, v.w));
+    }
+    fe_w3_a_core(xa, tm, 2 * i, pre_store);
+    fe_w3_a_core(xb, tm, 2 * i + 1, pre_store);
 }
 
 // Tensor Memory column of Y[n2][k1]: task n2 / 4, sub-sequence c = n2 % 4

@@ -74,11 +74,16 @@ static void run_whisper3(const FeWhisper2Params& p) {
                     for (int l = 0; l < 32; ++l) fe_w3_fill_manual(p, t, q, wq, l);
                 }
                 for (int member = 0; member < C::MEMBERS; ++member)
-                    for (int k = 0; k < fe_w3_a_count(member); ++k)
-                        for (int l = 0; l < 32; ++l) {
-                            FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
-                            fe_w3_stage_a(wq, tm, l, fe_w3_a_hu(member, k), FeNoHook());
+                    for (int l = 0; l < 32; ++l) {
+                        FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
+                        if (getenv("EMU_W3_PAIR")) {     // the A/B variant of the kernel (-DFE_W3_PAIR)
+                            fe_w3_stage_a_pair(wq, tm, l, member, FeNoHook());
+                            if (fe_w3_a_single(member) >= 0) fe_w3_stage_a(wq, tm, l, fe_w3_a_single(member), FeNoHook());
+                        } else {
+                            for (int k = 0; k < (fe_w3_a_single(member) >= 0 ? 3 : 2); ++k)
+                                fe_w3_stage_a(wq, tm, l, k < 2 ? 2 * member + k : fe_w3_a_single(member), FeNoHook());
                         }
+                    }
                 for (int member = 0; member < C::MEMBERS; ++member)
                     for (int k = 0; k < fe_w3_b_count(member); ++k)
                         for (int l = 0; l < 32; ++l) {
