@@ -14,6 +14,7 @@ DEPS = [
     os.path.join(HERE, "csrc", "fe_whisper2.cuh"),
     os.path.join(HERE, "csrc", "fe_whisper3.cuh"),
     os.path.join(HERE, "csrc", "fe_kaldi.cuh"),
+    os.path.join(HERE, "csrc", "fe_kaldi3.cuh"),
     os.path.join(HERE, "csrc", "fe_cosy.cuh"),
     os.path.join(HERE, "csrc", "fe_resample.cuh"),
     os.path.join(HERE, "csrc", "fe_resample_plan.h"),

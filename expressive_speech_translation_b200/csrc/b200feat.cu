@@ -20,6 +20,7 @@
 #include "fe_whisper2.cuh"
 #include "fe_whisper3.cuh"
 #include "fe_kaldi.cuh"
+#include "fe_kaldi3.cuh"
 #include "fe_cosy.cuh"
 #include "fe_resample.cuh"
 #define FE_RS_HAVE_PARAMS
@@ -670,6 +671,217 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
     }
 }
 
+// =====================================================================================================
+// kaldi fbank, Tensor-Memory formulation (fe_kaldi3.cuh) -- the skeleton of fe_whisper3_kernel
+// =====================================================================================================
+// Per unit `it` every warp runs, in program order:
+//   A(it)   : wait WFULL(it); [patch rows the box copy could not deliver; team barrier]; row partial sums; team barrier;
+//             frame mean; its two phase-A half-units [first Tensor Memory store waits BLOADED(it-1)]; arrive AFULL(it);
+//             the member that finishes last requests W(it+1)
+//   M(it-1) : wait PFULL(it-1); its filter groups of the mel projection straight to `out`; arrive PFREE(it-1)
+//   B(it)   : wait AFULL(it); its phase-B tasks [last task's loads landed: arrive BLOADED(it); first store into P waits
+//             PFREE(it-1)]; arrive PFULL(it)
+__global__ void __launch_bounds__(FeK3Cfg::NT, 1) fe_kaldi3_kernel(const FeKaldiParams p, const __grid_constant__ CUtensorMap tmap) {
+    typedef FeK3Cfg C;
+    extern __shared__ __align__(1024) float smk3[];
+    float* const sm = smk3;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const int team = warp & 3, member = warp >> 2;
+    float* const wq = sm + C::OFF_W + team * C::WT;
+    float* const P = sm + C::OFF_P;
+    float* const part = sm + C::OFF_PART + team * C::PARTS * C::PARTW;
+    const unsigned mb0 = (unsigned)__cvta_generic_to_shared(sm + C::OFF_MBAR);
+    FeW3Sync sy;
+    sy.wfull = mb0 + 8u * team; sy.afull = mb0 + 8u * (4 + team); sy.bloaded = mb0 + 8u * (8 + team);
+    sy.pfull = mb0 + 8u * 12; sy.pfree = mb0 + 8u * 13;
+    unsigned* const tm_slot = reinterpret_cast<unsigned*>(sm + C::OFF_MBAR + 2 * C::NMBAR);
+    int* const finished = reinterpret_cast<int*>(sm + C::OFF_MBAR + 2 * C::NMBAR + 4);   // per team: members done with phase A
+    if (tid < 4) finished[tid] = 0;
+    if (tid == 0) {
+        for (int q = 0; q < 4; ++q) {
+            fe_mbar_init(mb0 + 8u * q, 1);
+            fe_mbar_init(mb0 + 8u * (4 + q), C::MEMBERS);
+            fe_mbar_init(mb0 + 8u * (8 + q), C::MEMBERS);
+        }
+        fe_mbar_init(sy.pfull, C::NW);
+        fe_mbar_init(sy.pfree, C::NW);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    fe_k3_copy_tables(sm, tid, C::NT);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"((unsigned)__cvta_generic_to_shared(tm_slot)), "n"(C::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fe_tc_fence_before();
+    __syncthreads();
+    fe_tc_fence_after();
+    const unsigned tm_base = *tm_slot;
+    FeTm tm;
+    tm.base = tm_base + ((unsigned)(team * 32) << 16);
+
+    const int u0 = blockIdx.x, du = gridDim.x;
+    const int n_it = u0 < p.total_units ? (p.total_units - u0 + du - 1) / du : 0;
+    FeW3Pos pos;
+    pos.within = u0 / p.B; pos.b = u0 - pos.within * p.B;
+    const int n_b = fe_k3_b_count(member);
+    // W[q] of a unit: ONE tensor copy of the (34 rows x 164 floats) box; a dead team's phase is completed by a bare arrival
+    auto request_w = [&](const FeK3Unit& t) {
+        if (!fe_k3_team_live(t, team)) { fe_warp_arrive(sy.wfull, lane); return; }
+        if (lane == 0) {
+            fe_mbar_expect_tx(sy.wfull, C::ROWS * C::PITCH * 4);
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                         ::"r"((unsigned)__cvta_generic_to_shared(wq)), "l"(&tmap), "r"(0), "r"(t.t0 + C::FT * team), "r"(t.b), "r"(sy.wfull) : "memory");
+        }
+    };
+    if (member == 1 && n_it > 0) request_w(fe_k3_unit_at(p, pos.b, pos.within));
+    FeK3Unit prev;
+    memset(&prev, 0, sizeof(prev));
+#pragma unroll 1
+    for (int it = 0; it <= n_it; ++it) {
+        const bool has = it < n_it;
+        const unsigned par = (unsigned)(it & 1), ppar = par ^ 1u;
+        FeK3Unit cur = prev;
+        bool live = false;
+        // ---- A(it)
+        if (has) {
+            cur = fe_k3_unit_at(p, pos.b, pos.within);
+            live = fe_k3_team_live(cur, team);
+            fe_mbar_wait_bounded(sy.wfull, par);
+            if (live) {
+                if (!fe_k3_box_complete(p, cur, team)) {
+                    fe_k3_patch_rows(p, cur, team, wq, member, lane);
+                    fe_bar_sync(1 + team, C::MEMBERS * 32);
+                }
+                {
+                    FeK3Pre pre_regs;
+                    fe_k3_pre_load(wq, member, lane, pre_regs);
+                    fe_bar_sync(1 + team, C::MEMBERS * 32);          // every member has read its neighbours' samples
+                    fe_k3_pre_store(wq, part, member, lane, pre_regs);
+                }
+                fe_bar_sync(1 + team, C::MEMBERS * 32);
+                const float mean = fe_k3_frame_mean(part, lane), x0 = fe_k3_frame_x0(part, lane);
+                bool waited = false;
+                const FeW3WaitBLoaded pre{sy.bloaded, ppar, it > 0, &waited};
+#pragma unroll 1
+                for (int k = 0; k < 2; ++k) fe_k3_stage_a(wq, tm, lane, 2 * member + k, mean, x0, pre);
+                fe_tm_wait_st();
+            }
+            fe_tc_fence_before();
+            fe_warp_arrive(sy.afull, lane);
+            {
+                int last = 0;
+                if (lane == 0) {
+                    __threadfence_block();
+                    last = atomicAdd(finished + team, 1) == 4 * it + 3;
+                    __threadfence_block();
+                }
+                last = __shfl_sync(0xffffffffu, last, 0);
+                if (last && it + 1 < n_it) {
+                    const FeW3Pos p1 = fe_k3_pos_next(p, pos);
+                    request_w(fe_k3_unit_at(p, p1.b, p1.within));
+                }
+            }
+        }
+        // ---- M(it - 1)
+        if (it > 0) {
+            fe_mbar_wait_bounded(sy.pfull, ppar);
+            if (prev.t0 < prev.T) fe_k3_phase_mel(p, prev, sm, lane, warp);
+            else fe_k3_zero_unit(p, prev, lane, warp);
+            if (has) fe_warp_arrive(sy.pfree, lane);
+        }
+        // ---- B(it)
+        if (has) {
+            fe_mbar_wait_bounded(sy.afull, par);
+            fe_tc_fence_after();
+            bool waited = false;
+            const FeW3WaitPFree pre{sy.pfree, ppar, it > 0, &waited};
+            if (live) {
+#pragma unroll 1
+                for (int k = 0; k < n_b; ++k)
+                    fe_k3_stage_b(P, tm, lane, team, fe_k3_b_task(member, k), FeW3ArriveBLoaded{sy.bloaded, lane, k == n_b - 1}, pre);
+            } else {
+                FeW3ArriveBLoaded{sy.bloaded, lane, true}();
+            }
+            fe_warp_arrive(sy.pfull, lane);
+        }
+        prev = cur;
+        pos = fe_k3_pos_next(p, pos);
+    }
+    fe_tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm_base), "n"(C::TMEM_COLS) : "memory");
+}
+
+// CMN of the Tensor-Memory path: feat - feat.mean(0) per clip.  One CTA per (clip, half of the 80 columns): the half-tile
+// (T, 40) of a clip up to 6.4 s fits 100 KB of shared memory, so TWO CTAs are resident per SM and one's loads overlap the
+// other's stores (one CTA per clip with the whole tile: 0.34 ms for 4096 x 5 s; the traffic alone is 0.20 ms).  The tile
+// is read ONCE (global -> shared memory -> column means -> subtract -> write); longer clips make two passes over global
+// memory.  Fixed summation order: deterministic.
+__global__ void __launch_bounds__(320, 2) fe_kaldi3_cmn_kernel(const FeKaldiParams p, int smem_rows) {
+    typedef FeK3Cfg C;
+    constexpr int HC = C::NMEL / 2, H4 = HC / 4;       // 40 columns = 10 float4 per row and CTA
+    extern __shared__ __align__(16) float tile[];      // [T][HC]
+    __shared__ float partial[8][HC];
+    __shared__ float mean[HC];
+    const int b = blockIdx.x >> 1, c0 = (blockIdx.x & 1) * HC;
+    const FeK3Unit t = fe_k3_unit_at(p, b, 0);
+    const int T = t.T;
+    if (T <= 0) return;
+    float* __restrict__ o = p.out + (int64_t)b * p.out_batch_stride + c0;
+    const bool in_smem = T <= smem_rows;
+    const bool vec = (p.vec_ok & 2) != 0;
+    const int tid = threadIdx.x;
+    const int n4 = T * H4;
+    if (in_smem) {
+        if (vec) {
+            // eight independent 16-byte loads per thread in flight (2 CTAs x 320 threads x 128 B = 80 KB per SM)
+            for (int i0 = tid; i0 < n4; i0 += 320 * 8) {
+                float4 v[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int i = i0 + 320 * k;
+                    if (i < n4) v[k] = __ldcs(reinterpret_cast<const float4*>(o + (int64_t)(i / H4) * C::NMEL) + i % H4);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int i = i0 + 320 * k;
+                    if (i < n4) reinterpret_cast<float4*>(tile)[i] = v[k];
+                }
+            }
+        } else {
+            for (int i = tid; i < T * HC; i += 320) tile[i] = __ldcs(o + (int64_t)(i / HC) * C::NMEL + i % HC);
+        }
+        __syncthreads();
+    }
+    const int m = tid % HC, rg = tid / HC;             // 8 row groups x 40 columns
+    float acc = 0.0f;
+    if (in_smem) for (int r = rg; r < T; r += 8) acc += tile[r * HC + m];
+    else for (int r = rg; r < T; r += 8) acc += __ldcg(o + (int64_t)r * C::NMEL + m);
+    partial[rg][m] = acc;
+    __syncthreads();
+    if (tid < HC)
+        mean[tid] = (((partial[0][tid] + partial[1][tid]) + (partial[2][tid] + partial[3][tid])) +
+                     ((partial[4][tid] + partial[5][tid]) + (partial[6][tid] + partial[7][tid]))) / (float)T;
+    __syncthreads();
+    if (vec) {
+        for (int i = tid; i < n4; i += 320) {
+            const int r = i / H4, q = i % H4;
+            float4* dst = reinterpret_cast<float4*>(o + (int64_t)r * C::NMEL) + q;
+            float4 v = in_smem ? reinterpret_cast<const float4*>(tile)[i] : __ldcg(dst);
+            v.x -= mean[4 * q]; v.y -= mean[4 * q + 1]; v.z -= mean[4 * q + 2]; v.w -= mean[4 * q + 3];
+            __stcs(dst, v);
+        }
+    } else {
+        for (int i = tid; i < T * HC; i += 320) {
+            float* dst = o + (int64_t)(i / HC) * C::NMEL + i % HC;
+            *dst = (in_smem ? tile[i] : __ldcg(dst)) - mean[i % HC];
+        }
+    }
+}
+
 static int tiles_per_cta_env(const char* name, int dflt) {
     const char* s = getenv(name);
     const int t = s ? atoi(s) : dflt;
@@ -833,6 +1045,41 @@ static bool whisper3_make_tmap(const float* wave, int64_t wave_stride, int64_t L
     *rows_out = (int32_t)rows;
     return true;
 }
+// the same kind of map for the kaldi kernel: rows start at sample 0 of the clip (snip_edges framing, no padding)
+static bool kaldi3_make_tmap(const float* wave, int64_t wave_stride, int64_t L, int32_t B, CUtensorMap* map, int32_t* rows_out) {
+    typedef FeK3Cfg C;
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) fn = nullptr;
+        return reinterpret_cast<EncodeFn>(fn);
+    }();
+    memset(map, 0, sizeof(*map));
+    *rows_out = 0;
+    if (!encode || getenv("B200FEAT_NO_TMAP")) return false;
+    const int64_t rows = L < C::PITCH ? 0 : (L - C::PITCH) / C::HOP + 1;      // rows whose 164 floats lie inside the clip's buffer
+    if (rows < C::ROWS || rows > 0x7fffffff || B < 1) return false;
+    cuuint64_t gdim[3] = {(cuuint64_t)C::PITCH, (cuuint64_t)rows, (cuuint64_t)B};
+    cuuint64_t gstr[2] = {(cuuint64_t)C::HOP * 4, (cuuint64_t)wave_stride * 4};
+    cuuint32_t box[3] = {(cuuint32_t)C::PITCH, (cuuint32_t)C::ROWS, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult rc = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(wave), gdim, gstr, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) return false;
+    *rows_out = (int32_t)rows;
+    return true;
+}
+// B200FEAT_KALDI_KERNEL=1 forces the shared-memory kernel of round 1 (A/B timing)
+static int kaldi_kernel_choice() {      // read per call: tests switch it inside one process
+    const char* s = getenv("B200FEAT_KALDI_KERNEL");
+    return s ? atoi(s) : 3;
+}
+static constexpr int FE_K3_CMN_SMEM_ROWS = 640;      // (T, 80) float32 tiles up to 6.4 s stay in shared memory (200 KB)
+
 // B200FEAT_WHISPER_KERNEL=2 forces the shared-memory frame-pair kernel (A/B timing, profiles/); default: the
 // Tensor-Memory kernel wherever it applies (float32 input, 16-byte aligned rows)
 static int whisper_kernel_choice() {
@@ -918,6 +1165,9 @@ int check_device_arch() {
             if (whisper3_smem_attr()) return fail(B200FEAT_ECUDA, "cudaFuncSetAttribute(fe_whisper3_kernel, max dynamic shared memory) failed");
             FE_CUDA(cudaDeviceGetAttribute(&g_num_sms[dev < 64 ? dev : 0], cudaDevAttrMultiProcessorCount, dev));
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeKCfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_kaldi3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeK3Cfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_kaldi3_cmn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         FE_K3_CMN_SMEM_ROWS * (FeK3Cfg::NMEL / 2) * 4));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
         }
     }
@@ -1250,6 +1500,38 @@ int b200feat_kaldi_fbank(const float* wave, const int64_t* lengths, int32_t B, i
     p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
     if (aligned16(out) && out_batch_stride % 4 == 0) p.vec_ok |= 2;
     p.colsum = workspace ? reinterpret_cast<float*>(reinterpret_cast<char*>(workspace) + 16) : nullptr;
+    {   // Tensor-Memory kernel wherever the waveform can be described by a tensor map (16-byte aligned rows, >= 34 hops)
+        const int64_t units3 = (T_out + FeK3Cfg::UF - 1) / FeK3Cfg::UF;
+        CUtensorMap tmap;
+        if ((p.vec_ok & 1) && kaldi_kernel_choice() != 1 && (int64_t)B * units3 <= 0x7fffffff &&
+            kaldi3_make_tmap(wave, wave_stride, L, B, &tmap, &p.tmap_rows)) {
+            int dev = 0;
+            FE_CUDA(cudaGetDevice(&dev));
+            const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
+            p.clip0 = 0; p.nclips = B;
+            p.units_per_clip = (int32_t)units3;
+            p.total_units = (int32_t)(B * units3);
+            // (CMN fused into this kernel -- a CTA takes whole clips and re-reads each from L2 after its last unit -- was
+            // measured: 1.47 ms per 4096 x 5 s against 1.38 ms with the separate kernel below, the CTA-wide L2 round trips
+            // per clip cost more than the second pass; it also made a clip's result depend on the batch it is in.)
+            const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
+            p.step_w = (int32_t)(grid / (unsigned)B); p.step_b = (int32_t)(grid % (unsigned)B);
+            {
+                ProfScope ps(st, 0);
+                fe_kaldi3_kernel<<<grid, FeK3Cfg::NT, FeK3Cfg::SMEM_BYTES, st>>>(p, tmap);
+                g_launches++;
+            }
+            if (subtract_mean) {
+                const int rows = (int)(T_out < FE_K3_CMN_SMEM_ROWS ? T_out : FE_K3_CMN_SMEM_ROWS);
+                const bool fits = T_out <= FE_K3_CMN_SMEM_ROWS;
+                ProfScope ps(st, 1);
+                fe_kaldi3_cmn_kernel<<<2u * (unsigned)B, 320, fits ? (size_t)rows * (FeK3Cfg::NMEL / 2) * 4 : 0, st>>>(p, fits ? rows : 0);
+                g_launches++;
+            }
+            FE_CUDA(cudaGetLastError());
+            return 0;
+        }
+    }
     const int64_t clip_bytes = (int64_t)FeKCfg::NMEL * T_out * 4;
     int64_t per_wave = l2_wave_bytes() / clip_bytes;
     if (per_wave < 1) per_wave = 1;

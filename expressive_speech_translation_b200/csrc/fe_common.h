@@ -183,6 +183,11 @@ struct FeKaldiParams {
     int32_t vec_ok;            // bit 0: wave float4-loadable, bit 1: out float4-storable
     float* colsum;             // workspace (B, tiles_per_clip, 80): per-tile column sums for CMN
     int32_t clip0, nclips;
+    // Tensor-Memory kernel (fe_kaldi3.cuh) only:
+    int32_t tmap_rows;         // rows per clip in the launch's tensor map
+    int32_t units_per_clip;    // ceil(T_out / 128)
+    int32_t total_units;       // B * units_per_clip
+    int32_t step_b, step_w;    // gridDim.x units = step_w unit positions + step_b clips
 };
 
 FE_HD FE_INLINE int64_t fe_clip_len(const int64_t* lengths, int b, int64_t L) {

@@ -32,6 +32,7 @@ def load():
     lib.emu_f2h.argtypes = [vp, vp, i64]
     lib.emu_f2h.restype = None
     lib.emu_kaldi.argtypes = [vp, vp, i32, i64, i64, i32, vp, i64]
+    lib.emu_kaldi3.argtypes = [vp, vp, i32, i64, i64, i32, vp, i64]
     lib.emu_cosy.argtypes = [vp, vp, i32, i64, i64, vp, i64]
     f64 = ctypes.c_double
     lib.emu_resample.argtypes = [vp, i32, i32, vp, vp, i32, i64, i32, i32, i32, f64, i32, f64, vp, i64, vp]

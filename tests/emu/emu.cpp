@@ -235,6 +235,75 @@ extern "C" int emu_kaldi(const float* wave, const int64_t* lengths, int B, int64
     return 0;
 }
 
+// Tensor-Memory kaldi kernel (fe_kaldi3.cuh): box copy + patch, row sums, phases A / B / M in the order the mbarriers
+// enforce on the GPU, then the CMN kernel's arithmetic (4 row groups per column, fixed order)
+#include "fe_kaldi3.cuh"
+extern "C" int emu_kaldi3(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                          int subtract_mean, float* out, int64_t T_out) {
+    typedef FeK3Cfg C;
+    FeKaldiParams p;
+    memset(&p, 0, sizeof(p));
+    p.wave = wave; p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B;
+    p.subtract_mean = subtract_mean; p.out = out; p.out_batch_stride = T_out * 80; p.T_out = T_out;
+    p.vec_ok = ((((uintptr_t)wave & 15) == 0) && (stride % 4 == 0)) ? 1 : 0;
+    if ((((uintptr_t)out & 15) == 0) && (p.out_batch_stride % 4 == 0)) p.vec_ok |= 2;
+    const int64_t rows = L < C::PITCH ? 0 : (L - C::PITCH) / C::HOP + 1;
+    if (!(p.vec_ok & 1) || rows < C::ROWS) return -2;      // the library falls back to the shared-memory kernel
+    p.tmap_rows = (int)rows;
+    p.units_per_clip = (int)((T_out + C::UF - 1) / C::UF);
+    p.total_units = B * p.units_per_clip;
+    std::vector<float> sm(C::SMEM_FLOATS, 0.0f);
+    std::vector<float> tmem((size_t)C::TEAMS * 32 * C::TMEM_COLS, 0.0f);
+    fe_k3_copy_tables(sm.data(), 0, 1);
+    float* P = sm.data() + C::OFF_P;
+    for (int u = 0; u < p.total_units; ++u) {
+        const FeK3Unit t = fe_k3_unit(p, u);
+        if (!(t.t0 < t.T)) {
+            for (int w = 0; w < C::NW; ++w) for (int l = 0; l < 32; ++l) fe_k3_zero_unit(p, t, l, w);
+            continue;
+        }
+        for (int q = 0; q < C::TEAMS; ++q) {
+            if (!fe_k3_team_live(t, q)) continue;
+            float* wq = sm.data() + C::OFF_W + q * C::WT;
+            float* part = sm.data() + C::OFF_PART + q * C::PARTS * C::PARTW;
+            fe_k3_box_host(p, t, q, wq);
+            if (!fe_k3_box_complete(p, t, q))
+                for (int m = 0; m < C::MEMBERS; ++m) for (int l = 0; l < 32; ++l) fe_k3_patch_rows(p, t, q, wq, m, l);
+            {   // pre-pass: every thread of the team loads, (team barrier), every thread stores
+                std::vector<FeK3Pre> regs(C::MEMBERS * 32);
+                for (int m = 0; m < C::MEMBERS; ++m) for (int l = 0; l < 32; ++l) fe_k3_pre_load(wq, m, l, regs[m * 32 + l]);
+                for (int m = 0; m < C::MEMBERS; ++m) for (int l = 0; l < 32; ++l) fe_k3_pre_store(wq, part, m, l, regs[m * 32 + l]);
+            }
+            for (int m = 0; m < C::MEMBERS; ++m)
+                for (int k = 0; k < 2; ++k)
+                    for (int l = 0; l < 32; ++l) {
+                        FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
+                        fe_k3_stage_a(wq, tm, l, 2 * m + k, fe_k3_frame_mean(part, l), fe_k3_frame_x0(part, l), FeNoHook());
+                    }
+            for (int m = 0; m < C::MEMBERS; ++m)
+                for (int k = 0; k < fe_k3_b_count(m); ++k)
+                    for (int l = 0; l < 32; ++l) {
+                        FeTm tm; tm.row = tmem.data() + ((size_t)q * 32 + l) * C::TMEM_COLS;
+                        fe_k3_stage_b(P, tm, l, q, fe_k3_b_task(m, k), FeNoHook(), FeNoHook());
+                    }
+        }
+        for (int w = 0; w < C::NW; ++w) for (int l = 0; l < 32; ++l) fe_k3_phase_mel(p, t, sm.data(), l, w);
+    }
+    if (subtract_mean) {
+        for (int b = 0; b < B; ++b) {
+            const int T = fe_k3_unit_at(p, b, 0).T;
+            float* o = out + (int64_t)b * p.out_batch_stride;
+            for (int m = 0; m < 80 && T > 0; ++m) {
+                float part[8] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+                for (int r = 0; r < T; ++r) part[r & 7] += o[(int64_t)r * 80 + m];
+                const float mean = (((part[0] + part[1]) + (part[2] + part[3])) + ((part[4] + part[5]) + (part[6] + part[7]))) / (float)T;
+                for (int r = 0; r < T; ++r) o[(int64_t)r * 80 + m] -= mean;
+            }
+        }
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------ cosy
 #include "fe_cosy.cuh"
 extern "C" int emu_cosy(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,

@@ -250,3 +250,51 @@ def test_whisper3_f16_output_is_the_rounded_f32_output(emu):
         f32 = emu_whisper3(emu, x, nm, lengths=[30000, 17001])
         f16 = emu_whisper3(emu, x, nm, lengths=[30000, 17001], f16=True)
         assert np.array_equal(f16, f32.astype(np.float16))
+
+
+# ------------------------------------------------------------------------------------------------ Tensor-Memory kaldi kernel
+def emu_kaldi3(emu, x, cmn=1, lengths=None, T_out=None):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    T = 1 + (L - 400) // 160 if T_out is None else T_out
+    out = np.full((B, T, 80), 7.0, dtype=np.float32)
+    keep, lp = _lens(lengths)
+    assert emu.emu_kaldi3(x.ctypes.data_as(vp), lp, B, L, L, cmn, out.ctypes.data_as(vp), T) == 0
+    return out
+
+
+@pytest.mark.parametrize("B,L", [(2, 16000), (1, 80000), (3, 5444), (2, 23456)])
+def test_kaldi3(emu, B, L):
+    x = (0.1 * torch.randn(B, L, generator=torch.Generator().manual_seed(L))).clamp(-1, 1)
+    kaldi_check(emu_kaldi3(emu, x.numpy(), cmn=0), x, f"kaldi3 {B}x{L}")
+    got = emu_kaldi3(emu, x.numpy(), cmn=1)
+    for b in range(B):
+        ref = oracle.kaldi_fbank(x[b], subtract_mean=True, dtype=torch.float64).numpy()
+        raw = oracle.kaldi_fbank(x[b], subtract_mean=False, dtype=torch.float64).numpy()
+        raw32 = oracle.kaldi_fbank(x[b], subtract_mean=False).numpy()
+        assert np.abs(got[b] - ref).max() <= oracle.kaldi_log_tolerance(raw32, raw)
+    # the two formulations (same codelets for N = 512 = 32 x 16, other summation orders) differ by at most the sum of
+    # their distances to fp64 -- near-empty bins carry a few 1e-4 each (oracle.kaldi_log_tolerance)
+    a, c = emu_kaldi3(emu, x.numpy(), cmn=0), emu_kaldi(emu, x.numpy(), cmn=0)
+    for b in range(B):
+        raw = oracle.kaldi_fbank(x[b], subtract_mean=False, dtype=torch.float64).numpy()
+        raw32 = oracle.kaldi_fbank(x[b], subtract_mean=False).numpy()
+        assert np.abs(a[b] - c[b]).max() <= 2 * oracle.kaldi_log_tolerance(raw32, raw)
+
+
+def test_kaldi3_speech_zeros_ragged(emu):
+    gen = torch.Generator().manual_seed(21)
+    x = speech_like(gen, 2, 40000, 16000)
+    kaldi_check(emu_kaldi3(emu, x.numpy(), cmn=0), x, "kaldi3 speech")
+    z = emu_kaldi3(emu, np.zeros((1, 8000), np.float32), cmn=0)
+    assert np.allclose(z, np.log(1.1920928955078125e-07))
+    assert np.abs(emu_kaldi3(emu, np.zeros((1, 8000), np.float32), cmn=1)).max() < 1e-5
+    lens = [40000, 12345]
+    got = emu_kaldi3(emu, x.numpy(), cmn=0, lengths=lens)
+    T1 = 1 + (12345 - 400) // 160
+    ref = oracle.kaldi_fbank(x[1, :12345], subtract_mean=False, dtype=torch.float64).numpy()
+    assert np.abs(got[1, :T1] - ref).max() <= 5e-4 and not got[1, T1:].any()
+    kaldi_check(got[:1], x[:1], "kaldi3 ragged clip 0")
+    # T_out larger than any clip's frame count (rows of a longer batch buffer): whole dead units are zero-filled
+    got = emu_kaldi3(emu, x.numpy()[:, :6000], cmn=1, T_out=300)
+    assert not got[:, 1 + (6000 - 400) // 160:].any()

@@ -286,6 +286,73 @@ def gen_melloop(name, filt, nch, caps, n_bins=200, emit_cost=17, chunk_weight=No
     return "\n".join(out) + "\n"
 
 
+def gen_mel_segments(name, filt, nwarps, group=4, extra_load=None):
+    """tables for the segment form of a triangular filter bank in which every bin feeds at most two ADJACENT filters
+    (kaldi's mel banks).  Segment j (j = -1 .. n_mels - 1) = the bins whose lowest non-zero filter is j; in it filter j
+    falls (weight wf) and filter j + 1 rises (weight wr).  A lane accumulates `group` consecutive filters at a time:
+    group g = filters group * g .. + group - 1 scans segments group * g - 1 .. group * g + group - 1.
+      name_seg[j + 1]  = first bin of segment j (j = -1 .. n_mels; entry n_mels + 1 = end)
+      name_w[2 * k]    = (wf, wr) of bin k
+      name_groups[2 * w], [2 * w + 1] = the (at most two) groups warp w handles, -1 = none; longest-processing-time
+                         assignment on the cost model bins * 6 + 44 per group (+ extra_load[w])."""
+    n_mels, n_bins = filt.shape
+    seg_of = np.full(n_bins, -2, dtype=np.int64)
+    w2 = np.zeros((n_bins, 2), dtype=np.float64)
+    for k in range(n_bins):
+        nz = np.nonzero(filt[:, k])[0]
+        assert len(nz) <= 2, "a bin feeds more than two filters"
+        if len(nz) == 0:
+            continue
+        j = int(nz[0])
+        if len(nz) == 2:
+            assert nz[1] == j + 1, "the two filters of a bin must be adjacent"
+            w2[k] = (filt[j, k], filt[j + 1, k])
+        else:
+            w2[k] = (filt[j, k], 0.0)
+        seg_of[k] = j
+    live = np.nonzero(seg_of > -2)[0]
+    # bins of a segment are contiguous and segments ascend; bins before the first live one / dead gaps carry zero weights
+    first = int(live[0])
+    for k in range(first, n_bins):
+        if seg_of[k] == -2:
+            seg_of[k] = seg_of[k - 1]
+    assert np.all(np.diff(seg_of[first:]) >= 0)
+    seg = np.zeros(n_mels + 2, dtype=np.int64)            # seg[j + 1] = first bin of segment j
+    for j in range(-1, n_mels + 1):
+        ks = np.nonzero(seg_of[first:] >= j)[0]
+        seg[j + 1] = first + int(ks[0]) if len(ks) else n_bins
+    # rising part of filter 0 (segment -1) is empty when its left edge lies below the first live bin: fine
+    # check: rebuilding the matrix from the tables gives the matrix
+    chk = np.zeros_like(filt, dtype=np.float64)
+    for j in range(-1, n_mels):
+        for k in range(seg[j + 1], seg[j + 2]):
+            if j >= 0:
+                chk[j, k] += w2[k, 0]
+            if j + 1 < n_mels:
+                chk[j + 1, k] += w2[k, 1] if seg_of[k] == j else 0.0
+    assert np.array_equal(chk.astype(np.float32), filt.astype(np.float32)), "segment tables do not reproduce the filter bank"
+    ngroups = n_mels // group
+    assert ngroups * group == n_mels
+    cost = [6 * int(seg[group * gi + group + 1] - seg[group * gi]) + 44 for gi in range(ngroups)]
+    load = list(extra_load) if extra_load is not None else [0.0] * nwarps
+    slots = [[] for _ in range(nwarps)]
+    for gi in sorted(range(ngroups), key=lambda q: -cost[q]):
+        cand = [w for w in range(nwarps) if len(slots[w]) < 2]
+        w = min(cand, key=lambda q: load[q])
+        slots[w].append(gi)
+        load[w] += cost[gi]
+    groups = []
+    for w in range(nwarps):
+        groups += sorted(slots[w]) + [-1] * (2 - len(slots[w]))
+    out = [f"// segment tables of a {n_mels}-filter bank over {n_bins} bins ({int(np.count_nonzero(filt))} non-zeros); groups of {group} filters; "
+           f"per-warp cost {min(load):.0f} .. {max(load):.0f}",
+           f"#define {name.upper()}_GROUP {group}",
+           emit_array(name + "_seg", seg, per_line=16, ctype="int"),
+           emit_array(name + "_w", w2).replace("FE_CONSTANT float", "FE_CONSTANT __attribute__((aligned(8))) float"),
+           emit_array(name + "_groups", np.array(groups, dtype=np.int64), per_line=16, ctype="int")]
+    return "\n".join(out) + "\n"
+
+
 def gen_melrolled(name, filt, n_bins):
     """tables for the rolled mel projection of the one-frame-per-lane kernels (kaldi, CosyVoice): per filter
     name_desc[3*m] = first tap k0, [3*m+1] = taps padded to a multiple of 4, [3*m+2] = offset of its weights in
@@ -399,6 +466,25 @@ def main():
     share3 = [1.0] * 16
     tb.append(gen_melloop("fe_melloop3_w80", w80, 16, (2, 3, 4, 6, 8, 11, 14), chunk_weight=share3, k0_scale=512, emit_cost=22, by_class=True))
     tb.append(gen_melloop("fe_melloop3_w128", w128, 16, (1, 2, 3, 4, 6, 7, 9), chunk_weight=share3, k0_scale=512, emit_cost=22, by_class=True))
+    # ---- Tensor-Memory kaldi kernel (fe_kaldi3.cuh): N = 512 = 32 (n1) x 16 (n2), half-unit hu = sub-sequences 2 hu, 2 hu + 1
+    wk = (0.5 - 0.5 * np.cos(2 * np.pi * np.arange(400, dtype=np.float64) / 399.0)) ** 0.85
+    k3win = np.zeros((8, 25, 2))
+    k3tw = np.zeros((8, 15, 4))
+    for hu in range(8):
+        for n1 in range(25):
+            for c in range(2):
+                k3win[hu, n1, c] = wk[16 * n1 + 2 * hu + c]
+        for k1 in range(1, 16):
+            for c in range(2):
+                wr, wi = g.twiddle((2 * hu + c) * k1, 512)
+                k3tw[hu, k1 - 1, c] = wr
+                k3tw[hu, k1 - 1, 2 + c] = wi
+    tb.append("// kaldi (Tensor-Memory kernel) phase-A constants: povey window pairs [hu][n1][c], twiddles W_512^((2 hu + c) k1) as "
+              "[hu][k1 - 1][wr_c0, wr_c1, wi_c0, wi_c1], and W_512^(16 n2) as [n2][re, im] (applied in phase B)")
+    tb.append(emit_array("fe_k3_win", k3win).replace("FE_CONSTANT float", "FE_CONSTANT __attribute__((aligned(16))) float"))
+    tb.append(emit_array("fe_k3_tw", k3tw).replace("FE_CONSTANT float", "FE_CONSTANT __attribute__((aligned(16))) float"))
+    tb.append(emit_array("fe_k3_tw16", np.array([g.twiddle(16 * n2, 512) for n2 in range(16)])))
+    tb.append(gen_mel_segments("fe_k3_mel", kb[:, :256], 16))
     tb.append(gen_melrolled("fe_melroll_cosy", cz, 640))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
