@@ -1159,8 +1159,11 @@ int check_device_arch() {
     if (state[dev] == 0) {
         int major = 0;
         FE_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
-        state[dev] = (major == 10) ? 1 : -1;
-        if (state[dev] == 1) {
+        if (major != 10) {
+            state[dev] = -1;
+        } else {
+            // state stays 0 until every attribute call succeeded: a failure here is reported now AND retried by the next
+            // call (it used to be latched as "ok", and later launches failed with an opaque "invalid argument")
             if (whisper2_smem_attr()) return fail(B200FEAT_ECUDA, "cudaFuncSetAttribute(fe_whisper2_kernel, max dynamic shared memory) failed");
             if (whisper3_smem_attr()) return fail(B200FEAT_ECUDA, "cudaFuncSetAttribute(fe_whisper3_kernel, max dynamic shared memory) failed");
             FE_CUDA(cudaDeviceGetAttribute(&g_num_sms[dev < 64 ? dev : 0], cudaDevAttrMultiProcessorCount, dev));
@@ -1169,6 +1172,7 @@ int check_device_arch() {
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi3_cmn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          FE_K3_CMN_SMEM_ROWS * (FeK3Cfg::NMEL / 2) * 4));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
+            state[dev] = 1;
         }
     }
     if (state[dev] != 1) return fail(B200FEAT_EARCH, "device %d is not compute capability 10.x (sm_100a build)", dev);
@@ -1609,11 +1613,17 @@ int rs_get_plan(int orig_freq, int new_freq, int lpfw, double rolloff, int metho
         delete dp;
         return rc;
     }
-    // first call for this filter only: the table upload is synchronous
-    FE_CUDA(cudaMalloc(&dp->taps, dp->plan.taps.size() * sizeof(float)));
-    FE_CUDA(cudaMalloc(&dp->kstart, dp->plan.kstart.size() * sizeof(int32_t)));
-    FE_CUDA(cudaMemcpy(dp->taps, dp->plan.taps.data(), dp->plan.taps.size() * sizeof(float), cudaMemcpyHostToDevice));
-    FE_CUDA(cudaMemcpy(dp->kstart, dp->plan.kstart.data(), dp->plan.kstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    // first call for this filter only: the table upload is synchronous.  Nothing leaks when a step fails.
+    cudaError_t e = cudaMalloc(&dp->taps, dp->plan.taps.size() * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&dp->kstart, dp->plan.kstart.size() * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMemcpy(dp->taps, dp->plan.taps.data(), dp->plan.taps.size() * sizeof(float), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dp->kstart, dp->plan.kstart.data(), dp->plan.kstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        if (dp->taps) cudaFree(dp->taps);
+        if (dp->kstart) cudaFree(dp->kstart);
+        delete dp;
+        return fail(B200FEAT_ECUDA, "resample: uploading the tap table failed: %s", cudaGetErrorString(e));
+    }
     g_rs_plans[key] = dp;
     *out = dp;
     return 0;

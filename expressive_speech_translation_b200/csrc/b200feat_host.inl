@@ -5,28 +5,61 @@ namespace {
 
 constexpr int NSLOT = 4;
 
+// One Arena = a device buffer + NSLOT streams, used by ONE host call at a time.  Calls lease an arena from the device's
+// pool and give it back when they are done: concurrent calls (Flask runs threaded=True, /root/reference/Backend/app.py:523)
+// get different arenas and overlap on the GPU instead of queueing behind one whole-call lock; the pool only grows with
+// the number of calls that are really in flight at once.
 struct Arena {
-    std::mutex mu;
     int dev = -1;
     char* base = nullptr;
     size_t bytes = 0;
     cudaStream_t streams[NSLOT] = {nullptr, nullptr, nullptr, nullptr};
     bool streams_ok = false;
 };
+struct ArenaPool {
+    std::mutex mu;                 // held only while an arena is taken from / returned to the lists
+    std::vector<Arena*> idle, all;
+};
 
-std::mutex g_arenas_mu;
-std::vector<Arena*> g_arenas;  // index = device ordinal
+std::mutex g_pools_mu;
+std::vector<ArenaPool*> g_pools;   // index = device ordinal
 
-Arena* arena_for(int dev) {
-    std::lock_guard<std::mutex> lk(g_arenas_mu);
-    if ((int)g_arenas.size() <= dev) g_arenas.resize(dev + 1, nullptr);
-    if (!g_arenas[dev]) {
-        g_arenas[dev] = new Arena();
-        g_arenas[dev]->dev = dev;
-    }
-    return g_arenas[dev];
+ArenaPool* pool_for(int dev) {
+    std::lock_guard<std::mutex> lk(g_pools_mu);
+    if ((int)g_pools.size() <= dev) g_pools.resize(dev + 1, nullptr);
+    if (!g_pools[dev]) g_pools[dev] = new ArenaPool();
+    return g_pools[dev];
 }
 
+// the idle arena with the largest buffer, or a new one
+Arena* arena_lease(int dev) {
+    ArenaPool* pool = pool_for(dev);
+    std::lock_guard<std::mutex> lk(pool->mu);
+    if (!pool->idle.empty()) {
+        size_t best = 0;
+        for (size_t i = 1; i < pool->idle.size(); ++i)
+            if (pool->idle[i]->bytes > pool->idle[best]->bytes) best = i;
+        Arena* a = pool->idle[best];
+        pool->idle.erase(pool->idle.begin() + best);
+        return a;
+    }
+    Arena* a = new Arena();
+    a->dev = dev;
+    pool->all.push_back(a);
+    return a;
+}
+void arena_return(Arena* a) {
+    ArenaPool* pool = pool_for(a->dev);
+    std::lock_guard<std::mutex> lk(pool->mu);
+    pool->idle.push_back(a);
+}
+struct ArenaLease {
+    Arena* a;
+    explicit ArenaLease(int dev) : a(arena_lease(dev)) {}
+    ~ArenaLease() { arena_return(a); }
+};
+
+// the arena is leased: its streams are idle (every call synchronises them before it returns the arena)
 int arena_reserve(Arena* a, size_t need) {
     if (!a->streams_ok) {
         for (int i = 0; i < NSLOT; ++i) FE_CUDA(cudaStreamCreateWithFlags(&a->streams[i], cudaStreamNonBlocking));
@@ -34,7 +67,6 @@ int arena_reserve(Arena* a, size_t need) {
     }
     if (a->bytes >= need) return 0;
     if (a->base) {
-        FE_CUDA(cudaDeviceSynchronize());
         FE_CUDA(cudaFree(a->base));
         a->base = nullptr;
         a->bytes = 0;
@@ -70,8 +102,8 @@ int host_pipeline(int kind, const void* wave_host_v, int64_t in_esz, const int64
     FE_CUDA(cudaGetDevice(&prev));
     if (device < 0) device = prev;
     FE_CUDA(cudaSetDevice(device));
-    Arena* a = arena_for(device);
-    std::lock_guard<std::mutex> lk(a->mu);
+    ArenaLease lease(device);
+    Arena* a = lease.a;
 
     const int64_t in_bytes = L * in_esz, out_bytes = out_per_clip * out_esz;
     int64_t chunk = host_chunk_bytes() / (in_bytes + out_bytes);
@@ -163,18 +195,20 @@ int b200feat_kaldi_fbank_host(const float* wave_host, const int64_t* lengths_hos
                          });
 }
 
-void b200feat_release(void) {
-    std::lock_guard<std::mutex> lk(g_arenas_mu);
-    for (Arena* a : g_arenas) {
-        if (!a) continue;
-        std::lock_guard<std::mutex> lk2(a->mu);
+void b200feat_release(void) {      // frees every IDLE arena (arenas leased by calls in flight are left alone)
+    std::lock_guard<std::mutex> lk(g_pools_mu);
+    for (ArenaPool* pool : g_pools) {
+        if (!pool) continue;
+        std::lock_guard<std::mutex> lk2(pool->mu);
         int prev = 0;
         if (cudaGetDevice(&prev) != cudaSuccess) continue;
-        cudaSetDevice(a->dev);
-        if (a->base) { cudaFree(a->base); a->base = nullptr; a->bytes = 0; }
-        if (a->streams_ok) {
-            for (int i = 0; i < NSLOT; ++i) cudaStreamDestroy(a->streams[i]);
-            a->streams_ok = false;
+        for (Arena* a : pool->idle) {
+            cudaSetDevice(a->dev);
+            if (a->base) { cudaFree(a->base); a->base = nullptr; a->bytes = 0; }
+            if (a->streams_ok) {
+                for (int i = 0; i < NSLOT; ++i) cudaStreamDestroy(a->streams[i]);
+                a->streams_ok = false;
+            }
         }
         cudaSetDevice(prev);
     }

@@ -29,7 +29,12 @@
  *     stream); the library never synchronises the device in the device-pointer entry points.
  *   - every function returns 0 on success and a negative B200FEAT_E* code otherwise;
  *     b200feat_last_error() returns a thread-local description of the last failure.
- *   - reentrant and thread-safe: no global mutable scratch; constant tables live in the module image.
+ *   - reentrant and thread-safe.  Device-pointer entry points keep no mutable state of their own (scratch = the
+ *     caller's workspace; constant tables live in the module image) -- the one exception is
+ *     b200feat_whisper_logmel_noalloc, whose static scratch array is shared by all calls on a GPU (see there).
+ *     The *_host entry points lease a staging arena (device buffer + streams) per call from a per-device pool, so
+ *     concurrent calls overlap; pageable host buffers are accepted (the driver stages them: measured penalty in
+ *     DESIGN.md), pinned ones run at PCIe speed.
  */
 #ifndef B200FEAT_H
 #define B200FEAT_H
