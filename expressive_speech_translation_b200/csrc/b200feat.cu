@@ -438,7 +438,7 @@ static __device__ __forceinline__ void fe_w3_prefetch_l2(const FeWhisper2Params&
 //             arrive PFULL(it)
 // A warp arrives on phase k of a barrier only after it has waited for phase k-1 of it (where it waits at all), so no
 // barrier can run two phases ahead of a waiter (parity waits would alias).
-template <int NMELS, bool OUT16>
+template <int NMELS, bool OUT16, bool PAD>
 __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhisper2Params p, const __grid_constant__ CUtensorMap tmap) {
     typedef FeW3Cfg C;
     extern __shared__ __align__(1024) float sm3[];
@@ -485,9 +485,9 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
     FeW3Pos pos;
     pos.within = u0 / p.B; pos.b = u0 - pos.within * p.B;      // the one division of the kernel
     if (member == 1 && n_it > 0) {
-        fe_w3_request_w(p, &tmap, fe_w3_unit_at(p, pos.b, pos.within), team, wq, sy.wfull, lane);
+        fe_w3_request_w(p, &tmap, fe_w3_unit_at<false, PAD>(p, pos.b, pos.within), team, wq, sy.wfull, lane);
         const FeW3Pos p1 = fe_w3_pos_next(p, pos);
-        if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit_at(p, p1.b, p1.within), team, lane);
+        if (n_it > 1) fe_w3_prefetch_l2(p, fe_w3_unit_at<false, PAD>(p, p1.b, p1.within), team, lane);
     }
     FeW3Unit prev;
     memset(&prev, 0, sizeof(prev));
@@ -500,7 +500,7 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
         FE_T3(it, 0);
         // ---- A(it)
         if (has) {
-            cur = fe_w3_unit_at(p, pos.b, pos.within);
+            cur = fe_w3_unit_at<false, PAD>(p, pos.b, pos.within);
             live = fe_w3_team_live(cur, team);
             fe_mbar_wait_bounded(sy.wfull, par);
             FE_T3(it, 1);
@@ -536,8 +536,8 @@ __global__ void __launch_bounds__(FeW3Cfg::NT, 1) fe_whisper3_kernel(const FeWhi
                 last = __shfl_sync(0xffffffffu, last, 0);
                 if (last) {
                     const FeW3Pos p1 = fe_w3_pos_next(p, pos), p2 = fe_w3_pos_next(p, p1);
-                    if (it + 1 < n_it) fe_w3_request_w(p, &tmap, fe_w3_unit_at(p, p1.b, p1.within), team, wq, sy.wfull, lane);
-                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit_at(p, p2.b, p2.within), team, lane);
+                    if (it + 1 < n_it) fe_w3_request_w(p, &tmap, fe_w3_unit_at<false, PAD>(p, p1.b, p1.within), team, wq, sy.wfull, lane);
+                    if (it + 2 < n_it) fe_w3_prefetch_l2(p, fe_w3_unit_at<false, PAD>(p, p2.b, p2.within), team, lane);
                 }
             }
         }
@@ -594,6 +594,48 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
     __shared__ int list[256];
     __shared__ int count;
     const int2* __restrict__ ukeys = reinterpret_cast<const int2*>(p.unit_minmax);
+    const bool plain = p.win_frames == 0;
+    if (plain) {
+        // The tail of every clip: whole units of padding (the kernel skipped them; their value is the clip's threshold)
+        // and whole units behind the clip's last frame (0).  Written as contiguous runs along the output rows, one
+        // (clip, 16 rows) item per CTA pass, one row per warp: unit by unit (512 bytes every 4 * T_out bytes) the same
+        // bytes went out at 3 TB/s, profiles/r02_bench_realistic.txt.
+        constexpr int GROWS = 16, NG = (NMELS + GROWS - 1) / GROWS;
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        const bool vec = (p.vec_ok & 2) && (p.T_out & 3) == 0;
+        for (int w = blockIdx.x; w < p.B * NG; w += gridDim.x) {
+            const int b = w / NG, g = w - b * NG;
+            int64_t Tc;
+            const int64_t f0 = fe_w3_tail_start(p, b, &Tc);
+            if (f0 >= p.T_out) continue;
+            const float thr = f0 < Tc ? fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : b])) : 0.0f;
+            const unsigned short thr_h = fe_f2h_rn(thr);
+            for (int m = g * GROWS + warp; m < NMELS && m < (g + 1) * GROWS; m += 8) {
+                const int64_t row = (int64_t)b * p.out_batch_stride + (int64_t)m * p.T_out;
+                if (OUT16) {
+                    unsigned short* __restrict__ q = reinterpret_cast<unsigned short*>(p.out) + row;
+                    if (vec) {
+                        for (int64_t f = f0 + 4 * lane; f < p.T_out; f += 128) {
+                            const unsigned a0 = f < Tc ? thr_h : 0u, a1 = f + 1 < Tc ? thr_h : 0u;
+                            const unsigned a2 = f + 2 < Tc ? thr_h : 0u, a3 = f + 3 < Tc ? thr_h : 0u;
+                            *reinterpret_cast<uint2*>(q + f) = make_uint2(a0 | (a1 << 16), a2 | (a3 << 16));
+                        }
+                    } else {
+                        for (int64_t f = f0 + lane; f < p.T_out; f += 32) q[f] = f < Tc ? thr_h : (unsigned short)0;
+                    }
+                } else {
+                    float* __restrict__ q = reinterpret_cast<float*>(p.out) + row;
+                    if (vec) {
+                        for (int64_t f = f0 + 4 * lane; f < p.T_out; f += 128)
+                            *reinterpret_cast<float4*>(q + f) = make_float4(f < Tc ? thr : 0.0f, f + 1 < Tc ? thr : 0.0f,
+                                                                            f + 2 < Tc ? thr : 0.0f, f + 3 < Tc ? thr : 0.0f);
+                    } else {
+                        for (int64_t f = f0 + lane; f < p.T_out; f += 32) q[f] = f < Tc ? thr : 0.0f;
+                    }
+                }
+            }
+        }
+    }
     // unit u is checked by CTA u % gridDim.x: neighbouring units (the same position of neighbouring clips, which tend to
     // need the clamp together -- clip starts, silent stretches) go to DIFFERENT CTAs, so the rewrites spread over the
     // whole GPU.  (With contiguous blocks of units per CTA the 37 flagged units of the noise bench sat in a few CTAs
@@ -603,18 +645,19 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
         __syncthreads();
         const int u = base + (int)threadIdx.x * (int)gridDim.x + (int)blockIdx.x;
         if (u < p.total_units) {
-            const FeW3Unit t = fe_w3_unit(p, u);
+            const FeW3Unit t = fe_w3_unit<true>(p, u);
             const int n_in = t.n_in;
             const int n_live = t.Ts - t.t0;
             const float umin = -fe_key_float(ukeys[u].y);
             const float thr = fe_w2_threshold(fe_key_float(p.max_keys[p.norm_mode == FE_NORM_PER_CALL ? 0 : t.b]));
-            if ((n_live > 0 && umin < thr) || n_live < n_in) list[atomicAdd(&count, 1)] = u;
+            const bool in_tail = plain && (t.silent || n_live <= 0);       // written above, as part of a row run
+            if (!in_tail && (t.silent || (n_live > 0 && umin < thr) || n_live < n_in)) list[atomicAdd(&count, 1)] = u;
         }
         __syncthreads();
         const int n = count;
         for (int j = 0; j < n; ++j) {
             const int uu = list[j];
-            const FeW3Unit t = fe_w3_unit(p, uu);
+            const FeW3Unit t = fe_w3_unit<true>(p, uu);
             const int n_in = t.n_in;
             int n_live = t.Ts - t.t0;
             n_live = n_live < 0 ? 0 : (n_live > n_in ? n_in : n_live);
@@ -624,12 +667,31 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
             const bool clampu = n_live > 0 && umin < thr;
             constexpr int RSTEP = 256 / C::UF;
             const int c = threadIdx.x % C::UF, m0 = threadIdx.x / C::UF;
-            if (c < n_in) {
+            if ((p.vec_ok & 2) && (pitch & 3) == 0 && n_in == C::UF && ((t.silent && n_live == C::UF) || n_live == 0)) {
+                // a whole unit of padding, or a whole unit behind the clip's last frame: (n_mels x 128) times the
+                // threshold, or 0 -- 16 bytes (8 for float16) per thread and row
+                const int c4 = 4 * (threadIdx.x & 31), r0 = threadIdx.x >> 5;
+                const float fill = n_live == 0 ? 0.0f : thr;
+                if (OUT16) {
+                    const unsigned h = fe_f2h_rn(fill);
+                    const uint2 v = make_uint2(h | (h << 16), h | (h << 16));
+                    __half* __restrict__ q0 = reinterpret_cast<__half*>(p.out) + t.o0 + c4;
+#pragma unroll 4
+                    for (int m = r0; m < NMELS; m += 8) *reinterpret_cast<uint2*>(q0 + (int64_t)m * pitch) = v;
+                } else {
+                    const float4 v = make_float4(fill, fill, fill, fill);
+                    float* __restrict__ q0 = reinterpret_cast<float*>(p.out) + t.o0 + c4;
+#pragma unroll 4
+                    for (int m = r0; m < NMELS; m += 8) *reinterpret_cast<float4*>(q0 + (int64_t)m * pitch) = v;
+                }
+            } else if (c < n_in) {
                 if (OUT16) {
                     __half* __restrict__ q0 = reinterpret_cast<__half*>(p.out) + t.o0 + c;
                     const __half thr_h = __ushort_as_half(fe_f2h_rn(thr));
                     if (c >= n_live) {
                         for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * pitch] = __ushort_as_half(0);
+                    } else if (t.silent) {
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * pitch] = thr_h;
                     } else if (clampu) {
                         for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
                             __half v[8];
@@ -649,6 +711,8 @@ __global__ void __launch_bounds__(256) fe_whisper3_fixup_kernel(const FeWhisper2
                     float* __restrict__ q0 = reinterpret_cast<float*>(p.out) + t.o0 + c;
                     if (c >= n_live) {
                         for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * pitch] = 0.0f;
+                    } else if (t.silent) {
+                        for (int m = m0; m < NMELS; m += RSTEP) q0[(int64_t)m * pitch] = thr;
                     } else if (clampu) {
                         for (int mb = m0; mb < NMELS; mb += 8 * RSTEP) {
                             float v[8];
@@ -995,10 +1059,14 @@ static void launch_whisper2(int n_mels, bool out16, bool in16, unsigned grid, cu
 typedef void (*FeW3Kernel)(const FeWhisper2Params, const CUtensorMap);
 template <class F>
 static int whisper3_for_each(F f) {
-    if (int rc = f(fe_whisper3_kernel<80, false>, 0)) return rc;
-    if (int rc = f(fe_whisper3_kernel<80, true>, 1)) return rc;
-    if (int rc = f(fe_whisper3_kernel<128, false>, 2)) return rc;
-    if (int rc = f(fe_whisper3_kernel<128, true>, 3)) return rc;
+    if (int rc = f(fe_whisper3_kernel<80, false, false>, 0)) return rc;
+    if (int rc = f(fe_whisper3_kernel<80, true, false>, 1)) return rc;
+    if (int rc = f(fe_whisper3_kernel<128, false, false>, 2)) return rc;
+    if (int rc = f(fe_whisper3_kernel<128, true, false>, 3)) return rc;
+    if (int rc = f(fe_whisper3_kernel<80, false, true>, 4)) return rc;
+    if (int rc = f(fe_whisper3_kernel<80, true, true>, 5)) return rc;
+    if (int rc = f(fe_whisper3_kernel<128, false, true>, 6)) return rc;
+    if (int rc = f(fe_whisper3_kernel<128, true, true>, 7)) return rc;
     return 0;
 }
 static int whisper3_smem_attr() {
@@ -1007,7 +1075,8 @@ static int whisper3_smem_attr() {
     });
 }
 static void launch_whisper3(int n_mels, bool out16, unsigned grid, cudaStream_t st, const FeWhisper2Params& p, const CUtensorMap& tmap) {
-    const int want = (n_mels == 128 ? 2 : 0) + (out16 ? 1 : 0);
+    // padding >= 2 * PADL: units of pure padding exist and are skipped (fe_w3_silent); the variant without that test otherwise
+    const int want = (n_mels == 128 ? 2 : 0) + (out16 ? 1 : 0) + (p.padding >= 2 * FeW3Cfg::PADL ? 4 : 0);
     whisper3_for_each([&](FeW3Kernel k, int id) {
         if (id == want) k<<<grid, FeW3Cfg::NT, FeW3Cfg::SMEM_BYTES, st>>>(p, tmap);
         return 0;

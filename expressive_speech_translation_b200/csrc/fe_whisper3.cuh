@@ -137,7 +137,21 @@ struct FeW3Unit {
     int64_t o0;     // element offset in `out` of (mel row 0, frame t0)
     int64_t len;    // valid samples
     int64_t lp;     // len + padding
+    int silent;     // every frame of the unit reads only the zeros of `padding`: nothing to transform (see fe_w3_silent)
 };
+
+// A unit whose first frame starts at or behind the clip's last sample (t0 * HOP - PADL >= len) sees nothing but the
+// zeros whisper.audio pads with (padding = 480000 in whisper.transcribe: the second half of every 30-s clip's mel, more
+// for short clips).  Its power spectrum is exactly 0, its log-mel -inf before the floor, and the value the reference
+// ends up with is the clip's clamp threshold max(-10, max - 8) -- known only once the whole clip is done.  The kernel
+// skips such units (no copy, no transform, no store) and the fix-up kernel, which knows the threshold, fills them with
+// one write; before, they were transformed, stored as -inf, read back and rewritten (36 % of the kernels' time on
+// ragged padded speech, profiles/r02_bench_realistic.txt).  padding >= PADL keeps the reflect padding at the right
+// edge (it mirrors at most HOP + PADL samples before len + padding) inside the zeros as well.
+FE_HD FE_INLINE int fe_w3_silent(const FeWhisper2Params& p, const FeW3Unit& t) {
+    typedef FeW3Cfg C;
+    return p.padding >= 2 * C::PADL && t.t0 < t.T && (int64_t)t.t0 * C::HOP - C::PADL >= t.len;
+}
 
 // Plain call: clip b has units_per_clip units of 128 frames, rows of T_out.  Windowed call (p.win_frames > 0): window w of
 // clip b is its own (n_mels, win_frames) block; a unit never straddles two windows (units per window =
@@ -146,6 +160,30 @@ struct FeW3Unit {
 // the decode proper, from (clip, unit within the clip): no division by a run-time value on the plain path -- the
 // kernel advances (clip, within) incrementally (FeW3Pos), because a full decode per warp and unit was 7 % of the
 // kernel's time (profiles/r02_w3_trace_v7.txt: 850 cycles of every 12.6 k-cycle unit)
+// Plain calls: the first frame of clip b behind which every 128-frame unit is either pure padding or lies behind the
+// clip's last frame -- the part of each output row the fix-up writes as ONE contiguous run (threshold up to frame Tc,
+// 0 behind).  Returns T_out when there is no such part.
+FE_HD FE_INLINE int64_t fe_w3_tail_start(const FeWhisper2Params& p, int b, int64_t* Tc_out) {
+    typedef FeW3Cfg C;
+    const int64_t len = fe_clip_len(p.lengths, b, p.L), lp = len + p.padding;
+    int64_t Tc = lp / C::HOP;
+    if (Tc > p.T_out) Tc = p.T_out;
+    int64_t f0 = (Tc + C::UF - 1) / C::UF * C::UF;                              // first unit behind the last frame
+    if (p.padding >= 2 * C::PADL) {
+        const int64_t fs = (len + C::PADL + C::HOP - 1) / C::HOP;                // first frame with t * HOP - PADL >= len
+        const int64_t s0 = (fs + C::UF - 1) / C::UF * C::UF;
+        if (s0 < f0) f0 = s0;
+    }
+    *Tc_out = Tc;
+    return f0 < p.T_out ? f0 : p.T_out;
+}
+
+// FIXUP = false (the featurizer kernel, the emulation of its phases): a silent unit is returned with T = Ts = t0, i.e. as
+// a unit without frames to compute, and the kernel never looks at `silent`.  FIXUP = true: T / Ts as they are.
+// PAD = false: the caller knows that the call has no padding to speak of (padding < 2 * PADL), so no unit is silent; the
+// featurizer kernel is instantiated both ways, because the test costs it 1 % (1.040 against 1.029 ms per 1024 x 30 s,
+// a/b a/b on one box) that a call without padding need not pay.
+template <bool FIXUP = false, bool PAD = true>
 FE_HD FE_INLINE FeW3Unit fe_w3_unit_at(const FeWhisper2Params& p, int b, int within) {
     typedef FeW3Cfg C;
     FeW3Unit t;
@@ -170,6 +208,8 @@ FE_HD FE_INLINE FeW3Unit fe_w3_unit_at(const FeWhisper2Params& p, int b, int wit
             t.T = (int)(Tc < e ? Tc : e);
             t.Ts = t.t0; t.n_in = 0; t.pitch = W; t.o0 = 0;
         }
+        t.silent = PAD ? fe_w3_silent(p, t) : 0;
+        if (PAD && !FIXUP && t.silent) t.T = t.Ts = t.t0;
         return t;
     }
     t.t0 = within * C::UF;
@@ -178,14 +218,17 @@ FE_HD FE_INLINE FeW3Unit fe_w3_unit_at(const FeWhisper2Params& p, int b, int wit
     t.n_in = (int)(p.T_out - t.t0 < C::UF ? p.T_out - t.t0 : C::UF);
     t.pitch = (int)p.T_out;
     t.o0 = (int64_t)t.b * p.out_batch_stride + t.t0;
+    t.silent = PAD ? fe_w3_silent(p, t) : 0;
+    if (PAD && !FIXUP && t.silent) t.T = t.Ts = t.t0;
     return t;
 }
 // Unit order: POSITION-major, u = within * B + clip.  With clip-major order and gridDim.x = 148, a CTA would only ever
 // see 6 of a 30-s clip's 24 unit positions (gcd(148, 24) = 4), and the CTAs that keep drawing a clip's first / last unit
 // (edge rows, a 56-frame unit) finish 10 % apart (profiles/r02_w3_v8: 12 % of the SM cycles idle at the end).
+template <bool FIXUP = false>
 FE_HD FE_INLINE FeW3Unit fe_w3_unit(const FeWhisper2Params& p, int u) {
     const int within = u / p.B;
-    return fe_w3_unit_at(p, u - within * p.B, within);
+    return fe_w3_unit_at<FIXUP>(p, u - within * p.B, within);
 }
 // position of a CTA's current unit; one step = gridDim.x units = (step_w positions, step_b clips) with a carry
 struct FeW3Pos { int b, within; };
@@ -200,6 +243,9 @@ FE_HD FE_INLINE FeW3Pos fe_w3_pos_next(const FeWhisper2Params& p, FeW3Pos q) {
 // and of ragged ends -- are written element-wise by the issuing warp (2 + 3 rows of a 30-s clip's 3196).
 // fe_w3_team_live: the team has at least one frame to compute.
 FE_HD FE_INLINE bool fe_w3_team_live(const FeW3Unit& t, int q) { return t.t0 + FeW3Cfg::FT * q < t.T; }
+// (Stepping over such units in the kernel's loop -- every warp seeking its CTA's next unit with work instead of walking
+// the empty ones through the mbarrier pipeline -- was measured and dropped: 0.517 against 0.530 ms on the ragged
+// padded leg, but 1.18 against 1.03 ms on the headline, the loop being sensitive to its shape.)
 FE_HD FE_INLINE int64_t fe_w3_row0(const FeW3Unit& t, int q) {     // global sample index of row 0, column 0
     return ((int64_t)t.t0 + FeW3Cfg::FT * q) * FeW3Cfg::HOP - FeW3Cfg::PADL;
 }

@@ -60,7 +60,18 @@ static void run_whisper3(const FeWhisper2Params& p) {
     for (int u = 0; u < p.total_units; ++u) {
         const FeW3Unit t = fe_w3_unit(p, u);
         float mn = 3.0e38f, mx = -3.0e38f;
-        if (t.t0 < t.T) {
+        if (t.silent) {
+            // the kernel steps over the unit (T == t0 in its view); the fix-up fills its live columns with the threshold.
+            // Here: -inf, which the element-wise fix-up pass below turns into exactly that.
+            const FeW3Unit f = fe_w3_unit<true>(p, u);
+            const int n_live = std::max(0, std::min(f.Ts - f.t0, f.n_in));
+            for (int m = 0; m < NMELS; ++m)
+                for (int c = 0; c < n_live; ++c) {
+                    const int64_t i = t.o0 + (int64_t)m * t.pitch + c;
+                    if (OUT16) static_cast<unsigned short*>(p.out)[i] = 0xfc00u;
+                    else static_cast<float*>(p.out)[i] = -INFINITY;
+                }
+        } else if (t.t0 < t.T) {
             for (int q = 0; q < C::TEAMS; ++q) {
                 float* wq = sm.data() + C::OFF_W + q * C::WT;
                 if (!fe_w3_team_live(t, q)) continue;

@@ -244,6 +244,40 @@ def test_whisper3_speech_sine_zeros_percall_ragged(emu):
     assert not got[1, :, ref.shape[1]:].any()
 
 
+def test_whisper3_units_of_pure_padding_are_filled_not_transformed(emu):
+    """whisper.transcribe's call (padding = N_SAMPLES) on ragged clips: units that lie wholly in the zero padding are
+    skipped by the kernel and filled with the clip's clamp threshold by the fix-up (fe_w3_silent).  Lengths sit on and
+    next to the boundary  128 * k * 160 - 200  where a unit turns silent; one clip is all zeros."""
+    gen = torch.Generator().manual_seed(12)
+    L, pad = 2 * 128 * 160 + 900, 128 * 160 * 3
+    x = speech_like(gen, 5, L, 16000)
+    x[4] = 0.0
+    lengths = [L, 128 * 160 - 200, 128 * 160 - 201, 2 * 128 * 160 - 199, L]
+    for nm, norm in ((80, 0), (128, 1)):
+        got = emu_whisper3(emu, x.numpy(), nm, pad, norm=norm, lengths=lengths)
+        refs = [oracle.whisper_log_mel(x[b, :n], nm, padding=pad, dtype=torch.float64).numpy() for b, n in enumerate(lengths)]
+        for b, r in enumerate(refs):
+            T = r.shape[1]
+            if norm == 0:
+                assert np.abs(got[b, :, :T] - r).max() <= 1e-4, (nm, b)
+                # the padded tail is one constant: max(-10, max - 8) in the output scale
+                tail = got[b, :, (lengths[b] + 200) // 160 + 2:T]
+                assert tail.size and np.all(tail == tail.flat[0])
+                assert abs(float(tail.flat[0]) - max(-1.5, float(got[b, :, :T].max()) - 2.0)) <= 1e-6
+            assert not got[b, :, T:].any()
+        if norm == 1:      # per-call: one maximum, hence one threshold, for all clips
+            thr = max(-1.5, float(got.max()) - 2.0)
+            for b in range(5):
+                T = (lengths[b] + pad) // 160
+                tail = got[b, :, (lengths[b] + 200) // 160 + 2:T]
+                assert np.all(np.abs(tail - thr) <= 1e-6)
+        # float16 output: the rounded float32 output, silent units included
+        h = emu_whisper3(emu, x.numpy(), nm, pad, norm=norm, lengths=lengths, f16=True)
+        assert np.array_equal(h, got.astype(np.float16))
+        # element-wise loader path agrees bit for bit
+        assert np.array_equal(emu_whisper3(emu, x.numpy(), nm, pad, norm=norm, lengths=lengths, misalign=True), got)
+
+
 def test_whisper3_f16_output_is_the_rounded_f32_output(emu):
     x = speech_like(torch.Generator().manual_seed(9), 2, 30000, 16000).numpy()
     for nm in (80, 128):

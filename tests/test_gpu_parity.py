@@ -113,6 +113,32 @@ def test_whisper_host_path_equals_device_path(fe):
     assert torch.equal(dev, host)
 
 
+def test_whisper_transcribe_padding_ragged_units_of_pure_padding(fe):
+    """whisper.transcribe's call shape: padding = N_SAMPLES behind ragged clips.  Units that lie wholly in the zeros are
+    skipped by the Tensor-Memory kernel and filled by its fix-up (fe_w3_silent); the result must equal the oracle's within
+    TOL, be ONE constant per clip over the padded tail and 0 behind the clip's own frame count, in float32 and float16,
+    through the device and the host-buffer entry points."""
+    gen = torch.Generator().manual_seed(33)
+    L, pad = 2 * 128 * 160 + 900, 480000
+    x = speech_like(gen, 6, L, 16000)
+    x[5] = 0.0
+    lens = [L, 128 * 160 - 200, 128 * 160 - 201, 2 * 128 * 160 - 199, 4321, L]
+    for nm in (80, 128):
+        for odt in (torch.float32, torch.float16):
+            got = fe.whisper_log_mel_batch(x.cuda(), lengths=lens, n_mels=nm, padding=pad, out_dtype=odt).cpu()
+            for b, n in enumerate(lens):
+                ref = oracle.whisper_log_mel(x[b, :n], nm, padding=pad, dtype=torch.float64)
+                T = ref.shape[1]
+                tol = TOL if odt == torch.float32 else TOL + 2.0 ** -11 * 1.5
+                assert (got[b, :, :T].double() - ref).abs().max() <= tol, (nm, b)
+                assert not got[b, :, T:].any()
+                tail = got[b, :, (n + 200) // 160 + 2:T]
+                assert tail.numel() and bool((tail == tail.flatten()[0]).all())
+        # host-buffer entry point: same bits
+        host = fe.whisper_log_mel_host(x.pin_memory(), lengths=lens, n_mels=nm, padding=pad)
+        assert torch.equal(host, fe.whisper_log_mel_batch(x.cuda(), lengths=lens, n_mels=nm, padding=pad).cpu())
+
+
 def _same_half_bits(a16, b32):
     return torch.equal(a16.view(torch.int16), b32.to(torch.float16).view(torch.int16))
 

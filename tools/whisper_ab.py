@@ -29,6 +29,12 @@ print(f"step {ms:.4f} ms  kernel {pr['feature_ms'] / pr['feature_launches']:.4f}
 '''
 n_mels = sys.argv[1] if len(sys.argv) > 1 else "128"
 B = sys.argv[2] if len(sys.argv) > 2 else "1024"
+if os.environ.get("AB_LIBS"):       # A/B of two builds of the library instead: AB_LIBS=path_a,path_b -> a b a b on the same box
+    for lib in os.environ["AB_LIBS"].split(",") * 2:
+        env = dict(os.environ, B200FEAT_LIB=os.path.abspath(lib))
+        r = subprocess.run([sys.executable, "-c", CHILD, n_mels, B], env=env, capture_output=True, text=True, timeout=600)
+        print(f"{os.path.basename(lib)}: {r.stdout.strip()} {r.stderr.strip()[-400:]}")
+    sys.exit(0)
 for k in ("2", "3"):
     env = dict(os.environ, B200FEAT_WHISPER_KERNEL=k)
     r = subprocess.run([sys.executable, "-c", CHILD, n_mels, B], env=env, capture_output=True, text=True, timeout=600)
