@@ -12,6 +12,8 @@ from .api import (  # noqa: F401
     mel_spectrogram,
     fbank,
     whisper_log_mel_batch,
+    whisper_log_mel_windows,
+    whisper_num_windows,
     cosy_mel_batch,
     cosy_prompt_feat,
     kaldi_fbank_batch,

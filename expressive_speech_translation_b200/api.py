@@ -158,6 +158,51 @@ def whisper_log_mel_batch(wave, lengths=None, n_mels=80, padding=0, norm="per_cl
     return out
 
 
+N_SAMPLES = 480000      # whisper.audio.N_SAMPLES: 30 s at 16 kHz, the padding whisper.transcribe asks for
+N_FRAMES = 3000         # whisper.audio.N_FRAMES: frames of one encoder window
+
+
+def whisper_num_windows(n_samples, win_frames=N_FRAMES):
+    """windows whisper.transcribe decodes for a clip of n_samples: seek = 0, win_frames, ... < content_frames = n_samples // 160"""
+    return max(1, -(-(int(n_samples) // WHISPER_HOP) // int(win_frames)))
+
+
+def whisper_log_mel_windows(wave, lengths=None, n_mels=80, padding=N_SAMPLES, norm="per_clip", win_frames=N_FRAMES,
+                            out=None, out_dtype=torch.float16):
+    """(B, L) float32 waveform batch on a CUDA device -> (B, n_windows, n_mels, win_frames) encoder-ready windows, the
+    `pad_or_trim(mel[:, seek:seek + N_FRAMES], N_FRAMES).to(dtype)` slices whisper.transcribe feeds the encoder
+    (UPSTREAM transcribe.py, reached from /root/reference/Backend/services/cascaded_backend.py:158), for seek = 0, 3000,
+    ...: written by the kernel's epilogue in that layout and dtype (default float16, transcribe's fp16=True), no
+    intermediate (n_mels, T) tensor.  Identical, bit for bit, to slicing whisper_log_mel_batch(wave, padding=padding).
+    n_windows = whisper_num_windows(L); a ragged clip's own count is whisper_num_windows(lengths[b])."""
+    assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
+    wave = _as_float_tensor(wave, "wave")
+    device = _cuda_device(wave.device if wave.is_cuda else None)
+    w, stride = _prep_wave(wave, device)
+    if w.data_ptr() % 16 or stride % 4:             # the Tensor-Memory kernel's bulk copies need 16-byte aligned rows
+        Lp = (w.shape[1] + 3) // 4 * 4
+        buf = torch.zeros((w.shape[0], Lp), dtype=torch.float32, device=device)
+        buf[:, :w.shape[1]] = w
+        w, stride = buf[:, :w.shape[1]], Lp
+    B, L = w.shape
+    nw = whisper_num_windows(L, win_frames)
+    if out is None:
+        out = torch.empty((B, nw, n_mels, win_frames), dtype=out_dtype, device=device)
+    elif out.shape != (B, nw, n_mels, win_frames) or not out.is_contiguous() or out.device != device:
+        raise ValueError("out must be a contiguous float32 / float16 (B, n_windows, n_mels, win_frames) tensor on the wave's device")
+    if B == 0:
+        return out
+    ln = _lengths_dev(lengths, B, device)
+    ws, nws = _workspace(KIND_WHISPER, B, L + int(padding) + WHISPER_HOP * 128 * (nw + 1), device)
+    with torch.cuda.device(device):
+        rc = lib.b200feat_whisper_logmel_windows(_ptr(w), _ptr(ln), B, L, stride, n_mels, int(padding), _NORMS[norm],
+                                                 int(win_frames), nw, _ptr(out), _DTYPES[out_dtype], nw * n_mels * win_frames,
+                                                 _ptr(ws), nws, _stream(device))
+    check(rc, "b200feat_whisper_logmel_windows")
+    return out
+
+
 def cosy_mel_batch(wave, lengths=None, out=None, frame_major=False):
     """(B, L) 24 kHz batch on a CUDA device -> (B, 80, T) ln-mel (n_fft 1920, hop 480); frame_major=True writes
     (B, T, 80), the layout the CosyVoice frontend's `_extract_speech_feat` produces with `.transpose(0, 1)`."""

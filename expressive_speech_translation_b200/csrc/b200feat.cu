@@ -1338,17 +1338,30 @@ int64_t b200feat_workspace_bytes(int32_t kind, int32_t B, int64_t L) {
 static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* lengths, int32_t B, int64_t L,
                                int64_t wave_stride, int32_t n_mels, int32_t padding, int32_t norm_mode,
                                void* out, bool out16, int64_t out_batch_stride, int64_t T_out,
-                               void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+                               void* workspace, int64_t workspace_bytes, void* cuda_stream,
+                               int32_t win_frames = 0, int32_t n_windows = 0) {
     if (int rc = common_checks("whisper_logmel", wave, out, B, L, wave_stride)) return rc;
     if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "whisper_logmel: Unsupported n_mels: %d", n_mels);
     if (padding < 0) return fail(B200FEAT_EINVAL, "whisper_logmel: padding %d < 0", padding);
     if (norm_mode != FE_NORM_PER_CLIP && norm_mode != FE_NORM_PER_CALL) return fail(B200FEAT_EINVAL, "whisper_logmel: bad norm_mode %d", norm_mode);
     const int64_t T_full = (L + padding) / FeW2Cfg::HOP;
-    if (T_out < T_full) return fail(B200FEAT_EINVAL, "whisper_logmel: T_out %lld < %lld frames", (long long)T_out, (long long)T_full);
+    if (win_frames == 0 && T_out < T_full) return fail(B200FEAT_EINVAL, "whisper_logmel: T_out %lld < %lld frames", (long long)T_out, (long long)T_full);
     if (out_batch_stride < (int64_t)n_mels * T_out) return fail(B200FEAT_EINVAL, "whisper_logmel: out_batch_stride too small");
     if (L + padding <= FeW2Cfg::PADL && B > 0 && T_out > 0)
         return fail(B200FEAT_EINVAL, "whisper_logmel: reflect padding (200) needs more than 200 samples, got %lld", (long long)(L + padding));
-    const int64_t units = (T_out + FeW2Cfg::FT - 1) / FeW2Cfg::FT;
+    int64_t units = (T_out + FeW2Cfg::FT - 1) / FeW2Cfg::FT;
+    if (win_frames > 0) {
+        // windowed output (b200feat_whisper_logmel_windows): complete slices of the padded mel, all of the longest clip's
+        // content covered (the frames behind the last window are transformed for the clip's maximum, not stored)
+        if (T_out != (int64_t)win_frames * n_windows) return fail(B200FEAT_EINVAL, "whisper_logmel_windows: internal T_out");
+        if ((int64_t)n_windows * win_frames > T_full)
+            return fail(B200FEAT_EINVAL, "whisper_logmel_windows: %d windows of %d frames exceed the %lld frames of the padded clip "
+                        "(whisper.transcribe pads with padding = N_SAMPLES)", n_windows, win_frames, (long long)T_full);
+        if ((int64_t)n_windows * win_frames < L / FeW2Cfg::HOP)
+            return fail(B200FEAT_EINVAL, "whisper_logmel_windows: %d windows of %d frames do not cover the clip's %lld content frames",
+                        n_windows, win_frames, (long long)(L / FeW2Cfg::HOP));
+        units = (int64_t)n_windows * ((win_frames + FeW3Cfg::UF - 1) / FeW3Cfg::UF) + 1;
+    }
     const int64_t keys_bytes = 16 + (((int64_t)B * 4 + 15) & ~(int64_t)15);
     if (workspace == nullptr || workspace_bytes < keys_bytes + (int64_t)B * units * 8)
         return fail(B200FEAT_EWORKSPACE, "whisper_logmel: workspace too small (%lld bytes, need %lld)",
@@ -1374,13 +1387,16 @@ static int whisper_logmel_impl(const void* wave, bool in_s16, const int64_t* len
     p.max_keys = reinterpret_cast<int32_t*>(workspace);
     p.unit_minmax = reinterpret_cast<float2*>(reinterpret_cast<char*>(workspace) + keys_bytes);
     const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
-    const bool v3 = !in_s16 && (p.vec_ok & 1) && whisper_kernel_choice() != 2;
+    const bool v3 = !in_s16 && (p.vec_ok & 1) && (whisper_kernel_choice() != 2 || win_frames > 0);
+    if (win_frames > 0 && !v3)
+        return fail(B200FEAT_EINVAL, "whisper_logmel_windows: needs float32 samples in 16-byte aligned rows (wave pointer and wave_stride * 4 multiples of 16)");
     if (v3) {
         // Tensor-Memory kernel: 128-frame units; their (max, -min) keys are accumulated with atomicMax, so the unit
         // table is initialised together with the per-clip keys
-        const int64_t units3 = (T_out + FeW3Cfg::UF - 1) / FeW3Cfg::UF;
+        const int64_t units3 = win_frames > 0 ? units : (T_out + FeW3Cfg::UF - 1) / FeW3Cfg::UF;
         p.units_per_clip = (int32_t)units3;
         p.total_units = (int32_t)(B * units3);
+        p.win_frames = win_frames; p.n_windows = n_windows;
         FE_CUDA(cudaMemsetAsync(workspace, FE_KEY_INIT_BYTE, (size_t)(keys_bytes + (int64_t)B * units3 * 8), st));
         {
             const unsigned grid = (unsigned)(p.total_units < sms ? p.total_units : sms);
@@ -1449,6 +1465,20 @@ int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64
     if (int rc = whisper_ex_dtypes("whisper_logmel_ex", wave_dtype, out_dtype)) return rc;
     return whisper_logmel_impl(wave, wave_dtype == B200FEAT_S16, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out,
                                out_dtype == B200FEAT_F16, out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
+}
+
+int b200feat_whisper_logmel_windows(const float* wave, const int64_t* lengths, int32_t B, int64_t L, int64_t wave_stride,
+                                    int32_t n_mels, int32_t padding, int32_t norm_mode, int32_t win_frames, int32_t n_windows,
+                                    void* out, int32_t out_dtype, int64_t out_batch_stride,
+                                    void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    if (int rc = whisper_ex_dtypes("whisper_logmel_windows", B200FEAT_F32, out_dtype)) return rc;
+    if (win_frames <= 0 || n_windows <= 0 || (int64_t)win_frames * n_windows >= (1 << 24))
+        return fail(B200FEAT_EINVAL, "whisper_logmel_windows: win_frames %d, n_windows %d must be positive (and their product < 2^24)", win_frames, n_windows);
+    if (out_batch_stride < (int64_t)n_windows * n_mels * win_frames)
+        return fail(B200FEAT_EINVAL, "whisper_logmel_windows: out_batch_stride < n_windows * n_mels * win_frames");
+    return whisper_logmel_impl(wave, false, lengths, B, L, wave_stride, n_mels, padding, norm_mode, out, out_dtype == B200FEAT_F16,
+                               out_batch_stride, (int64_t)win_frames * n_windows, workspace, workspace_bytes, cuda_stream,
+                               win_frames, n_windows);
 }
 
 // ------------------------------------------------------------------------------------------ Whisper, no allocation

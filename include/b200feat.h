@@ -92,6 +92,28 @@ int b200feat_whisper_logmel_ex(const void* wave, int32_t wave_dtype, const int64
                                void* out, int32_t out_dtype, int64_t out_batch_stride, int64_t T_out,
                                void* workspace, int64_t workspace_bytes, void* cuda_stream);
 
+/* Whisper log-mel as encoder-ready WINDOWS.  Replaces, for a batch of clips, what
+ * whisper.transcribe does with the mel of a clip (UPSTREAM openai-whisper transcribe.py, reached from
+ * /root/reference/Backend/services/cascaded_backend.py:158 `self.asr_model.transcribe(...)`):
+ *     mel = log_mel_spectrogram(audio, n_mels, padding=N_SAMPLES)          # (n_mels, content_frames + 3000)
+ *     mel_segment = mel[:, seek : seek + N_FRAMES]; pad_or_trim(mel_segment, N_FRAMES).to(dtype)    # seek = 0, 3000, ...
+ * out: (B, n_windows, n_mels, win_frames), float32 or binary16 (out_dtype), out_batch_stride elements between clips:
+ * window w of clip b = frames [w * win_frames, (w + 1) * win_frames) of the clip's padded log-mel, written by the
+ * kernel's epilogue straight into that layout -- no (n_mels, T) intermediate, no slicing copy, no cast pass.
+ *   - The clamp max - 8 uses the maximum over the clip's WHOLE padded mel, as transcribe's call does, including the
+ *     frames behind the last window (they are transformed, not stored).
+ *   - The windows must be complete slices: n_windows * win_frames <= (L + padding) / 160, and they must cover the
+ *     content: n_windows * win_frames >= L / 160.  With transcribe's padding = 480000 and win_frames = 3000:
+ *     n_windows = ceil((L / 160) / 3000).
+ *   - Ragged clips (`lengths`): windows behind a clip's own content hold what transcribe's padding gives (the clip's
+ *     clamp threshold) up to frame (len + padding) / 160 and 0 behind it.
+ *   - wave: float32, 16-byte aligned rows (pointer and wave_stride * 4 multiples of 16); workspace:
+ *     b200feat_workspace_bytes(B200FEAT_KIND_WHISPER, B, L + padding + 160 * 128 * (n_windows + 1)) bytes. */
+int b200feat_whisper_logmel_windows(const float* wave, const int64_t* lengths, int32_t B, int64_t L, int64_t wave_stride,
+                                    int32_t n_mels, int32_t padding, int32_t norm_mode, int32_t win_frames, int32_t n_windows,
+                                    void* out, int32_t out_dtype, int64_t out_batch_stride,
+                                    void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
 /* Whisper log-mel WITHOUT any allocation and without a caller workspace.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid it).  Same arithmetic, kernels and result as b200feat_whisper_logmel (float32 in / out);

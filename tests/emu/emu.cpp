@@ -199,6 +199,55 @@ extern "C" int emu_whisper3(const float* wave, const int64_t* lengths, int B, in
     return emu_whisper_any(wave, false, lengths, B, L, stride, n_mels, padding, norm_mode, out, out16 != 0, T_out, 3);
 }
 
+// b200feat_whisper_logmel_windows: the Tensor-Memory kernel's windowed unit map + the fix-up's arithmetic per element
+extern "C" int emu_whisper3_windows(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride, int n_mels,
+                                    int padding, int norm_mode, int win_frames, int n_windows, void* out, int out16) {
+    typedef FeW3Cfg C;
+    std::vector<int> keys(B > 0 ? B : 1, FE_KEY_INIT);
+    FeWhisper2Params p;
+    memset(&p, 0, sizeof(p));
+    p.wave = wave; p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B; p.padding = padding;
+    p.n_mels = n_mels; p.norm_mode = norm_mode; p.out = out;
+    p.out_batch_stride = (int64_t)n_windows * n_mels * win_frames; p.T_out = (int64_t)n_windows * win_frames;
+    p.win_frames = win_frames; p.n_windows = n_windows;
+    p.units_per_clip = n_windows * ((win_frames + C::UF - 1) / C::UF) + 1; p.total_units = B * p.units_per_clip;
+    p.vec_ok = ((((uintptr_t)wave & 15) == 0) && (stride % 4 == 0)) ? 1 : 0;
+    if (!(p.vec_ok & 1)) return -2;
+    if ((((uintptr_t)out & 15) == 0) && (p.out_batch_stride % 4 == 0)) p.vec_ok |= 2;
+    std::vector<float2> mm((size_t)std::max(p.total_units, 1));
+    p.max_keys = keys.data(); p.unit_minmax = mm.data();
+    {
+        const int64_t first = (int64_t)C::TMAP_ROW0 * 160 - 200;
+        const int64_t rows = L - first - C::PITCH < 0 ? 0 : (L - first - C::PITCH) / 160 + 1;
+        p.use_tmap = (rows >= C::ROWS && use_tmap_env()) ? 1 : 0;
+        p.tmap_rows = p.use_tmap ? (int)rows : 0;
+    }
+    if (n_mels == 80 && !out16) run_whisper3<80, false>(p);
+    else if (n_mels == 80) run_whisper3<80, true>(p);
+    else if (n_mels == 128 && !out16) run_whisper3<128, false>(p);
+    else if (n_mels == 128) run_whisper3<128, true>(p);
+    else return -1;
+    for (int b = 0; b < B; ++b) {
+        const float thr = fe_w2_threshold(fe_key_float(keys[norm_mode == FE_NORM_PER_CALL ? 0 : b]));
+        const int64_t Tb = (fe_clip_len(lengths, b, L) + padding) / 160;
+        for (int w = 0; w < n_windows; ++w)
+            for (int m = 0; m < n_mels; ++m)
+                for (int c = 0; c < win_frames; ++c) {
+                    const int64_t i = (int64_t)b * p.out_batch_stride + ((int64_t)w * n_mels + m) * win_frames + c;
+                    const int64_t t = (int64_t)w * win_frames + c;
+                    if (out16) {
+                        unsigned short& h = static_cast<unsigned short*>(out)[i];
+                        const unsigned short th = fe_f2h_rn(thr);
+                        h = t < Tb ? (half_bits_to_float(h) < half_bits_to_float(th) ? th : h) : (unsigned short)0;
+                    } else {
+                        float& v = static_cast<float*>(out)[i];
+                        v = t < Tb ? (v < thr ? thr : v) : 0.0f;
+                    }
+                }
+    }
+    return 0;
+}
+
 extern "C" int emu_whisper_f16(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
                                int n_mels, int padding, int norm_mode, unsigned short* out, int64_t T_out) {
     return emu_whisper_any(wave, false, lengths, B, L, stride, n_mels, padding, norm_mode, out, true, T_out);

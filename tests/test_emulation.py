@@ -278,6 +278,35 @@ def test_whisper3_units_of_pure_padding_are_filled_not_transformed(emu):
         assert np.array_equal(emu_whisper3(emu, x.numpy(), nm, pad, norm=norm, lengths=lengths, misalign=True), got)
 
 
+def test_whisper3_windows_are_slices_of_the_padded_mel(emu):
+    """b200feat_whisper_logmel_windows: (B, n_windows, n_mels, W) == the W-frame slices of the padded
+    log-mel, bit for bit against the plain layout of the same kernel, and within 1e-4 of the oracle's slices.  Small W so
+    that the emulation stays fast: W = 300 (two 128-frame units + one of 44), padding = W * 160 like transcribe's."""
+    W, pad = 300, 300 * 160
+    gen = torch.Generator().manual_seed(44)
+    L = 2 * W * 160 + 160 * 31 + 76           # content 631 frames -> 3 windows; a multiple of 4: 16-byte aligned rows
+    x = np.ascontiguousarray(speech_like(gen, 3, L, 16000).numpy())
+    lengths = [L, W * 160, 12345]             # W * 160: content exactly one window, signal reaches into the frames behind it
+    la = np.asarray(lengths, dtype=np.int64)
+    nw = -(-(L // 160) // W)
+    assert nw == 3
+    for nm, f16 in ((80, False), (128, True)):
+        out = np.full((3, nw, nm, W), 7.0, dtype=np.float16 if f16 else np.float32)
+        assert emu.emu_whisper3_windows(x.ctypes.data_as(vp), la.ctypes.data_as(vp), 3, L, L, nm, pad, 0, W, nw,
+                                        out.ctypes.data_as(vp), int(f16)) == 0
+        plain = emu_whisper3(emu, x, nm, pad, lengths=lengths, f16=f16)          # (3, nm, (L + pad) // 160)
+        for w in range(nw):
+            assert np.array_equal(out[:, w], plain[:, :, w * W:(w + 1) * W]), (nm, w)
+        if not f16:
+            for b, n in enumerate(lengths):
+                ref = oracle.whisper_log_mel(torch.from_numpy(x[b, :n]), nm, padding=pad, dtype=torch.float64).numpy()
+                for w in range(nw):
+                    r = ref[:, w * W:(w + 1) * W]
+                    if r.shape[1]:
+                        assert np.abs(out[b, w, :, :r.shape[1]] - r).max() <= 1e-4
+                    assert not out[b, w, :, r.shape[1]:].any()
+
+
 def test_whisper3_f16_output_is_the_rounded_f32_output(emu):
     x = speech_like(torch.Generator().manual_seed(9), 2, 30000, 16000).numpy()
     for nm in (80, 128):

@@ -139,6 +139,47 @@ def test_whisper_transcribe_padding_ragged_units_of_pure_padding(fe):
         assert torch.equal(host, fe.whisper_log_mel_batch(x.cuda(), lengths=lens, n_mels=nm, padding=pad).cpu())
 
 
+def test_whisper_windows_equal_transcribe_slices(fe):
+    """`pad_or_trim(mel[:, seek:seek + 3000], 3000).to(float16)` of whisper.transcribe for seek = 0, 3000,
+    ... straight from the epilogue: (B, n_windows, n_mels, 3000) must equal, bit for bit, the slices of
+    whisper_log_mel_batch(..., padding=480000) (same kernel, plain layout), in float16 and float32, ragged clips included;
+    and the float32 windows lie within TOL of the oracle's slices."""
+    gen = torch.Generator().manual_seed(61)
+    L = 480000 + 160 * 700 + 80                    # 37 s: 3700 content frames -> 2 windows
+    x = speech_like(gen, 4, L, 16000)
+    lens = [L, 480000, 480000 - 1, 30001]           # exactly one window of content; one sample short of it; a short clip
+    assert fe.whisper_num_windows(L) == 2 and fe.whisper_num_windows(480000) == 1 and fe.whisper_num_windows(480160) == 2
+    for nm in (80, 128):
+        plain = fe.whisper_log_mel_batch(x.cuda(), lengths=lens, n_mels=nm, padding=480000)
+        for odt in (torch.float16, torch.float32):
+            win = fe.whisper_log_mel_windows(x.cuda(), lengths=lens, n_mels=nm, out_dtype=odt)
+            assert win.shape == (4, 2, nm, 3000) and win.dtype == odt
+            for w in range(2):
+                want = plain[:, :, 3000 * w:3000 * (w + 1)].to(odt)
+                assert torch.equal(win[:, w].view(torch.int16 if odt == torch.float16 else torch.int32),
+                                   want.contiguous().view(torch.int16 if odt == torch.float16 else torch.int32)), (nm, odt, w)
+        win = fe.whisper_log_mel_windows(x.cuda(), lengths=lens, n_mels=nm, out_dtype=torch.float32).cpu()
+        for b, n in enumerate(lens):
+            ref = oracle.whisper_log_mel(x[b, :n], nm, padding=480000, dtype=torch.float64)
+            for w in range(2):
+                r = ref[:, 3000 * w:3000 * (w + 1)]
+                if r.shape[1]:
+                    assert (win[b, w, :, :r.shape[1]].double() - r).abs().max() <= TOL
+                assert not win[b, w, :, r.shape[1]:].any()
+    # an unaligned view (rows not 16-byte aligned) is copied to aligned rows by the Python layer: same result
+    y = torch.zeros(4, L + 1)
+    y[:, 1:] = x
+    win2 = fe.whisper_log_mel_windows(y.cuda()[:, 1:], lengths=lens, n_mels=128, out_dtype=torch.float32).cpu()
+    assert torch.equal(win2, win)
+    # preallocated output, per-call normalisation, and the C-ABI's refusals
+    out = torch.empty((4, 2, 80, 3000), dtype=torch.float16, device="cuda")
+    assert fe.whisper_log_mel_windows(x.cuda(), n_mels=80, norm="per_call", out=out) is out
+    pc = fe.whisper_log_mel_batch(x.cuda(), n_mels=80, padding=480000, norm="per_call", out_dtype=torch.float16)
+    assert torch.equal(out[:, 1].view(torch.int16), pc[:, :, 3000:6000].contiguous().view(torch.int16))
+    with pytest.raises(ValueError):
+        fe.whisper_log_mel_windows(x.cuda(), n_mels=80, padding=0)          # windows must be complete slices of the padded mel
+
+
 def _same_half_bits(a16, b32):
     return torch.equal(a16.view(torch.int16), b32.to(torch.float16).view(torch.int16))
 
