@@ -87,6 +87,18 @@ class Workload:
             self.featurizer = "kaldi_fbank"
             self.traffic_key = None
             self.cpu_desc = "torchaudio.compliance.kaldi.fbank per clip + mean subtraction, as the reference calls it"
+        elif key == "w2l":
+            # SURVEY 8(f)3 (not a BASELINE config): measured inside the default run's other_workloads block only
+            self.B, self.L, self.sr, self.n_mels = 256, 160000, 16000, 80
+            self.T = 1 + self.L // 200
+            self.out_shape = (self.B, self.n_mels, self.T)
+            self.kernel = "fe_wav2lip_kernel"
+            self.cpu_clips = 64
+            self.desc = ("SURVEY 8(f)3: Wav2Lip / Diff2Lip melspectrogram (Backend/diff2lip/audio/audio.py:45-51; pre-emphasis, "
+                         "n_fft 800, hop 200, 80 bins 55-7600 Hz, dB, [-4, 4]), 256 x 10 s @ 16 kHz per GPU")
+            self.featurizer = "wav2lip_mel"
+            self.traffic_key = None
+            self.cpu_desc = "oracle.wav2lip (the reference's numpy/scipy arithmetic, float64)"
         elif key == "cfg5":
             # the manifest sweep: a FIXED total of 10 000 clips, contiguous shards per rank (strong scaling), each shard
             # featurized in sub-batches of <= 512 clips like the manifest runner does
@@ -120,7 +132,7 @@ class Workload:
         else:
             raise ValueError(key)
         # algorithmic flops per audio-second (sparse mel, 2.5 N log2 N real-FFT model)
-        self.flops_per_audio_s = {"cfg2": 1.05e6, "cfg2pcm": None, "cfg3": 2.7e6, "cfg4": 1.4e6, "cfg5": 1.04e6}[key]
+        self.flops_per_audio_s = {"cfg2": 1.05e6, "cfg2pcm": None, "cfg3": 2.7e6, "cfg4": 1.4e6, "cfg5": 1.04e6, "w2l": 1.6e6}[key]
         self.audio_s_per_step = self.B * self.L / self.sr              # this rank's share
         self.scaling = "strong" if key == "cfg5" else "weak"
         # whole-job audio per step: fixed total for the sweep, per-GPU work x N otherwise
@@ -161,6 +173,8 @@ class Workload:
             return sweep
         if self.key == "cfg3":
             return lambda: fe.cosy_mel_batch(x, out=out)
+        if self.key == "w2l":
+            return lambda: fe.wav2lip_mel_batch(x, out=out)
         return lambda: fe.kaldi_fbank_batch(x, subtract_mean=True, out=out)
 
     def host_step(self, fe, xh, oh, dev):
@@ -379,7 +393,7 @@ def measure_light(fe, wl, dev, rank, world, steps, barrier, max_over_ranks):
                                                    "move: int16 PCM in + float32 features out; the float32 waveform in between is extra traffic",
                            "frac_whole_step": chain_bytes / 1e9 / (ms_step * 1e-3) / peak}
     else:
-        res["roofline"] = {"bound": "hbm" if wl.key != "cfg3" else "fp32", "frac": bytes_step / 1e9 / (k_ms_step * 1e-3) / peak,
+        res["roofline"] = {"bound": "hbm" if wl.key not in ("cfg3", "w2l") else "fp32", "frac": bytes_step / 1e9 / (k_ms_step * 1e-3) / peak,
                            "frac_whole_step": bytes_step / 1e9 / (ms_step * 1e-3) / peak if world == 1 or wl.scaling == "weak" else None,
                            "fp32_frac": wl.flops_per_audio_s * wl.audio_s_per_step / (k_ms_step * 1e-3) / 1e12 / FP32_PEAK_TFLOPS}
     return res
@@ -682,7 +696,7 @@ def run_ours(args, rank, world, local_rank):
         del xh, oh
         torch.cuda.empty_cache()
         others = {}
-        for key in ("cfg3", "cfg4", "cfg2pcm", "cfg5"):
+        for key in ("cfg3", "cfg4", "cfg2pcm", "w2l", "cfg5"):
             wl = Workload(key, rank, world)
             others[key] = measure_light(fe, wl, dev, rank, world, 3 if key == "cfg5" else min(args.steps, 5), barrier, max_over_ranks)
 

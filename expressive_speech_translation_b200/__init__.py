@@ -13,6 +13,9 @@ from .api import (  # noqa: F401
     fbank,
     whisper_log_mel_batch,
     whisper_log_mel_windows,
+    wav2lip_mel_batch,
+    wav2lip_num_frames,
+    melspectrogram,
     whisper_num_windows,
     cosy_mel_batch,
     cosy_prompt_feat,

@@ -227,6 +227,53 @@ def cosy_mel_batch(wave, lengths=None, out=None, frame_major=False):
     return out
 
 
+PAD_REFLECT, PAD_ZEROS = 0, 1
+_PAD_MODES = {"reflect": PAD_REFLECT, "constant": PAD_ZEROS}
+
+
+def wav2lip_num_frames(n_samples):
+    return 1 + int(n_samples) // 200
+
+
+def wav2lip_mel_batch(wave, lengths=None, out=None, frame_major=False, pad_mode="reflect"):
+    """(B, L) 16 kHz batch on a CUDA device -> (B, 80, 1 + L // 200) Wav2Lip / Diff2Lip mel in [-4, 4]
+    (/root/reference/Backend/diff2lip/audio/audio.py:45-51 with hparams.py:22-65); frame_major=True writes (B, T, 80), the
+    `.T` its callers take (generate.py:53).  pad_mode: what librosa.stft pads with -- "reflect" (librosa 0.9.2, the
+    reference's pin) or "constant" (librosa >= 0.10)."""
+    wave = _as_float_tensor(wave, "wav")
+    device = _cuda_device(wave.device if wave.is_cuda else None)
+    w, stride = _prep_wave(wave, device)
+    B, L = w.shape
+    T = wav2lip_num_frames(L)
+    shape = (B, T, 80) if frame_major else (B, 80, T)
+    if out is None:
+        out = torch.empty(shape, dtype=torch.float32, device=device)
+    elif out.shape != shape or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError(f"out must be a contiguous float32 {shape} tensor on the wave's device")
+    if B == 0:
+        return out
+    ln = _lengths_dev(lengths, B, device)
+    with torch.cuda.device(device):
+        rc = lib.b200feat_wav2lip_mel(_ptr(w), _ptr(ln), B, L, stride, _PAD_MODES[pad_mode], int(bool(frame_major)),
+                                      _ptr(out), 80 * T, T, _stream(device))
+    check(rc, "b200feat_wav2lip_mel")
+    return out
+
+
+def melspectrogram(wav):
+    """Drop-in for /root/reference/Backend/diff2lip/audio/audio.py:45 `melspectrogram(wav)`: 1-D waveform at 16 kHz
+    (numpy, as librosa.load returns it, or a torch tensor) -> (80, 1 + len // 200) in [-4, 4].  numpy in -> numpy out.
+    float32 (the reference's lfilter promotes to float64; the values agree within 1e-4)."""
+    is_np = not torch.is_tensor(wav)
+    w = _as_float_tensor(wav, "wav")
+    if w.dim() != 1:
+        raise ValueError(f"melspectrogram expects a 1-D wav, got shape {tuple(w.shape)}")
+    out = wav2lip_mel_batch(w[None])[0]
+    if is_np:
+        return out.cpu().numpy()
+    return out if w.is_cuda else out.cpu()
+
+
 def kaldi_fbank_batch(wave, lengths=None, subtract_mean=True, out=None):
     """(B, L) 16 kHz batch on a CUDA device -> (B, T, 80) kaldi fbank, optionally mean-normalised per clip."""
     wave = _as_float_tensor(wave, "waveform")
@@ -553,6 +600,7 @@ def install(verbose=False):
                ("whisper.transcribe", "log_mel_spectrogram", log_mel_spectrogram),
                ("whisper", "log_mel_spectrogram", log_mel_spectrogram),
                ("matcha.utils.audio", "mel_spectrogram", mel_spectrogram),
+               ("audio.audio", "melspectrogram", melspectrogram),        # Backend/diff2lip: `from audio import audio`
                ("torchaudio.compliance.kaldi", "fbank", fbank),
                ("torchaudio.functional", "resample", resample),
                ("torchaudio.transforms", "Resample", Resample)]

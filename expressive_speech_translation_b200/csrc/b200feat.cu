@@ -1015,19 +1015,24 @@ __global__ void __launch_bounds__(256) fe_kaldi_cmn_kernel(const FeKaldiParams p
 
 // One tile (16 frames) per CTA.  A multi-tile CTA with the next tile's loads in flight (as in the kaldi kernel) was
 // measured: 0.926 ms against 0.905 ms for 256 x 10 s, the tile load is not what this kernel waits for.
-__global__ void __launch_bounds__(FeCCfg::NT, 1) fe_cosy_kernel(const FeCosyParams p) {
+template <class C, int MINB>
+static __device__ __forceinline__ void fe_stft3_body(const FeCosyParams& p) {
     extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x, cta = blockIdx.x;
-    fe_c_phase_load(p, sm, tid, cta);
+    fe_c_phase_load<C>(p, sm, tid, cta);
     __syncthreads();
-    fe_c_phase_a(p, sm, tid, cta);
+    fe_c_phase_a<C>(p, sm, tid, cta);
     __syncthreads();
-    fe_c_phase_b(p, sm, tid, cta);
+    fe_c_phase_b<C>(p, sm, tid, cta);
     __syncthreads();
-    fe_c_phase_c(p, sm, tid, cta);
+    fe_c_phase_c<C>(p, sm, tid, cta);
     __syncthreads();
-    fe_c_phase_mel(p, sm, tid, cta);
+    fe_c_phase_mel<C>(p, sm, tid, cta);
 }
+__global__ void __launch_bounds__(FeCCfg::NT, 1) fe_cosy_kernel(const FeCosyParams p) { fe_stft3_body<FeCCfg, 1>(p); }
+// Wav2Lip / Diff2Lip mel: the same three stages with N = 800 = 16 x 5 x 10; 85 KB of shared
+// memory per CTA, two CTAs per SM
+__global__ void __launch_bounds__(FeLCfg::NT, 2) fe_wav2lip_kernel(const FeCosyParams p) { fe_stft3_body<FeLCfg, 2>(p); }
 
 // the eight instantiations (mel bins x output dtype x input dtype) behind one switch
 template <class F>
@@ -1241,6 +1246,7 @@ int check_device_arch() {
             FE_CUDA(cudaFuncSetAttribute(fe_kaldi3_cmn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          FE_K3_CMN_SMEM_ROWS * (FeK3Cfg::NMEL / 2) * 4));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_wav2lip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeLCfg::SMEM_BYTES));
             state[dev] = 1;
         }
     }
@@ -1577,6 +1583,44 @@ int b200feat_cosy_mel_frames(const float* wave, const int64_t* lengths, int32_t 
                              int64_t wave_stride, float* out, int64_t out_batch_stride, int64_t T_out,
                              void* workspace, int64_t workspace_bytes, void* cuda_stream) {
     return cosy_mel_impl(wave, lengths, B, L, wave_stride, out, true, out_batch_stride, T_out, workspace, workspace_bytes, cuda_stream);
+}
+
+// ------------------------------------------------------------------------------------------ Wav2Lip / Diff2Lip mel
+int64_t b200feat_wav2lip_num_frames(int64_t n_samples) { return n_samples < 0 ? -1 : 1 + n_samples / FeLCfg::HOP; }
+
+int b200feat_wav2lip_mel(const float* wave, const int64_t* lengths, int32_t B, int64_t L, int64_t wave_stride,
+                         int32_t pad_mode, int32_t frame_major, float* out, int64_t out_batch_stride, int64_t T_out,
+                         void* cuda_stream) {
+    if (int rc = common_checks("wav2lip_mel", wave, out, B, L, wave_stride)) return rc;
+    if (pad_mode != B200FEAT_PAD_REFLECT && pad_mode != B200FEAT_PAD_ZEROS)
+        return fail(B200FEAT_EINVAL, "wav2lip_mel: pad_mode %d (B200FEAT_PAD_REFLECT or B200FEAT_PAD_ZEROS)", pad_mode);
+    const int64_t T_full = b200feat_wav2lip_num_frames(L);
+    if (T_out < T_full) return fail(B200FEAT_EINVAL, "wav2lip_mel: T_out %lld < %lld frames", (long long)T_out, (long long)T_full);
+    if (out_batch_stride < (int64_t)FeLCfg::NMEL * T_out) return fail(B200FEAT_EINVAL, "wav2lip_mel: out_batch_stride too small");
+    if (pad_mode == B200FEAT_PAD_REFLECT && L <= FeLCfg::PADL && B > 0)
+        return fail(B200FEAT_EINVAL, "wav2lip_mel: reflect padding (400) needs more than 400 samples, got %lld", (long long)L);
+    if (B == 0 || T_out == 0) return 0;
+    if (int rc = check_device_arch()) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    FeCosyParams p;
+    memset(&p, 0, sizeof(p));
+    p.wave = wave; p.lengths = lengths; p.wave_stride = wave_stride; p.L = L; p.B = B;
+    p.out = out; p.out_batch_stride = out_batch_stride; p.T_out = T_out; p.frame_major = frame_major ? 1 : 0;
+    p.pad_mode = pad_mode;
+    const int64_t tiles = (T_out + FeLCfg::FT - 1) / FeLCfg::FT;
+    p.tiles_per_clip = (int32_t)tiles;
+    p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
+    const int64_t per_launch = 0x7fffffff / tiles;
+    if (per_launch < 1) return fail(B200FEAT_EINVAL, "wav2lip_mel: clip too long");
+    for (int64_t c0 = 0; c0 < B; c0 += per_launch) {
+        const int64_t nc = (B - c0 < per_launch) ? (B - c0) : per_launch;
+        p.clip0 = (int32_t)c0; p.nclips = (int32_t)nc;
+        ProfScope ps(st, 0);
+        fe_wav2lip_kernel<<<(unsigned)(nc * tiles), FeLCfg::NT, FeLCfg::SMEM_BYTES, st>>>(p);
+        g_launches++;
+    }
+    FE_CUDA(cudaGetLastError());
+    return 0;
 }
 
 // ------------------------------------------------------------------------------------------ kaldi

@@ -14,6 +14,7 @@
 #define FE_HD __device__
 #define FE_INLINE __forceinline__
 #define FE_CONSTANT __constant__ const
+#define FE_TABLE __device__ const       // tables that do not fit the 64 KB constant bank: global memory, read through L1
 // lg2.approx.ftz: one MUFU, max abs error 2^-22 on log2; every caller floors its argument at a
 // normal number first (1e-10, 1e-5, FLT_EPSILON), so flushing subnormals never triggers
 static __device__ __forceinline__ float fe_lg2_ftz(float x) {
@@ -27,6 +28,7 @@ static __device__ __forceinline__ float fe_lg2_ftz(float x) {
 #define FE_HD
 #define FE_INLINE inline __attribute__((always_inline))
 #define FE_CONSTANT static const
+#define FE_TABLE static const
 #define FE_LOG2(x) log2f(x)
 #define FE_SQRT(x) sqrtf(x)
 struct float2 { float x, y; };
@@ -167,6 +169,7 @@ struct FeCosyParams {
     int32_t tiles_per_clip;    // ceil(T_out / 16)
     int32_t vec_ok;
     int32_t clip0, nclips;     // clips [clip0, clip0 + nclips) are processed by this launch
+    int32_t pad_mode;          // Wav2Lip mel only: 0 = reflect (librosa 0.9.2, the reference's pin), 1 = zeros (librosa >= 0.10)
 };
 
 struct FeKaldiParams {

@@ -181,6 +181,26 @@ int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, cons
                       int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width, double rolloff,
                       int32_t method, double beta, float* out, int64_t out_stride, int64_t L_out, void* cuda_stream);
 
+/* Wav2Lip / Diff2Lip mel.  Replaces, for a batch of clips,
+ *     /root/reference/Backend/diff2lip/audio/audio.py:45-51  melspectrogram(wav)
+ * with the parameters of /root/reference/Backend/diff2lip/audio/hparams.py:22-65, as called at
+ * /root/reference/Backend/diff2lip/generate.py:53 and generate_dist.py:49 (`audio.melspectrogram(wav).T`):
+ *   pre-emphasis y[n] = x[n] - 0.97 x[n-1] (audio.py:19-22) | librosa.stft(n_fft 800, hop 200, win 800, periodic Hann,
+ *   center=True) | magnitude | 80 Slaney filters 55..7600 Hz (librosa.filters.mel, audio.py:99-103) |
+ *   20 log10(max(1e-5, .)) - 20 (audio.py:105-107, :47) | clip(8 (S + 100) / 100 - 4, -4, 4) (audio.py:112-118).
+ * wave: (B, wave_stride) float32 at 16 kHz; out: (B, 80, T_out) float32 -- melspectrogram's layout -- or, frame_major != 0,
+ * (B, T_out, 80), the `.T` the callers take; T_out >= b200feat_wav2lip_num_frames(L) = 1 + L / 200.  Ragged clips
+ * (`lengths`): frames past 1 + len / 200 are 0.
+ * pad_mode: the padding librosa.stft applies after the pre-emphasis -- B200FEAT_PAD_REFLECT is librosa 0.9.2's default, the
+ * version the reference pins (/root/reference/Backend/requirements.txt:14; needs clips of more than 400 samples);
+ * B200FEAT_PAD_ZEROS is the default of librosa >= 0.10.
+ * The reference computes this mel in float64 (lfilter promotes); this is float32, within 1e-4 of it in the [-4, 4] scale. */
+enum { B200FEAT_PAD_REFLECT = 0, B200FEAT_PAD_ZEROS = 1 };
+int64_t b200feat_wav2lip_num_frames(int64_t n_samples);
+int b200feat_wav2lip_mel(const float* wave, const int64_t* lengths, int32_t B, int64_t L, int64_t wave_stride,
+                         int32_t pad_mode, int32_t frame_major, float* out, int64_t out_batch_stride, int64_t T_out,
+                         void* cuda_stream);
+
 /* Host-buffer variants (the end-to-end path): wave_host / out_host are HOST pointers (pinned memory
  * gives full PCIe bandwidth); clips are streamed through a library-owned device arena in chunks with
  * H2D copy, kernels and D2H copy overlapped on internal streams.  Blocks until out_host is complete.

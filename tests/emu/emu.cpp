@@ -366,25 +366,34 @@ extern "C" int emu_kaldi3(const float* wave, const int64_t* lengths, int B, int6
 
 // ------------------------------------------------------------------------------------------ cosy
 #include "fe_cosy.cuh"
-extern "C" int emu_cosy(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
-                        float* out, int64_t T_out) {
-    typedef FeCCfg C;
+template <class C>
+static int emu_stft3(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride, float* out, int64_t T_out,
+                     int frame_major, int pad_mode) {
     FeCosyParams p;
     memset(&p, 0, sizeof(p));
     p.wave = wave; p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B;
-    p.out = out; p.out_batch_stride = T_out * 80; p.T_out = T_out;
+    p.out = out; p.out_batch_stride = T_out * 80; p.T_out = T_out; p.frame_major = frame_major; p.pad_mode = pad_mode;
     p.tiles_per_clip = (int)((T_out + C::FT - 1) / C::FT);
     p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
     p.clip0 = 0; p.nclips = B;
     std::vector<float> sm(C::SMEM_FLOATS);
     for (int cta = 0; cta < B * p.tiles_per_clip; ++cta) {
-        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_load(p, sm.data(), tid, cta);
-        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_a(p, sm.data(), tid, cta);
-        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_b(p, sm.data(), tid, cta);
-        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_c(p, sm.data(), tid, cta);
-        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_mel(p, sm.data(), tid, cta);
+        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_load<C>(p, sm.data(), tid, cta);
+        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_a<C>(p, sm.data(), tid, cta);
+        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_b<C>(p, sm.data(), tid, cta);
+        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_c<C>(p, sm.data(), tid, cta);
+        for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_mel<C>(p, sm.data(), tid, cta);
     }
     return 0;
+}
+extern "C" int emu_cosy(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                        float* out, int64_t T_out) {
+    return emu_stft3<FeCCfg>(wave, lengths, B, L, stride, out, T_out, 0, 0);
+}
+// Wav2Lip / Diff2Lip mel (FeLCfg): out (B, 80, T_out) or, frame_major, (B, T_out, 80)
+extern "C" int emu_wav2lip(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride,
+                           float* out, int64_t T_out, int frame_major, int pad_mode) {
+    return emu_stft3<FeLCfg>(wave, lengths, B, L, stride, out, T_out, frame_major, pad_mode);
 }
 
 // ------------------------------------------------------------------------------------------ resample

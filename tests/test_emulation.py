@@ -204,6 +204,44 @@ def test_cosy_speech_zeros_ragged(emu):
     assert not got[1, :, ref.shape[1]:].any()
 
 
+# ------------------------------------------------------------------------------------------------ Wav2Lip / Diff2Lip mel
+def emu_wav2lip(emu, x, lengths=None, frame_major=False, pad_mode=0):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    B, L = x.shape
+    T = 1 + L // 200
+    out = np.full((B, T, 80) if frame_major else (B, 80, T), 7.0, dtype=np.float32)
+    keep, lp = _lens(lengths)
+    assert emu.emu_wav2lip(x.ctypes.data_as(vp), lp, B, L, L, out.ctypes.data_as(vp), T, int(frame_major), pad_mode) == 0
+    return out
+
+
+def test_wav2lip_mel_against_the_reference_restatement(emu):
+    """the kernel's phases (N = 800 = 16 x 5 x 10, pre-emphasis and reflect padding in the loader) against
+    oracle.wav2lip (the reference's audio.py:45-51 in its own float64 arithmetic): <= 1e-4 in the normalised [-4, 4]
+    scale; noise, speech-like, a sine, silence, ragged clips, zero padding mode, frame-major layout."""
+    from oracle import wav2lip as w2l
+    gen = torch.Generator().manual_seed(8)
+    x = np.concatenate([(0.1 * torch.randn(1, 9000, generator=gen)).clamp(-1, 1).numpy(), speech_like(gen, 2, 9000, 16000).numpy()])
+    x[2] *= 0.01                                   # a quiet clip: bins near the 1e-5 floor
+    got = emu_wav2lip(emu, x)
+    for b in range(3):
+        ref = w2l.wav2lip_mel(x[b])
+        assert got[b].shape == ref.shape and np.abs(got[b] - ref).max() <= 1e-4, b
+    assert np.array_equal(emu_wav2lip(emu, x, frame_major=True), got.transpose(0, 2, 1))
+    for b in range(3):
+        assert np.abs(emu_wav2lip(emu, x, pad_mode=1)[b] - w2l.wav2lip_mel(x[b], pad_mode="constant")).max() <= 1e-4
+    t = np.arange(8000) / 16000.0
+    s = (0.5 * np.sin(2 * np.pi * 440 * t)).astype(np.float32)[None]
+    assert np.abs(emu_wav2lip(emu, s)[0] - w2l.wav2lip_mel(s[0])).max() <= 1e-4
+    z = emu_wav2lip(emu, np.zeros((1, 3000), np.float32))
+    assert np.all(z == -4.0)                        # 20 log10(1e-5) - 20 = -120 dB -> clipped at -max_abs_value
+    got = emu_wav2lip(emu, x, lengths=[9000, 4567, 401])
+    for b, n in enumerate([9000, 4567, 401]):
+        ref = w2l.wav2lip_mel(x[b, :n])
+        assert np.abs(got[b, :, :ref.shape[1]] - ref).max() <= 1e-4
+        assert not got[b, :, ref.shape[1]:].any()
+
+
 # ------------------------------------------------------------------------------------------------ Tensor-Memory kernel
 @pytest.mark.parametrize("B,L,nm,pad", [(2, 48000, 80, 0), (1, 12345, 128, 777), (3, 4000, 128, 0), (1, 8000, 80, 48000),
                                         (1, 160 * 300 + 57, 128, 0)])

@@ -404,6 +404,8 @@ def main():
     cl.append(gen_codelet("fe_rdft16_h9", 16, real_in=True, outs=range(9), real_out=(0, 8)))
     cl.append(gen_codelet("fe_cdft12", 12))
     cl.append(gen_codelet("fe_cdft10", 10))
+    # Wav2Lip / Diff2Lip: N = 800 = 16 x 5 x 10 (shares fe_rdft16_h9 and fe_cdft10 with CosyVoice)
+    cl.append(gen_codelet("fe_cdft5", 5))
     with open(os.path.join(OUT, "fe_codelets.h"), "w") as f:
         f.write("\n".join(cl))
 
@@ -487,11 +489,24 @@ def main():
     tb.append(gen_mel_segments("fe_k3_mel", kb[:, :256], 16))
     tb.append(gen_melrolled("fe_melroll_cosy", cz, 640))
     tb.append(gen_melproj("fe_melproj_kaldi", kb, 16, 255))
+    # ---- Wav2Lip / Diff2Lip mel (fe_cosy.cuh, FeLCfg): N = 800 = 16 x 5 x 10.  These tables live in global memory
+    # (FE_TABLE): the 64 KB constant bank is full.
+    def table(txt):
+        return txt.replace("FE_CONSTANT", "FE_TABLE")
+    n = np.arange(800, dtype=np.float64)
+    tb.append("// periodic Hann, N = 800 (librosa.stft window='hann', fftbins=True)")
+    tb.append(table(emit_array("fe_win_w2l", 0.5 - 0.5 * np.cos(2 * np.pi * n / 800.0))))
+    tb.append("// Wav2Lip stage-A twiddles W_800^(m*k1), [m = 0..49][k1 = 0..8]")
+    tb.append(table(emit_array("fe_tw_w2l_a", twiddle_table(800, 50, 9))))
+    tb.append("// Wav2Lip stage-B twiddles W_50^(n3*k2), [n3 = 0..9][k2 = 0..4]")
+    tb.append(table(emit_array("fe_tw_w2l_b", twiddle_table(50, 10, 5))))
+    wl = slaney(16000, 800, 80, 55.0, 7600.0)
+    tb.append(table(gen_melrolled("fe_melroll_w2l", wl, 401)))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
         f.write("\n".join(tb))
     # the float32 tables the kernels bake, for the parity tests (tests/ compares them to the oracle's)
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", "baked_filters.npz"),
-                        whisper80=w80, whisper128=w128, cosy80=cz, kaldi80=kb)
+                        whisper80=w80, whisper128=w128, cosy80=cz, kaldi80=kb, w2l80=wl)
     print("wrote", OUT)
 
 
