@@ -27,7 +27,12 @@ struct FeS3Cfg : P {
     static constexpr int R1 = 16;
     static constexpr int M = P::R2 * P::R3;
     static constexpr int NK1 = R1 / 2 + 1;               // 9
-    static constexpr int FT = 16;                        // frames per tile (half a warp)
+    // Frames per tile: half a warp, two task slots per warp.  (Measured and dropped in round 2: FT = 8 with four slots per
+    // warp and conflict-free strides, so that two CTAs of the N = 1920 instance fit an SM -- 2.04 ms against 0.90 ms per
+    // 256 x 10 s, and 0.51 against 0.44 ms for N = 800: the window / twiddle / mel-weight reads are indexed constant loads
+    // with one address per slot, four slots replay them four times, and the kernel is MIO-bound to begin with --
+    // stall mio_throttle 3.0 per issue, profiles/r02_stft3_ncu_summary.txt.)
+    static constexpr int FT = 16;
     static constexpr int NW = 16, NT = NW * 32;
     static constexpr int RT = (FT - 1) * P::HOP + P::N;  // samples a tile reads
     static constexpr int SW = RT + RT / P::HOP + 2;
