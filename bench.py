@@ -156,12 +156,8 @@ class Workload:
 
     def device_step(self, fe, x, out):
         if self.key == "cfg2pcm":
-            wav = torch.empty((self.B, self.L), dtype=torch.float32, device=x.device)
-
-            def chain():
-                fe.condition_pcm(x, self.pcm_sr, self.sr, out=wav)
-                fe.whisper_log_mel_batch(wav, n_mels=self.n_mels, norm="per_clip", out=out)
-            return chain
+            # ONE library call: mono mix + resampler, then the log-mel kernels; the waveform lives in the call's workspace
+            return lambda: fe.pcm_whisper_log_mel_batch(x, self.pcm_sr, self.sr, n_mels=self.n_mels, norm="per_clip", out=out)
         if self.key == "cfg2":
             return lambda: fe.whisper_log_mel_batch(x, n_mels=self.n_mels, norm="per_clip", out=out)
         if self.key == "cfg5":
@@ -179,25 +175,8 @@ class Workload:
 
     def host_step(self, fe, xh, oh, dev):
         if self.key == "cfg2pcm":
-            # pinned int16 PCM in -> pinned float32 features out, 128 clips at a time on two streams so that the copies of
-            # one slice overlap the kernels of the other (the library has no host-buffer twin of the resampler yet)
-            streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
-            n = 128
-            xd = [torch.empty((n,) + tuple(xh.shape[1:]), dtype=torch.int16, device=dev) for _ in streams]
-            wd = [torch.empty((n, self.L), dtype=torch.float32, device=dev) for _ in streams]
-            od = [torch.empty((n,) + tuple(self.out_shape[1:]), dtype=torch.float32, device=dev) for _ in streams]
-
-            def chain_host():
-                for i, (lo, hi) in enumerate(manifest.sub_batches(0, xh.shape[0], n)):
-                    k, m = i % 2, hi - lo
-                    with torch.cuda.stream(streams[k]):
-                        xd[k][:m].copy_(xh[lo:hi], non_blocking=True)
-                        fe.condition_pcm(xd[k][:m], self.pcm_sr, self.sr, out=wd[k][:m])
-                        fe.whisper_log_mel_batch(wd[k][:m], n_mels=self.n_mels, norm="per_clip", out=od[k][:m])
-                        oh[lo:hi].copy_(od[k][:m], non_blocking=True)
-                for st in streams:
-                    st.synchronize()
-            return chain_host
+            # pinned int16 PCM in -> pinned float32 features out through the library's chunked pipeline (b200feat_pcm_whisper_logmel_host)
+            return lambda: fe.pcm_whisper_log_mel_host(xh, self.pcm_sr, self.sr, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
         if self.key in ("cfg2", "cfg5"):
             return lambda: fe.whisper_log_mel_host(xh, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
         if self.key == "cfg3":
@@ -625,7 +604,7 @@ def run_ours(args, rank, world, local_rank):
            "ms_per_step": e2e_ms, "steps": e2e_steps, "clips_per_step_per_gpu": ne, "host_cpus_bound": len(bound) if bound else None,
            "api": (f"{WL.featurizer}_host -> b200feat_*_host (pinned host buffers, chunked H2D/kernel/D2H pipeline, blocking)"
                    if WL.key != "cfg2pcm" else
-                   "pinned int16 PCM -> condition_pcm + whisper_log_mel_batch on two streams, 128 clips per slice -> pinned float32 features")}
+                   "pcm_whisper_log_mel_host -> b200feat_pcm_whisper_logmel_host (pinned int16 PCM in, chunked H2D / resample / log-mel / D2H, blocking)")}
 
     if alone_ms is not None:
         alone = ne * WL.L / WL.sr / (alone_ms * 1e-3)

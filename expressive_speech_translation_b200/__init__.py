@@ -24,6 +24,10 @@ from .api import (  # noqa: F401
     cosy_mel_host,
     kaldi_fbank_host,
     condition_pcm,
+    condition_stereo_auto,
+    pcm_whisper_log_mel_batch,
+    pcm_whisper_log_mel_host,
+    REFERENCE_RESAMPLER,
     resample,
     resample_out_len,
     Resample,

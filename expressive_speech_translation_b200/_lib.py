@@ -63,6 +63,19 @@ SYMBOLS = {
     "b200feat_wav2lip_num_frames": (_c.c_int64, [_c.c_int64]),
     "b200feat_wav2lip_mel": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64, _c.c_int32, _c.c_int32,
                                         _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p]),
+    "b200feat_condition_stereo_auto": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64,
+                                                  _c.c_int32, _c.c_int32, _c.c_int32, _c.c_double, _c.c_int32, _c.c_double,
+                                                  _c.c_void_p, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p,
+                                                  _c.c_void_p, _c.c_void_p]),
+    "b200feat_pcm_whisper_workspace_bytes": (_c.c_int64, [_c.c_int32, _c.c_int64, _c.c_int32, _c.c_int32, _c.c_int32]),
+    "b200feat_pcm_whisper_logmel": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_void_p, _c.c_int32,
+                                               _c.c_int64, _c.c_int64, _c.c_int32, _c.c_int32, _c.c_int32, _c.c_double,
+                                               _c.c_int32, _c.c_double, _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p,
+                                               _c.c_int32, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64, _c.c_void_p]),
+    "b200feat_pcm_whisper_logmel_host": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_void_p, _c.c_int32,
+                                                    _c.c_int64, _c.c_int32, _c.c_int32, _c.c_int32, _c.c_double, _c.c_int32,
+                                                    _c.c_double, _c.c_int32, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_int32,
+                                                    _c.c_int32]),
     "b200feat_profile_begin": (_c.c_int, []),
     "b200feat_profile_end": (_c.c_int, [_c.POINTER(_c.c_double), _c.POINTER(_c.c_int64), _c.POINTER(_c.c_double),
                                         _c.POINTER(_c.c_int64)]),

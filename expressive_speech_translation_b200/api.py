@@ -534,6 +534,133 @@ def condition_pcm(pcm, orig_freq, new_freq, lengths=None, mix=None, lowpass_filt
     return out
 
 
+# /root/reference/Backend/services/audio_processor.py:296-303: the filter the reference's AudioProcessor deploys
+REFERENCE_RESAMPLER = dict(lowpass_filter_width=128, rolloff=0.95, resampling_method="sinc_interp_kaiser", beta=14.769656459379492)
+
+
+def _pcm_tensor(pcm):
+    if isinstance(pcm, np.ndarray):
+        pcm = torch.from_numpy(pcm)
+    if not torch.is_tensor(pcm):
+        raise TypeError(f"pcm must be a torch.Tensor or numpy.ndarray, got {type(pcm).__name__}")
+    if pcm.dtype != torch.int16:
+        if not pcm.is_floating_point():
+            raise TypeError(f"Expected floating point type for waveform tensor, but received {pcm.dtype}.")
+        pcm = pcm if pcm.dtype == torch.float32 else pcm.to(torch.float32)
+    if pcm.dim() == 2:
+        pcm = pcm.unsqueeze(-1)
+    if pcm.dim() != 3 or pcm.shape[2] not in (1, 2):
+        raise ValueError(f"expected (B, L) or (B, L, C) PCM with C in (1, 2), got shape {tuple(pcm.shape)}")
+    return pcm
+
+
+def _rs_args(orig_freq, new_freq, lowpass_filter_width, rolloff, resampling_method, beta):
+    if not (int(orig_freq) == orig_freq and int(new_freq) == new_freq):
+        raise Exception("Frequencies must be of integer type to ensure quality resampling computation.")
+    if orig_freq <= 0.0 or new_freq <= 0.0:
+        raise ValueError("Original frequency and desired frequecy should be positive")
+    if resampling_method not in _RS_METHODS:
+        raise ValueError("Invalid resampling method: {}".format(resampling_method))
+    if lowpass_filter_width <= 0:
+        raise ValueError("Low pass filter width should be positive.")
+    return (int(orig_freq), int(new_freq), int(lowpass_filter_width), float(rolloff), _RS_METHODS[resampling_method],
+            14.769656459379492 if beta is None else float(beta))
+
+
+def condition_stereo_auto(pcm, orig_freq, new_freq, lengths=None, lowpass_filter_width=128, rolloff=0.95,
+                          resampling_method="sinc_interp_kaiser", beta=14.769656459379492, return_decisions=False):
+    """The reference's conditioning of a stereo clip, batched, on the device
+    (/root/reference/Backend/services/audio_processor.py:294-319): resample BOTH channels (defaults = the reference's
+    kaiser filter), take the inter-channel correlation of the resampled channels, and mix per clip:
+    mean of the channels if correlation > 0.5, else mid + 0.3 * side.  pcm: (B, L, 2) int16 or float32 ->
+    (B, ceil(new * L / orig)) float32 [, (decisions int32 (B,), correlations float32 (B,))]."""
+    x = _pcm_tensor(pcm)
+    if x.shape[2] != 2:
+        raise ValueError("condition_stereo_auto expects (B, L, 2) stereo PCM")
+    of, nf, width, ro, meth, bt = _rs_args(orig_freq, new_freq, lowpass_filter_width, rolloff, resampling_method, beta)
+    device = _cuda_device(x.device if x.is_cuda else None)
+    x = x.to(device).contiguous()
+    B, L, C = x.shape
+    L_out = resample_out_len(L, of, nf)
+    out = torch.empty((B, L_out), dtype=torch.float32, device=device)
+    scratch = torch.empty((B, L_out), dtype=torch.float32, device=device)
+    dec = torch.empty((B,), dtype=torch.int32, device=device)
+    cor = torch.empty((B,), dtype=torch.float32, device=device)
+    ld = _lengths_dev(lengths, B, device)
+    with torch.cuda.device(device):
+        check(lib.b200feat_condition_stereo_auto(_ptr(x), _DTYPES[x.dtype], _ptr(ld), B, L, L * C, of, nf, width, ro, meth, bt,
+                                                 _ptr(out), L_out, L_out, _ptr(scratch), scratch.numel(), _ptr(dec), _ptr(cor),
+                                                 _stream(device)), "b200feat_condition_stereo_auto")
+    return (out, (dec, cor)) if return_decisions else out
+
+
+def pcm_whisper_log_mel_batch(pcm, orig_freq, new_freq=WHISPER_SR, lengths=None, mix=None, n_mels=80, padding=0, norm="per_clip",
+                              out=None, out_dtype=torch.float32, lowpass_filter_width=6, rolloff=0.99,
+                              resampling_method="sinc_interp_hann", beta=None):
+    """PCM in, Whisper log-mel out, ONE library call on the device: (B, L) / (B, L, C) int16 or float32 PCM at orig_freq
+    -> mono mix + resample to 16 kHz -> (B, n_mels, (ceil(16000 * L / orig) + padding) // 160).  The waveform in between lives
+    in the call's workspace.  Same result as whisper_log_mel_batch(condition_pcm(pcm, ...), ...), bit for bit.
+    `lengths` = input frames per clip."""
+    assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
+    x = _pcm_tensor(pcm)
+    of, nf, width, ro, meth, bt = _rs_args(orig_freq, new_freq, lowpass_filter_width, rolloff, resampling_method, beta)
+    device = _cuda_device(x.device if x.is_cuda else None)
+    x = x.to(device).contiguous()
+    B, L, C = x.shape
+    Lw = resample_out_len(L, of, nf)
+    T = (Lw + int(padding)) // WHISPER_HOP
+    if out is None:
+        out = torch.empty((B, n_mels, T), dtype=out_dtype, device=device)
+    elif out.shape != (B, n_mels, T) or not out.is_contiguous() or out.device != device:
+        raise ValueError("out must be a contiguous float32 / float16 (B, n_mels, T) tensor on the PCM's device")
+    if B == 0 or T == 0:
+        return out
+    mix_arr = None
+    if mix is not None:
+        if len(mix) != C:
+            raise ValueError(f"mix has {len(mix)} weights for {C} channel(s)")
+        mix_arr = (ctypes.c_float * C)(*[float(v) for v in mix])
+    ld = _lengths_dev(lengths, B, device)
+    nws = int(lib.b200feat_pcm_whisper_workspace_bytes(B, L, of, nf, int(padding)))
+    ws = torch.empty(nws, dtype=torch.uint8, device=device)
+    with torch.cuda.device(device):
+        check(lib.b200feat_pcm_whisper_logmel(_ptr(x), _DTYPES[x.dtype], C, mix_arr, _ptr(ld), B, L, L * C, of, nf, width, ro, meth, bt,
+                                              n_mels, int(padding), _NORMS[norm], _ptr(out), _DTYPES[out_dtype], n_mels * T, T,
+                                              _ptr(ws), nws, _stream(device)), "b200feat_pcm_whisper_logmel")
+    return out
+
+
+def pcm_whisper_log_mel_host(pcm, orig_freq, new_freq=WHISPER_SR, lengths=None, mix=None, n_mels=80, padding=0, norm="per_clip",
+                             out=None, out_dtype=torch.float32, device=None, pin_output=True, lowpass_filter_width=6,
+                             rolloff=0.99, resampling_method="sinc_interp_hann", beta=None):
+    """The host-buffer twin: host (ideally pinned) int16 / float32 PCM -> host log-mel through the library's chunked
+    H2D / resample / log-mel / D2H pipeline.  PCM crosses PCIe, the float32 waveform never does.  Blocks."""
+    assert n_mels in {80, 128}, f"Unsupported n_mels: {n_mels}"
+    out_dtype = _out_dtype(out.dtype if out is not None else out_dtype)
+    x = _pcm_tensor(pcm)
+    if x.is_cuda:
+        raise ValueError("pcm: the *_host entry points take host memory")
+    x = x.contiguous()
+    of, nf, width, ro, meth, bt = _rs_args(orig_freq, new_freq, lowpass_filter_width, rolloff, resampling_method, beta)
+    B, L, C = x.shape
+    Lw = resample_out_len(L, of, nf)
+    T = (Lw + int(padding)) // WHISPER_HOP
+    dev = _cuda_device(device)
+    out = _host_out((B, n_mels, T), out, pin_output, out_dtype)
+    mix_arr = None
+    if mix is not None:
+        if len(mix) != C:
+            raise ValueError(f"mix has {len(mix)} weights for {C} channel(s)")
+        mix_arr = (ctypes.c_float * C)(*[float(v) for v in mix])
+    ln = _host_lengths(lengths, B)
+    if B and T:
+        check(lib.b200feat_pcm_whisper_logmel_host(_ptr(x), _DTYPES[x.dtype], C, mix_arr, _ptr(ln), B, L, of, nf, width, ro, meth, bt,
+                                                   n_mels, int(padding), _NORMS[norm], _ptr(out), _DTYPES[out_dtype], dev.index),
+              "b200feat_pcm_whisper_logmel_host")
+    return out
+
+
 def resample(waveform, orig_freq: int, new_freq: int, lowpass_filter_width: int = 6, rolloff: float = 0.99,
              resampling_method: str = "sinc_interp_hann", beta=None):
     """torchaudio.functional.resample (functional.py:1435): `(..., time)` -> `(..., ceil(new * time / orig))`, same

@@ -1034,6 +1034,63 @@ __global__ void __launch_bounds__(FeCCfg::NT, 1) fe_cosy_kernel(const FeCosyPara
 // memory per CTA, two CTAs per SM
 __global__ void __launch_bounds__(FeLCfg::NT, 2) fe_wav2lip_kernel(const FeCosyParams p) { fe_stft3_body<FeLCfg, 2>(p); }
 
+// =====================================================================================================
+// waveform conditioning: the reference's stereo -> mono rule, and the glue of the one-call PCM -> log-mel path
+// =====================================================================================================
+// /root/reference/Backend/services/audio_processor.py:307-319, applied to the RESAMPLED channels r0 / r1 of a clip:
+//     correlation = sum(r0 * r1) / sqrt(sum(r0 ** 2) * sum(r1 ** 2))
+//     audio = mean(r0, r1)                 if correlation > 0.5
+//           = mid + 0.3 * side             otherwise   (mid = (r0 + r1) / 2, side = (r0 - r1) / 2)
+// One CTA per clip: pass 1 = the three sums (float64 accumulators, fixed reduction order: deterministic), pass 2 = the mix,
+// written over r0, with the reference's own float32 operations (no FMA contraction).  r1's second read comes from L2.
+__global__ void __launch_bounds__(1024) fe_mono_auto_kernel(float* __restrict__ r0, const float* __restrict__ r1, int64_t stride,
+                                                            int64_t n, int32_t* __restrict__ decision, float* __restrict__ corr_out) {
+    __shared__ double red[3][32];
+    __shared__ int use_mean;
+    float* __restrict__ a = r0 + (int64_t)blockIdx.x * stride;
+    const float* __restrict__ b = r1 + (int64_t)blockIdx.x * stride;
+    double s01 = 0.0, s00 = 0.0, s11 = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const double x = a[i], y = b[i];
+        s01 += x * y; s00 += x * x; s11 += y * y;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        s01 += __shfl_xor_sync(0xffffffffu, s01, o);
+        s00 += __shfl_xor_sync(0xffffffffu, s00, o);
+        s11 += __shfl_xor_sync(0xffffffffu, s11, o);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { red[0][warp] = s01; red[1][warp] = s00; red[2][warp] = s11; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t01 = 0.0, t00 = 0.0, t11 = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { t01 += red[0][w]; t00 += red[1][w]; t11 += red[2][w]; }
+        // 0 / 0 = NaN for a silent channel, and NaN > 0.5 is false: the mid / side branch, as in the reference
+        const float c = (float)(t01 / sqrt(t00 * t11));
+        use_mean = c > 0.5f ? 1 : 0;
+        if (decision) decision[blockIdx.x] = use_mean;
+        if (corr_out) corr_out[blockIdx.x] = c;
+    }
+    __syncthreads();
+    const bool mean = use_mean != 0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const float x = a[i], y = b[i];
+        const float mid = __fmul_rn(__fadd_rn(x, y), 0.5f);                       // torch.mean over 2 rows == (x + y) / 2
+        a[i] = mean ? mid : __fadd_rn(mid, __fmul_rn(0.3f, __fmul_rn(__fsub_rn(x, y), 0.5f)));
+    }
+}
+
+// input frames per clip -> resampled samples per clip, ceil(new * len / orig) with the reduced ratio (fe_rs_out_len)
+__global__ void fe_rs_lengths_kernel(const int64_t* __restrict__ in_len, int64_t* __restrict__ out_len, int32_t B, int64_t L_in,
+                                     int64_t orig_r, int64_t new_r, int64_t L_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B) return;
+    int64_t n = in_len[i];
+    n = n < 0 ? 0 : (n > L_in ? L_in : n);
+    int64_t o = (new_r * n + orig_r - 1) / orig_r;
+    out_len[i] = o > L_out ? L_out : o;
+}
+
 // the eight instantiations (mel bins x output dtype x input dtype) behind one switch
 template <class F>
 static int whisper2_for_each(F f) {
@@ -1823,6 +1880,75 @@ int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, cons
     }
     FE_CUDA(cudaGetLastError());
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------ conditioning, reference rule
+int b200feat_condition_stereo_auto(const void* pcm, int32_t pcm_dtype, const int64_t* lengths, int32_t B, int64_t L_in,
+                                   int64_t pcm_stride, int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width,
+                                   double rolloff, int32_t method, double beta, float* out, int64_t out_stride, int64_t L_out,
+                                   float* scratch, int64_t scratch_floats, int32_t* decisions, float* correlations,
+                                   void* cuda_stream) {
+    if (B > 0 && L_out > 0 && scratch == nullptr) return fail(B200FEAT_EINVAL, "condition_stereo_auto: null scratch");
+    if (scratch_floats < (int64_t)B * out_stride)
+        return fail(B200FEAT_EWORKSPACE, "condition_stereo_auto: scratch holds %lld floats, need B * out_stride = %lld",
+                    (long long)scratch_floats, (long long)((int64_t)B * out_stride));
+    const float only0[2] = {1.0f, 0.0f}, only1[2] = {0.0f, 1.0f};
+    if (int rc = b200feat_resample(pcm, pcm_dtype, 2, only0, lengths, B, L_in, pcm_stride, orig_freq, new_freq, lowpass_filter_width,
+                                   rolloff, method, beta, out, out_stride, L_out, cuda_stream)) return rc;
+    if (int rc = b200feat_resample(pcm, pcm_dtype, 2, only1, lengths, B, L_in, pcm_stride, orig_freq, new_freq, lowpass_filter_width,
+                                   rolloff, method, beta, scratch, out_stride, L_out, cuda_stream)) return rc;
+    if (B == 0 || L_out == 0) return 0;
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    {
+        ProfScope ps(st, 1);
+        fe_mono_auto_kernel<<<(unsigned)B, 1024, 0, st>>>(out, scratch, out_stride, L_out, decisions, correlations);
+        g_launches++;
+    }
+    FE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------ PCM -> log-mel in one call
+int64_t b200feat_pcm_whisper_workspace_bytes(int32_t B, int64_t L_in, int32_t orig_freq, int32_t new_freq, int32_t padding) {
+    if (B < 0 || L_in < 0 || orig_freq <= 0 || new_freq <= 0 || padding < 0) return -1;
+    const int64_t L = fe_rs_out_len(L_in, orig_freq, new_freq);
+    const int64_t Ls = (L + 3) / 4 * 4;                          // waveform rows 16-byte aligned (the Tensor-Memory kernel's copies)
+    return 256 + (((int64_t)B * 8 + 255) & ~(int64_t)255) + (((int64_t)B * Ls * 4 + 255) & ~(int64_t)255) +
+           b200feat_workspace_bytes(B200FEAT_KIND_WHISPER, B, L + padding);
+}
+
+int b200feat_pcm_whisper_logmel(const void* pcm, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                                const int64_t* lengths, int32_t B, int64_t L_in, int64_t pcm_stride,
+                                int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width, double rolloff,
+                                int32_t method, double beta, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                                void* out, int32_t out_dtype, int64_t out_batch_stride, int64_t T_out,
+                                void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    if (int rc = whisper_ex_dtypes("pcm_whisper_logmel", B200FEAT_F32, out_dtype)) return rc;
+    if (B < 0 || L_in < 0 || orig_freq <= 0 || new_freq <= 0 || padding < 0)
+        return fail(B200FEAT_EINVAL, "pcm_whisper_logmel: negative size, padding or frequency");
+    const int64_t need = b200feat_pcm_whisper_workspace_bytes(B, L_in, orig_freq, new_freq, padding);
+    if (B > 0 && (workspace == nullptr || workspace_bytes < need))
+        return fail(B200FEAT_EWORKSPACE, "pcm_whisper_logmel: workspace too small (%lld bytes, need %lld)", (long long)workspace_bytes, (long long)need);
+    if (B == 0) return 0;
+    const int64_t L = fe_rs_out_len(L_in, orig_freq, new_freq), Ls = (L + 3) / 4 * 4;
+    char* w = static_cast<char*>(workspace);
+    w += (256 - (reinterpret_cast<uintptr_t>(w) & 255)) & 255;
+    int64_t* d_len = reinterpret_cast<int64_t*>(w);
+    w += ((int64_t)B * 8 + 255) & ~(int64_t)255;
+    float* wave = reinterpret_cast<float*>(w);
+    w += ((int64_t)B * Ls * 4 + 255) & ~(int64_t)255;
+    const int64_t ws_left = workspace_bytes - (w - static_cast<char*>(workspace));
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    if (int rc = b200feat_resample(pcm, pcm_dtype, channels, mix_host, lengths, B, L_in, pcm_stride, orig_freq, new_freq,
+                                   lowpass_filter_width, rolloff, method, beta, wave, Ls, L, cuda_stream)) return rc;
+    if (lengths) {
+        int64_t g = orig_freq, h = new_freq;
+        while (h) { const int64_t t = g % h; g = h; h = t; }
+        fe_rs_lengths_kernel<<<(unsigned)((B + 255) / 256), 256, 0, st>>>(lengths, d_len, B, L_in, orig_freq / g, new_freq / g, L);
+        g_launches++;
+    }
+    return whisper_logmel_impl(wave, false, lengths ? d_len : nullptr, B, L, Ls, n_mels, padding, norm_mode, out,
+                               out_dtype == B200FEAT_F16, out_batch_stride, T_out, w, ws_left, cuda_stream);
 }
 
 }  // extern "C"

@@ -92,7 +92,8 @@ int64_t host_chunk_bytes() {
 // launch(d_wave (void*), d_len_or_null, nclips, d_out (void*), d_ws, ws_bytes, stream) -> rc
 template <class Launch>
 int host_pipeline(int kind, const void* wave_host_v, int64_t in_esz, const int64_t* lengths_host, int32_t B, int64_t L, int64_t ws_L,
-                  int64_t out_per_clip, void* out_host_v, int64_t out_esz, int device, bool single_chunk, Launch launch) {
+                  int64_t out_per_clip, void* out_host_v, int64_t out_esz, int device, bool single_chunk, Launch launch,
+                  int64_t extra_ws_per_clip = 0, int64_t extra_ws_fixed = 0) {
     const char* wave_host = static_cast<const char*>(wave_host_v);
     char* out_host = static_cast<char*>(out_host_v);
     if (B < 0 || L < 0) return fail(B200FEAT_EINVAL, "host call: negative B or L");
@@ -113,7 +114,7 @@ int host_pipeline(int kind, const void* wave_host_v, int64_t in_esz, const int64
     const size_t s_wave = round_up((size_t)chunk * in_bytes, 256);
     const size_t s_out = round_up((size_t)chunk * out_bytes, 256);
     const size_t s_len = round_up((size_t)chunk * 8, 256);
-    const size_t s_ws = round_up((size_t)b200feat_workspace_bytes(kind, (int32_t)chunk, ws_L), 256);
+    const size_t s_ws = round_up((size_t)(b200feat_workspace_bytes(kind, (int32_t)chunk, ws_L) + chunk * extra_ws_per_clip + extra_ws_fixed), 256);
     const size_t slot_bytes = s_wave + s_out + s_len + s_ws;
     int rc = arena_reserve(a, slot_bytes * nslot);
     if (rc) { cudaSetDevice(prev); return rc; }
@@ -175,6 +176,33 @@ int b200feat_whisper_logmel_ex_host(const void* wave_host, int32_t wave_dtype, c
     if (int rc = whisper_ex_dtypes("whisper_logmel_ex_host", wave_dtype, out_dtype)) return rc;
     return whisper_logmel_host_impl(wave_host, wave_dtype == B200FEAT_S16, lengths_host, B, L, n_mels, padding, norm_mode,
                                     out_host, out_dtype == B200FEAT_F16, device);
+}
+
+// PCM in -> log-mel out through the chunked pipeline: the H2D copy carries int16 PCM at the capture rate (44.1 kHz stereo:
+// 5.3 KB per audio-ms ... 176 KB per audio-second), the resampled float32 waveform lives only in the arena.
+int b200feat_pcm_whisper_logmel_host(const void* pcm_host, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                                     const int64_t* lengths_host, int32_t B, int64_t L_in, int32_t orig_freq, int32_t new_freq,
+                                     int32_t lowpass_filter_width, double rolloff, int32_t method, double beta,
+                                     int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host, int32_t out_dtype,
+                                     int32_t device) {
+    if (int rc = whisper_ex_dtypes("pcm_whisper_logmel_host", B200FEAT_F32, out_dtype)) return rc;
+    if (pcm_dtype != B200FEAT_F32 && pcm_dtype != B200FEAT_S16)
+        return fail(B200FEAT_EINVAL, "pcm_whisper_logmel_host: pcm_dtype must be B200FEAT_F32 or B200FEAT_S16, got %d", pcm_dtype);
+    if (channels != 1 && channels != 2) return fail(B200FEAT_EINVAL, "pcm_whisper_logmel_host: channels must be 1 or 2, got %d", channels);
+    if (n_mels != 80 && n_mels != 128) return fail(B200FEAT_EINVAL, "pcm_whisper_logmel_host: Unsupported n_mels: %d", n_mels);
+    if (padding < 0 || orig_freq <= 0 || new_freq <= 0) return fail(B200FEAT_EINVAL, "pcm_whisper_logmel_host: negative padding or frequency");
+    const int64_t L = fe_rs_out_len(L_in, orig_freq, new_freq), Ls = (L + 3) / 4 * 4;
+    const int64_t T = (L + padding) / FeW2Cfg::HOP;
+    const int64_t frame_bytes = (int64_t)channels * (pcm_dtype == B200FEAT_S16 ? 2 : 4);
+    return host_pipeline(B200FEAT_KIND_WHISPER, pcm_host, frame_bytes, lengths_host, B, L_in, L + padding, (int64_t)n_mels * T,
+                         out_host, out_dtype == B200FEAT_F16 ? 2 : 4, device, norm_mode == FE_NORM_PER_CALL,
+                         [=](const void* dw, const int64_t* dl, int32_t nc, void* dout, void* ws, int64_t wsb, cudaStream_t st) {
+                             return b200feat_pcm_whisper_logmel(dw, pcm_dtype, channels, mix_host, dl, nc, L_in, L_in * channels,
+                                                                orig_freq, new_freq, lowpass_filter_width, rolloff, method, beta,
+                                                                n_mels, padding, norm_mode, dout, out_dtype, (int64_t)n_mels * T, T,
+                                                                ws, wsb, st);
+                         },
+                         Ls * 4 + 8, 1024);
 }
 
 int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,

@@ -201,6 +201,44 @@ int b200feat_wav2lip_mel(const float* wave, const int64_t* lengths, int32_t B, i
                          int32_t pad_mode, int32_t frame_major, float* out, int64_t out_batch_stride, int64_t T_out,
                          void* cuda_stream);
 
+/* The reference's stereo -> mono rule on the device.  Replaces, for a batch of stereo clips,
+ * /root/reference/Backend/services/audio_processor.py:294-319: Resample both channels, then
+ *     correlation = sum(r0 * r1) / sqrt(sum(r0 ** 2) * sum(r1 ** 2))
+ *     mono = mean(r0, r1) if correlation > 0.5 else mid + 0.3 * side        (mid = (r0 + r1) / 2, side = (r0 - r1) / 2)
+ * per clip, with the correlation taken over the RESAMPLED channels as the reference does.  Two passes of the resampler (one
+ * per channel; `out` receives r0, `scratch` r1) and one CTA per clip for the sums (float64 accumulators, fixed order) and the
+ * mix, which uses the reference's float32 operations in its order.
+ *   pcm      device pointer, (B, L_in, 2) interleaved, B200FEAT_F32 or B200FEAT_S16; lengths as in b200feat_resample
+ *   scratch  device, >= B * out_stride floats;  decisions (int32[B], 1 = mean, 0 = mid/side) and correlations (float[B])
+ *            are optional outputs (NULL to skip).
+ * The reference's filter is lowpass_filter_width 128, rolloff 0.95, B200FEAT_RESAMPLE_KAISER, beta 14.769656459379492. */
+int b200feat_condition_stereo_auto(const void* pcm, int32_t pcm_dtype, const int64_t* lengths, int32_t B, int64_t L_in,
+                                   int64_t pcm_stride, int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width,
+                                   double rolloff, int32_t method, double beta, float* out, int64_t out_stride, int64_t L_out,
+                                   float* scratch, int64_t scratch_floats, int32_t* decisions, float* correlations,
+                                   void* cuda_stream);
+
+/* PCM in, Whisper log-mel out, ONE call ("int16 PCM goes in and features come out"):
+ * b200feat_resample (mono mix + sinc resampler, arguments as there) followed by b200feat_whisper_logmel_ex on the same
+ * stream; the float32 waveform between them lives in `workspace` (b200feat_pcm_whisper_workspace_bytes), never in a
+ * caller tensor.  Replaces load_audio's int16 -> float cast + the resample + log_mel_spectrogram chain in front of
+ * /root/reference/Backend/services/cascaded_backend.py:158 (SURVEY.md cfg1 recipe: Backend/harvard.wav, 44.1 kHz stereo).
+ * lengths: input FRAMES per clip (device int64[B] or NULL).  out / out_dtype / T_out / norm_mode as in
+ * b200feat_whisper_logmel_ex with L = b200feat_resample_out_len(L_in, orig_freq, new_freq). */
+int64_t b200feat_pcm_whisper_workspace_bytes(int32_t B, int64_t L_in, int32_t orig_freq, int32_t new_freq, int32_t padding);
+int b200feat_pcm_whisper_logmel(const void* pcm, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                                const int64_t* lengths, int32_t B, int64_t L_in, int64_t pcm_stride,
+                                int32_t orig_freq, int32_t new_freq, int32_t lowpass_filter_width, double rolloff,
+                                int32_t method, double beta, int32_t n_mels, int32_t padding, int32_t norm_mode,
+                                void* out, int32_t out_dtype, int64_t out_batch_stride, int64_t T_out,
+                                void* workspace, int64_t workspace_bytes, void* cuda_stream);
+/* the same through the chunked host pipeline (pinned or pageable host buffers, blocking): PCM crosses PCIe, not float32 */
+int b200feat_pcm_whisper_logmel_host(const void* pcm_host, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                                     const int64_t* lengths_host, int32_t B, int64_t L_in, int32_t orig_freq, int32_t new_freq,
+                                     int32_t lowpass_filter_width, double rolloff, int32_t method, double beta,
+                                     int32_t n_mels, int32_t padding, int32_t norm_mode, void* out_host, int32_t out_dtype,
+                                     int32_t device);
+
 /* Host-buffer variants (the end-to-end path): wave_host / out_host are HOST pointers (pinned memory
  * gives full PCIe bandwidth); clips are streamed through a library-owned device arena in chunks with
  * H2D copy, kernels and D2H copy overlapped on internal streams.  Blocks until out_host is complete.

@@ -94,3 +94,24 @@ def mono_mix(pcm, weights=None, dtype=torch.float64):
 def condition(pcm, orig_freq, new_freq, weights=None, dtype=torch.float64, **kw):
     """mono mix + resample: the whole front row, ground truth in float64"""
     return resample_restated(mono_mix(pcm, weights, dtype), orig_freq, new_freq, dtype=dtype, **kw)
+
+
+def reference_stereo_to_mono(audio):
+    """/root/reference/Backend/services/audio_processor.py:306-319, the reference's own torch operations in its order,
+    on a (2, L) tensor of RESAMPLED channels.  Returns ((1, L) mono, correlation, took_the_mean_branch)."""
+    correlation = torch.sum(audio[0] * audio[1]) / torch.sqrt(                       # :309-311
+        torch.sum(audio[0] ** 2) * torch.sum(audio[1] ** 2))
+    if correlation > 0.5:                                                            # :313
+        return torch.mean(audio, dim=0, keepdim=True), float(correlation), True     # :314
+    mid = (audio[0] + audio[1]) / 2                                                  # :316
+    side = (audio[0] - audio[1]) / 2                                                 # :317
+    return (mid + 0.3 * side).unsqueeze(0), float(correlation), False               # :318
+
+
+def reference_condition_stereo(audio, orig_freq, new_freq=16000):
+    """audio_processor.py:294-319 on one (2, L) float32 clip: torchaudio.transforms.Resample with the reference's kaiser
+    filter (the real class, float32), then the stereo -> mono rule above."""
+    if orig_freq != new_freq:
+        audio = reference_resample_transform(audio, orig_freq, new_freq, lowpass_filter_width=128, rolloff=0.95,
+                                             resampling_method="sinc_interp_kaiser", beta=14.769656459379492)
+    return reference_stereo_to_mono(audio)
