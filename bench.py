@@ -114,7 +114,7 @@ class Workload:
             self.featurizer = "whisper_log_mel"
             self.traffic_key = None
             self.cpu_desc = "oracle fp32 = torch.stft + dense mel matmul + log10/max-8 (the ops whisper.audio runs)"
-        elif key == "cfg2pcm":
+        elif key in ("cfg2pcm", "cfg2pcmk"):
             # cfg2 as the audio really arrives -- 44.1 kHz stereo int16 PCM -> mono mix +
             # torchaudio-compatible resampling to 16 kHz (b200feat_resample) -> Whisper 128-bin log-mel, device-resident
             self.B, self.L, self.sr, self.n_mels = 1024, 480000, 16000, 128
@@ -129,35 +129,44 @@ class Workload:
             self.traffic_key = "fe_resample_kernel_s16x2_dram_bytes_per_1024_clips"
             self.cpu_desc = ("mean of the channels + torchaudio.functional.resample(44100 -> 16000) + oracle fp32 log-mel "
                              "(torch.stft + dense mel matmul + log10/max-8): the reference's own ops")
+            self.rs_kw = {}
+            if key == "cfg2pcmk":
+                # the filter the reference's AudioProcessor builds (Backend/services/audio_processor.py:296-303): kaiser window,
+                # lowpass_filter_width 128, rolloff 0.95 -- 160 phases x 1185 taps, run as a 3 x TF32 GEMM on the tensor cores
+                self.rs_kw = dict(lowpass_filter_width=128, rolloff=0.95, resampling_method="sinc_interp_kaiser", beta=14.769656459379492)
+                self.kernel = "fe_resample_tc_kernel"
+                self.desc = self.desc.replace("mono + resample", "mono + resample (the reference's kaiser / width-128 filter, tensor cores)")
+                self.featurizer = "condition_pcm(kaiser 128) + whisper_log_mel"
+                self.traffic_key = None
         else:
             raise ValueError(key)
         # algorithmic flops per audio-second (sparse mel, 2.5 N log2 N real-FFT model)
-        self.flops_per_audio_s = {"cfg2": 1.05e6, "cfg2pcm": None, "cfg3": 2.7e6, "cfg4": 1.4e6, "cfg5": 1.04e6, "w2l": 1.6e6}[key]
+        self.flops_per_audio_s = {"cfg2": 1.05e6, "cfg2pcm": None, "cfg2pcmk": None, "cfg3": 2.7e6, "cfg4": 1.4e6, "cfg5": 1.04e6, "w2l": 1.6e6}[key]
         self.audio_s_per_step = self.B * self.L / self.sr              # this rank's share
         self.scaling = "strong" if key == "cfg5" else "weak"
         # whole-job audio per step: fixed total for the sweep, per-GPU work x N otherwise
         self.global_audio_s = (self.total_clips if key == "cfg5" else self.B * world) * self.L / self.sr
         self.e2e_clips = min(self.B, 1024)                              # clips of the shard the host-buffer leg streams per step
-        if key == "cfg2pcm" and world > 1:
+        if key in ("cfg2pcm", "cfg2pcmk") and world > 1:
             self.e2e_clips = 256                                        # 5.3 KB of pinned PCM per audio-ms: keep N ranks' pinned buffers small
         self.out_per_clip = self.out_shape[1] * self.out_shape[2]
         self.bytes_per_clip = 4 * self.L + 4 * self.out_per_clip     # algorithmic: 4*(in) + 4*(out)
-        if key == "cfg2pcm":                                          # the roofline kernel here is the resampler: PCM in + waveform out
+        if key in ("cfg2pcm", "cfg2pcmk"):                            # the roofline kernel here is the resampler: PCM in + waveform out
             self.bytes_per_clip = self.pcm_L * self.pcm_ch * 2 + 4 * self.L
 
     def config(self, n_gpus):
         tot_in, tot_out = self.B * self.L * 4 / 1e9, self.B * self.out_per_clip * 4 / 1e9
         return {"workload": self.desc, "featurizer": self.featurizer, "n_mels": self.n_mels, "clips_per_gpu": self.B,
                 "samples_per_clip": self.L, "pcm": (f"{self.pcm_sr} Hz x {self.pcm_ch} ch int16, {self.pcm_L} frames per clip"
-                                                    if self.key == "cfg2pcm" else None), "global_clips": self.total_clips if self.key == "cfg5" else self.B * n_gpus,
+                                                    if self.key in ("cfg2pcm", "cfg2pcmk") else None), "global_clips": self.total_clips if self.key == "cfg5" else self.B * n_gpus,
                 "norm": "per_clip" if self.key in ("cfg2", "cfg5") else None,
                 "parallelism": f"clip-sharded x{n_gpus}, no collective",
                 "l2_policy": f"inputs ({tot_in:.2f} GB) and outputs ({tot_out:.2f} GB) per step exceed the 126 MB L2; no flush needed"}
 
     def device_step(self, fe, x, out):
-        if self.key == "cfg2pcm":
+        if self.key in ("cfg2pcm", "cfg2pcmk"):
             # ONE library call: mono mix + resampler, then the log-mel kernels; the waveform lives in the call's workspace
-            return lambda: fe.pcm_whisper_log_mel_batch(x, self.pcm_sr, self.sr, n_mels=self.n_mels, norm="per_clip", out=out)
+            return lambda: fe.pcm_whisper_log_mel_batch(x, self.pcm_sr, self.sr, n_mels=self.n_mels, norm="per_clip", out=out, **self.rs_kw)
         if self.key == "cfg2":
             return lambda: fe.whisper_log_mel_batch(x, n_mels=self.n_mels, norm="per_clip", out=out)
         if self.key == "cfg5":
@@ -174,9 +183,9 @@ class Workload:
         return lambda: fe.kaldi_fbank_batch(x, subtract_mean=True, out=out)
 
     def host_step(self, fe, xh, oh, dev):
-        if self.key == "cfg2pcm":
+        if self.key in ("cfg2pcm", "cfg2pcmk"):
             # pinned int16 PCM in -> pinned float32 features out through the library's chunked pipeline (b200feat_pcm_whisper_logmel_host)
-            return lambda: fe.pcm_whisper_log_mel_host(xh, self.pcm_sr, self.sr, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
+            return lambda: fe.pcm_whisper_log_mel_host(xh, self.pcm_sr, self.sr, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev, **self.rs_kw)
         if self.key in ("cfg2", "cfg5"):
             return lambda: fe.whisper_log_mel_host(xh, n_mels=self.n_mels, norm="per_clip", out=oh, device=dev)
         if self.key == "cfg3":
@@ -337,7 +346,7 @@ def measure_light(fe, wl, dev, rank, world, steps, barrier, max_over_ranks):
         x = torch.empty(wl.B, wl.L, dtype=torch.float32, device=dev)
         for lo, hi in manifest.sub_batches(0, wl.B, 256):
             x[lo:hi].normal_(generator=gen).mul_(0.1).clamp_(-1, 1)
-    elif wl.key == "cfg2pcm":
+    elif wl.key in ("cfg2pcm", "cfg2pcmk"):
         x = torch.randint(-20000, 20000, (wl.B, wl.pcm_L, wl.pcm_ch), generator=gen, dtype=torch.int16, device=dev)
     else:
         x = (0.1 * torch.randn(wl.B, wl.L, generator=gen, device=dev)).clamp_(-1, 1)
@@ -366,7 +375,7 @@ def measure_light(fe, wl, dev, rank, world, steps, barrier, max_over_ranks):
     res = {"workload": wl.desc, "scaling": wl.scaling, "ms_per_step": ms_step, "value": wl.global_audio_s / (ms_step * 1e-3), "unit": UNIT,
            "steps": steps, "kernel": wl.kernel, "kernel_ms_per_step": k_ms_step, "epilogue_ms_per_step": prof["epilogue_ms"] / steps,
            "launches_per_step": (prof["feature_launches"] + prof["epilogue_launches"]) // steps}
-    if wl.key == "cfg2pcm":
+    if wl.key in ("cfg2pcm", "cfg2pcmk"):
         chain_bytes = wl.B * (wl.pcm_L * wl.pcm_ch * 2 + 4 * wl.out_per_clip)
         res["roofline"] = {"bound": "hbm", "note": "whole chain (mono mix + resampler, then log-mel) against the bytes a fully fused chain would "
                                                    "move: int16 PCM in + float32 features out; the float32 waveform in between is extra traffic",
@@ -675,7 +684,7 @@ def run_ours(args, rank, world, local_rank):
         del xh, oh
         torch.cuda.empty_cache()
         others = {}
-        for key in ("cfg3", "cfg4", "cfg2pcm", "w2l", "cfg5"):
+        for key in ("cfg3", "cfg4", "cfg2pcm", "cfg2pcmk", "w2l", "cfg5"):
             wl = Workload(key, rank, world)
             others[key] = measure_light(fe, wl, dev, rank, world, 3 if key == "cfg5" else min(args.steps, 5), barrier, max_over_ranks)
 

@@ -21,6 +21,7 @@
 #include "fe_whisper3.cuh"
 #include "fe_kaldi.cuh"
 #include "fe_kaldi3.cuh"
+#include "fe_resample_tc.cuh"
 #include "fe_cosy.cuh"
 #include "fe_resample.cuh"
 #define FE_RS_HAVE_PARAMS
@@ -1035,6 +1036,239 @@ __global__ void __launch_bounds__(FeCCfg::NT, 1) fe_cosy_kernel(const FeCosyPara
 __global__ void __launch_bounds__(FeLCfg::NT, 2) fe_wav2lip_kernel(const FeCosyParams p) { fe_stft3_body<FeLCfg, 2>(p); }
 
 // =====================================================================================================
+// resampler, long filters: tensor-core GEMM (fe_resample_tc.cuh)
+// =====================================================================================================
+// interleaved PCM -> mono float32 rows (the A-operand producers read 16-byte aligned float32 rows)
+template <bool IN16, int CH>
+__global__ void __launch_bounds__(256) fe_pcm_mono_kernel(const void* __restrict__ pcm, int64_t pcm_stride, float w0, float w1,
+                                                          float* __restrict__ out, int64_t out_stride, int64_t L) {
+    const int b = blockIdx.y;
+    float* __restrict__ o = out + (int64_t)b * out_stride;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < L; i += (int64_t)gridDim.x * blockDim.x) {
+        float v;
+        if (IN16) {
+            const short* __restrict__ s = static_cast<const short*>(pcm) + (int64_t)b * pcm_stride + i * CH;
+            v = CH == 2 ? fmaf(w1, (float)s[1] * (1.0f / 32768.0f), w0 * ((float)s[0] * (1.0f / 32768.0f))) : w0 * ((float)s[0] * (1.0f / 32768.0f));
+        } else {
+            const float* __restrict__ s = static_cast<const float*>(pcm) + (int64_t)b * pcm_stride + i * CH;
+            v = CH == 2 ? fmaf(w1, s[1], w0 * s[0]) : w0 * s[0];
+        }
+        o[i] = v;
+    }
+}
+
+// bounded spin on the barrier's phase WITHOUT a suspend-time hint: the roles of the GEMM kernel hand stages to each other
+// every few hundred cycles, a parked warp wakes too late for that
+static __device__ __forceinline__ void fe_mbar_wait_spin(unsigned addr, unsigned parity) {
+    unsigned ok = 0;
+#pragma unroll 1
+    for (int spin = 0; spin < (1 << 26); ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.b32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (ok) return;
+    }
+    __trap();
+}
+
+// S16X2: the rows are interleaved int16 stereo PCM; a 4-byte frame takes the place of a float32 sample in the producers'
+// loads and is mixed to mono there (w0 * l / 32768 + w1 * r / 32768), so the usual capture format needs no pre-pass
+template <bool S16X2>
+__global__ void __launch_bounds__(FeRsTcCfg::NTHREADS, 1) fe_resample_tc_kernel(const FeRsTcParams p) {
+    typedef FeRsTcCfg C;
+    extern __shared__ __align__(1024) unsigned char tc_smem[];
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const int N = p.newf;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(tc_smem);
+    const uint32_t stage_bytes = (uint32_t)(2 * N * C::KC * 4);            // H(hi, lo) of one chunk
+    const uint32_t bar0 = sbase + (uint32_t)C::NST * stage_bytes;          // full[NST], empty[NST], accf[2], acce[2], tmem slot
+    const uint32_t full0 = bar0, empty0 = bar0 + 8u * C::NST, accf0 = bar0 + 16u * C::NST, acce0 = accf0 + 16u;
+    uint32_t* const tm_slot = reinterpret_cast<uint32_t*>(tc_smem + (size_t)C::NST * stage_bytes + 16 * C::NST + 32);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < C::NST; ++s) {
+            fe_mbar_init(full0 + 8u * s, 5);        // four producer warps + the loader's arrive.expect_tx
+            fe_mbar_init(empty0 + 8u * s, 1);       // tcgen05.commit of the chunk's MMAs
+        }
+        for (int a = 0; a < 2; ++a) {
+            fe_mbar_init(accf0 + 8u * a, 1);        // tcgen05.commit of the tile's last MMA
+            fe_mbar_init(acce0 + 8u * a, 4);        // four epilogue warps
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == C::MMA_WARP) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(tm_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fe_tc_fence_before();
+    __syncthreads();
+    fe_tc_fence_after();
+    const uint32_t tmem = *tm_slot;
+    const int first = blockIdx.x, step = gridDim.x;
+
+    if (warp < 4 * C::PGROUPS) {
+        // ------------------------------------------------------------------ producers: one row of the A operand per thread,
+        // written straight into Tensor Memory (lane = row, 32 columns of hi and 32 of lo per stage).  PGROUPS groups of four
+        // warps take the chunks in turn: a group's global loads (an L2 / HBM round trip of 1.5-3 k cycles) overlap the other
+        // groups' conversion and stores (profiles/r02_resample_tc.txt).
+        const int group = warp >> 2, r = threadIdx.x & 127;
+        const uint32_t lane_base = tmem + ((uint32_t)(32 * (warp & 3)) << 16);
+        uint32_t it = 0, s = 0, ph = 0;
+        for (int tile = first; tile < p.total_tiles; tile += step) {
+            const int b = tile / p.tiles_per_clip, tq = tile - b * p.tiles_per_clip;
+            const int64_t len = fe_clip_len(p.lengths, b, p.L_in);
+            const float* __restrict__ x = p.x + (int64_t)b * p.x_stride;
+            const int64_t g0 = ((int64_t)tq * C::M + r) * p.orig - p.width;
+#pragma unroll 1
+            for (int c = 0; c < p.nch; ++c, ++it, s = (s + 1 == C::NST ? 0 : s + 1), ph ^= (s == 0 ? 1u : 0u)) {
+                if (it % (uint32_t)C::PGROUPS != (uint32_t)group) continue;
+                const int64_t g = g0 + (int64_t)c * C::KC;
+                float e[C::KC];      // 4-byte elements: float32 samples, or (S16X2) int16 stereo frames as raw bits
+                if (g >= 0 && g + C::KC + 4 <= len) {
+                    // 36 elements from the 16-byte boundary below g, shifted by g & 3 in registers
+                    const float4* __restrict__ q4 = reinterpret_cast<const float4*>(x + (g & ~(int64_t)3));
+                    float v[C::KC + 4];
+#pragma unroll
+                    for (int j = 0; j < C::KC / 4 + 1; ++j) {
+                        const float4 t = q4[j];
+                        v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+                    }
+                    const int sh = (int)(g & 3);
+#pragma unroll
+                    for (int j = 0; j < C::KC; ++j) {
+                        const float a01 = (sh & 1) ? v[j + 1] : v[j], a23 = (sh & 1) ? v[j + 3] : v[j + 2];
+                        e[j] = (sh & 2) ? a23 : a01;
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < C::KC; ++j) {
+                        const int64_t i = g + j;
+                        e[j] = (i >= 0 && i < len) ? x[i] : 0.0f;      // bits 0 = a frame of two zero samples
+                    }
+                }
+                if (S16X2) {
+#pragma unroll
+                    for (int j = 0; j < C::KC; ++j) {
+                        const uint32_t f = __float_as_uint(e[j]);
+                        const float l = (float)(short)(f & 0xffffu) * (1.0f / 32768.0f), rr = (float)(short)(f >> 16) * (1.0f / 32768.0f);
+                        e[j] = fmaf(p.w1, rr, p.w0 * l);
+                    }
+                }
+                float hi[C::KC], lo[C::KC];
+#pragma unroll
+                for (int j = 0; j < C::KC; ++j) { hi[j] = fe_tf32_rna(e[j]); lo[j] = fe_tf32_rna(e[j] - hi[j]); }
+                fe_mbar_wait_spin(empty0 + 8u * s, ph ^ 1u);
+                fe_tc_fence_after();
+                const uint32_t t_hi = lane_base + C::a_hi_col(s), t_lo = lane_base + C::a_lo_col(s);
+#pragma unroll
+                for (int j = 0; j < C::KC; j += 8) {
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                 ::"r"(t_hi + j), "f"(hi[j]), "f"(hi[j + 1]), "f"(hi[j + 2]), "f"(hi[j + 3]), "f"(hi[j + 4]), "f"(hi[j + 5]),
+                                   "f"(hi[j + 6]), "f"(hi[j + 7]) : "memory");
+                    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                                 ::"r"(t_lo + j), "f"(lo[j]), "f"(lo[j + 1]), "f"(lo[j + 2]), "f"(lo[j + 3]), "f"(lo[j + 4]), "f"(lo[j + 5]),
+                                   "f"(lo[j + 6]), "f"(lo[j + 7]) : "memory");
+                }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                fe_tc_fence_before();
+                fe_warp_arrive(full0 + 8u * s, lane);
+            }
+        }
+    } else if (warp < 4 * C::PGROUPS + 4) {
+        // ------------------------------------------------------------------ epilogue: one output row (block q) per lane
+        const int w = warp - 4 * C::PGROUPS, r = 32 * w + lane;
+        uint32_t i = 0;
+        for (int tile = first; tile < p.total_tiles; tile += step, ++i) {
+            const uint32_t a = i & 1u, aph = (i >> 1) & 1u;
+            const int b = tile / p.tiles_per_clip, tq = tile - b * p.tiles_per_clip;
+            const int64_t len = fe_clip_len(p.lengths, b, p.L_in);
+            int64_t olen = (len * p.newf + p.orig - 1) / p.orig;               // samples this clip yields; zeros behind
+            if (olen > p.L_out) olen = p.L_out;
+            const int64_t o0 = ((int64_t)tq * C::M + r) * N;                   // first output sample of this lane's row
+            float* __restrict__ orow = p.out + (int64_t)b * p.out_stride + o0;
+            fe_mbar_wait_bounded(accf0 + 8u * a, aph);                        // a whole tile away: park the warp
+            fe_tc_fence_after();
+            const uint32_t taddr = tmem + ((uint32_t)(32 * w) << 16) + a * (uint32_t)C::ACC_STRIDE;
+#pragma unroll 1
+            for (int c0 = 0; c0 < N; c0 += 16) {
+                uint32_t v[16];
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                             : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                               "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                             : "r"(taddr + (uint32_t)c0) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const int64_t i0 = o0 + c0;
+                if (p.out_vec && i0 + 16 <= olen) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        *reinterpret_cast<float4*>(orow + c0 + 4 * j) = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                                                                    __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (i0 + j < p.L_out) orow[c0 + j] = i0 + j < olen ? __uint_as_float(v[j]) : 0.0f;
+                }
+            }
+            fe_tc_fence_before();
+            fe_warp_arrive(acce0 + 8u * a, lane);
+        }
+    } else if (warp == C::MMA_WARP) {
+        // ------------------------------------------------------------------ MMA issuer: A from Tensor Memory, H from shared memory
+        if (lane == 0) {
+            const uint32_t idesc = fe_umma_idesc_tf32(C::M, N);
+            const uint32_t lo_off = (uint32_t)(N * C::KC * 4);
+            uint32_t s = 0, ph = 0, i = 0;
+            for (int tile = first; tile < p.total_tiles; tile += step, ++i) {
+                const uint32_t a = i & 1u, aph = (i >> 1) & 1u;
+                fe_mbar_wait_spin(acce0 + 8u * a, aph ^ 1u);                   // the epilogue has drained this accumulator
+                fe_tc_fence_after();
+                const uint32_t d = tmem + a * (uint32_t)C::ACC_STRIDE;
+#pragma unroll 1
+                for (int c = 0; c < p.nch; ++c) {
+                    fe_mbar_wait_spin(full0 + 8u * s, ph);
+                    fe_tc_fence_after();
+                    const uint32_t t_hi = tmem + C::a_hi_col(s), t_lo = tmem + C::a_lo_col(s);
+                    const uint64_t dbh = fe_umma_desc(sbase + s * stage_bytes), dbl = fe_umma_desc(sbase + s * stage_bytes + lo_off);
+#pragma unroll
+                    for (int ks = 0; ks < C::KC / 8; ++ks) {
+                        const uint64_t ko = (uint64_t)(ks * 2 * C::LBO >> 4);  // the descriptor's address field counts 16-byte units
+                        fe_umma_tf32_ts(d, t_hi + 8 * ks, dbh + ko, idesc, (c | ks) != 0 ? 1u : 0u);
+                        fe_umma_tf32_ts(d, t_hi + 8 * ks, dbl + ko, idesc, 1u);
+                        fe_umma_tf32_ts(d, t_lo + 8 * ks, dbh + ko, idesc, 1u);
+                    }
+                    fe_umma_commit(empty0 + 8u * s);       // arrives when the MMAs issued so far have read this stage
+                    if (++s == C::NST) { s = 0; ph ^= 1u; }
+                }
+                fe_umma_commit(accf0 + 8u * a);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ------------------------------------------------------------------ H loader
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (int tile = first; tile < p.total_tiles; tile += step) {
+#pragma unroll 1
+                for (int c = 0; c < p.nch; ++c) {
+                    fe_mbar_wait_spin(empty0 + 8u * s, ph ^ 1u);
+                    fe_mbar_expect_tx(full0 + 8u * s, stage_bytes);
+                    const float* src = p.hpack + (size_t)c * (size_t)(2 * N * C::KC);
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                 ::"r"(sbase + s * stage_bytes), "l"(src), "r"(stage_bytes), "r"(full0 + 8u * s) : "memory");
+                    if (++s == C::NST) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+        __syncwarp();
+    }
+    fe_tc_fence_before();
+    __syncthreads();
+    if (warp == C::MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+}
+
+// =====================================================================================================
 // waveform conditioning: the reference's stereo -> mono rule, and the glue of the one-call PCM -> log-mel path
 // =====================================================================================================
 // /root/reference/Backend/services/audio_processor.py:307-319, applied to the RESAMPLED channels r0 / r1 of a clip:
@@ -1772,7 +2006,45 @@ struct RsDevicePlan {
     FeRsPlan plan;
     float4* taps = nullptr;
     int32_t* kstart = nullptr;
+    // tensor-core path (fe_resample_tc.cuh): the dense tap matrix, split hi / lo, in the B-operand layout
+    float* hpack = nullptr;
+    int nch = 0;
 };
+
+// long filters with a phase count the MMA takes as N: the polyphase sum runs as a 3 x TF32 GEMM
+static bool rs_tc_applicable(const FeRsPlan& pl, int lpfw, double rolloff) {
+    const char* e = getenv("B200FEAT_RESAMPLE_TC");
+    if (e && atoi(e) == 0) return false;
+    // The GEMM is dense over K = 2 * width + orig taps per phase; the window's support is 2 * lpfw * orig / base of them.
+    // Short filters (torchaudio's default: 33 live taps of 475 at 44.1 -> 16 kHz) stay on the CUDA-core kernel, which only
+    // touches the live taps and runs near the HBM roofline there.
+    const int K = 2 * pl.width + pl.orig;
+    const double live = 2.0 * lpfw * pl.orig / (std::min(pl.orig, pl.newf) * rolloff);
+    return pl.newf % 16 == 0 && pl.newf >= 16 && pl.newf <= FeRsTcCfg::MAX_N && live >= 256.0 && live >= 0.4 * K;
+}
+static float tf32_rna_host(float v) {            // cvt.rna.tf32.f32: nearest, ties away from zero
+    uint32_t u;
+    memcpy(&u, &v, 4);
+    u = (u + 0x1000u) & 0xffffe000u;
+    memcpy(&v, &u, 4);
+    return v;
+}
+static std::vector<float> rs_tc_pack(const FeRsPlan& pl, int lpfw, double rolloff, int method, double beta, int* nch_out) {
+    typedef FeRsTcCfg C;
+    const int N = pl.newf, K = 2 * pl.width + pl.orig, nch = (K + C::KC - 1) / C::KC;
+    std::vector<float> h((size_t)nch * 2 * N * C::KC, 0.0f);
+    for (int p = 0; p < N; ++p)
+        for (int k = 0; k < K; ++k) {
+            const float v = (float)fe_rs_tap(pl.orig, pl.newf, pl.width, lpfw, rolloff, method, beta, p, k);
+            const float hi = tf32_rna_host(v), lo = tf32_rna_host(v - hi);
+            const int c = k / C::KC, kk = k % C::KC;
+            const size_t off = (size_t)(p / 8) * (C::SBO / 4) + (size_t)(kk / 4) * (C::LBO / 4) + (p % 8) * 4 + (kk % 4);
+            h[((size_t)c * 2 + 0) * N * C::KC + off] = hi;
+            h[((size_t)c * 2 + 1) * N * C::KC + off] = lo;
+        }
+    *nch_out = nch;
+    return h;
+}
 typedef std::tuple<int, int, int, int, double, int, double> RsKey;
 std::mutex g_rs_mu;
 std::map<RsKey, RsDevicePlan*> g_rs_plans;
@@ -1818,9 +2090,19 @@ int rs_get_plan(int orig_freq, int new_freq, int lpfw, double rolloff, int metho
     if (e == cudaSuccess) e = cudaMalloc(&dp->kstart, dp->plan.kstart.size() * sizeof(int32_t));
     if (e == cudaSuccess) e = cudaMemcpy(dp->taps, dp->plan.taps.data(), dp->plan.taps.size() * sizeof(float), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(dp->kstart, dp->plan.kstart.data(), dp->plan.kstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && rs_tc_applicable(dp->plan, lpfw, rolloff)) {
+        const std::vector<float> hp = rs_tc_pack(dp->plan, lpfw, rolloff, method, beta, &dp->nch);
+        e = cudaMalloc(&dp->hpack, hp.size() * sizeof(float));
+        if (e == cudaSuccess) e = cudaMemcpy(dp->hpack, hp.data(), hp.size() * sizeof(float), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(fe_resample_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeRsTcCfg::smem_bytes(FeRsTcCfg::MAX_N));
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(fe_resample_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeRsTcCfg::smem_bytes(FeRsTcCfg::MAX_N));
+    }
     if (e != cudaSuccess) {
         if (dp->taps) cudaFree(dp->taps);
         if (dp->kstart) cudaFree(dp->kstart);
+        if (dp->hpack) cudaFree(dp->hpack);
         delete dp;
         return fail(B200FEAT_ECUDA, "resample: uploading the tap table failed: %s", cudaGetErrorString(e));
     }
@@ -1860,6 +2142,67 @@ int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, cons
     RsDevicePlan* dp = nullptr;
     if (int rc = rs_get_plan(orig_freq, new_freq, lowpass_filter_width, rolloff, method, beta, &dp)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    if (dp->hpack != nullptr && B <= 65535) {
+        // ---- tensor-core path: (mono mix to aligned float32 rows, unless the input is that already) + the GEMM kernel
+        typedef FeRsTcCfg C;
+        const bool in16 = pcm_dtype == B200FEAT_S16;
+        const float w0 = mix_host ? mix_host[0] : 1.0f / channels, w1 = channels == 2 ? (mix_host ? mix_host[1] : 0.5f) : 0.0f;
+        const bool direct = channels == 1 && !in16 && w0 == 1.0f && aligned16(pcm) && pcm_stride % 4 == 0;
+        const bool s16x2 = channels == 2 && in16 && aligned16(pcm) && pcm_stride % 8 == 0;     // frames read as 4-byte elements
+        float* mono = nullptr;
+        const int64_t Ls = (L_in + 3) / 4 * 4;
+        if (!direct && !s16x2) {
+            {   // stream-ordered scratch for the mono rows: keep the pool's memory across calls (the default releases it at
+                // every synchronisation and the next call maps it again -- milliseconds for a 5 GB batch)
+                static std::atomic<int> pool_set[64];
+                int dev0 = 0;
+                FE_CUDA(cudaGetDevice(&dev0));
+                if (dev0 >= 0 && dev0 < 64 && pool_set[dev0].exchange(1) == 0) {
+                    cudaMemPool_t pool;
+                    if (cudaDeviceGetDefaultMemPool(&pool, dev0) == cudaSuccess) {
+                        uint64_t keep = ~(uint64_t)0;
+                        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+                    }
+                }
+            }
+            FE_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&mono), (size_t)B * Ls * sizeof(float), st));
+            int64_t gx = (L_in + 255) / 256;
+            if (gx > 2048) gx = 2048;
+            const dim3 grid((unsigned)gx, (unsigned)B);
+            ProfScope ps(st, 1);
+            if (in16 && channels == 2) fe_pcm_mono_kernel<true, 2><<<grid, 256, 0, st>>>(pcm, pcm_stride, w0, w1, mono, Ls, L_in);
+            else if (in16) fe_pcm_mono_kernel<true, 1><<<grid, 256, 0, st>>>(pcm, pcm_stride, w0, w1, mono, Ls, L_in);
+            else if (channels == 2) fe_pcm_mono_kernel<false, 2><<<grid, 256, 0, st>>>(pcm, pcm_stride, w0, w1, mono, Ls, L_in);
+            else fe_pcm_mono_kernel<false, 1><<<grid, 256, 0, st>>>(pcm, pcm_stride, w0, w1, mono, Ls, L_in);
+            g_launches++;
+        }
+        FeRsTcParams q;
+        memset(&q, 0, sizeof(q));
+        q.x = (direct || s16x2) ? static_cast<const float*>(pcm) : mono;
+        q.x_stride = direct ? pcm_stride : (s16x2 ? pcm_stride / 2 : Ls);
+        q.w0 = w0; q.w1 = w1;
+        q.lengths = lengths; q.L_in = L_in; q.out = out; q.out_stride = out_stride; q.L_out = L_out;
+        q.hpack = dp->hpack; q.B = B; q.orig = dp->plan.orig; q.newf = dp->plan.newf; q.width = dp->plan.width;
+        q.nch = dp->nch;
+        const int64_t nblocks = (L_out + q.newf - 1) / q.newf;
+        q.tiles_per_clip = (int32_t)((nblocks + C::M - 1) / C::M);
+        const int64_t total = (int64_t)B * q.tiles_per_clip;
+        if (total > 0x7fffffff) return fail(B200FEAT_EINVAL, "resample: batch too large");
+        q.total_tiles = (int32_t)total;
+        q.out_vec = (aligned16(out) && out_stride % 4 == 0) ? 1 : 0;
+        int dev = 0;
+        FE_CUDA(cudaGetDevice(&dev));
+        const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
+        {
+            ProfScope ps(st, 0);
+            if (s16x2) fe_resample_tc_kernel<true><<<(unsigned)(total < sms ? total : sms), C::NTHREADS, C::smem_bytes(q.newf), st>>>(q);
+            else fe_resample_tc_kernel<false><<<(unsigned)(total < sms ? total : sms), C::NTHREADS, C::smem_bytes(q.newf), st>>>(q);
+            g_launches++;
+        }
+        if (mono) FE_CUDA(cudaFreeAsync(mono, st));
+        FE_CUDA(cudaGetLastError());
+        return 0;
+    }
     FeResampleParams p;
     memset(&p, 0, sizeof(p));
     fe_rs_fill_params(p, dp->plan, L_in, L_out, channels, pcm_dtype == B200FEAT_S16, mix_host);

@@ -310,3 +310,51 @@ def test_gpu_install_patches_resample(fe):
     finally:
         fe.uninstall()
     assert torchaudio.functional.resample is orig
+
+
+@pytest.mark.gpu
+def test_gpu_reference_kaiser_filter_on_tensor_cores_full_size():
+    """The filter the reference deploys (audio_processor.py:296-303: kaiser, width 128, rolloff 0.95; 44.1 -> 16 kHz = 160
+    phases x 1185 taps) runs as a 3 x TF32 GEMM on the tensor cores (fe_resample_tc.cuh).  At BASELINE configs[1]'s size
+    (1024 x 30 s): two clips against the float64 restatement within 4e-6, determinism, batch independence, ragged ends,
+    int16 stereo input through the mono pre-pass; and the launch really is the tensor-core kernel."""
+    import expressive_speech_translation_b200 as fe
+    kw = dict(fe.REFERENCE_RESAMPLER)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    B, L = 1024, 1323000
+    x = torch.empty(B, L, device="cuda")
+    for lo in range(0, B, 128):
+        x[lo:lo + 128].normal_(generator=g).mul_(0.25).clamp_(-1, 1)
+    n0 = fe.launch_count()
+    out = fe.condition_pcm(x, 44100, 16000, **kw)
+    assert fe.launch_count() - n0 == 1                       # float32 mono, aligned rows: the GEMM kernel alone
+    assert out.shape == (B, 480000) and bool(torch.isfinite(out).all())
+    assert torch.equal(out, fe.condition_pcm(x, 44100, 16000, **kw))
+    assert torch.equal(out[517:518], fe.condition_pcm(x[517:518], 44100, 16000, **kw))
+    for b in (0, 1023):
+        ref = orc.resample_restated(x[b].cpu(), 44100, 16000, dtype=torch.float64, **kw)
+        assert (out[b].cpu().double() - ref).abs().max() <= 4e-6, b
+    del out
+    lens = torch.full((B,), L, dtype=torch.int64)
+    lens[3], lens[900] = 441 * 128 * 7 + 13, 5000
+    rag = fe.condition_pcm(x, 44100, 16000, lengths=lens, **kw)
+    for b in (3, 900):
+        n = int(lens[b])
+        ref = orc.resample_restated(x[b, :n].cpu(), 44100, 16000, dtype=torch.float64, **kw)
+        m = ref.shape[0]
+        assert (rag[b, :m].cpu().double() - ref).abs().max() <= 4e-6
+        assert not rag[b, m:].any()
+    del rag, x
+    pcm = torch.randint(-20000, 20000, (64, 441 * 300 + 7, 2), generator=torch.Generator().manual_seed(2), dtype=torch.int16)
+    got = fe.condition_pcm(pcm.cuda(), 44100, 16000, mix=(0.65, 0.35), **kw).cpu()
+    ref = orc.condition(pcm[:2], 44100, 16000, weights=(0.65, 0.35), **kw)
+    assert (got[:2].double() - ref).abs().max() <= 4e-6
+    # rows of a multiple of 4 frames: the kernel reads the int16 stereo frames itself (no mono pre-pass: ONE launch), ragged too
+    pcm4 = pcm[:, :441 * 300 + 4].contiguous()
+    n0 = fe.launch_count()
+    got4 = fe.condition_pcm(pcm4.cuda(), 44100, 16000, lengths=[pcm4.shape[1]] * 63 + [7001], **kw).cpu()
+    assert fe.launch_count() - n0 == 1
+    ref = orc.condition(pcm4[:1], 44100, 16000, **kw)
+    assert (got4[:1].double() - ref).abs().max() <= 4e-6
+    ref = orc.condition(pcm4[63:, :7001], 44100, 16000, **kw)
+    assert (got4[63:, :ref.shape[1]].double() - ref).abs().max() <= 4e-6 and not got4[63, ref.shape[1]:].any()
