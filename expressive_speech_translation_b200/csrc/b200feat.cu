@@ -1020,6 +1020,7 @@ template <class C, int MINB>
 static __device__ __forceinline__ void fe_stft3_body(const FeCosyParams& p) {
     extern __shared__ __align__(16) float sm[];
     const int tid = threadIdx.x, cta = blockIdx.x;
+    fe_c_copy_tables<C>(sm, tid);
     fe_c_phase_load<C>(p, sm, tid, cta);
     __syncthreads();
     fe_c_phase_a<C>(p, sm, tid, cta);

@@ -42,7 +42,16 @@ struct FeS3Cfg : P {
     static constexpr int R0 = (SW > P::NBIN * PS) ? SW : P::NBIN * PS;
     static constexpr int OFF_A = (R0 + 3) / 4 * 4;       // A holds float2: keep it 16-byte aligned
     static_assert(OFF_A % 4 == 0, "A must be aligned for float2 access");
+    // A/B build only (-DFE_S3_SMEM_TABLES): window and stage-A / stage-B twiddles copied to shared memory by the CTA.  Measured
+    // 1.006 against 0.898 ms for N = 1920 and 0.428 against 0.440 ms for N = 800 (profiles/r02_stft3_ncu_summary.txt): the
+    // constant bank stays.
+    static constexpr int OFF_TAB = OFF_A + FT * FS * 2;
+    static constexpr int TAB_WIN = 0, TAB_TWA = P::N, TAB_TWB = P::N + M * 18, TAB_FLOATS = P::N + M * 18 + P::R3 * 2 * P::R2;
+#ifdef FE_S3_SMEM_TABLES
+    static constexpr int SMEM_FLOATS = OFF_TAB + TAB_FLOATS;
+#else
     static constexpr int SMEM_FLOATS = OFF_A + FT * FS * 2;
+#endif
     static constexpr int SMEM_BYTES = SMEM_FLOATS * 4;
     static constexpr int TASKS_A = 16 * ((M + 31) / 32); // warp-tasks: slots (m, m + 16), m = 32*j + i
     static constexpr int TASKS_B = (NK1 * P::R3 + 1) / 2;
@@ -86,6 +95,27 @@ struct FeW2LTraits {
 };
 typedef FeS3Cfg<FeCosyTraits> FeCCfg;
 typedef FeS3Cfg<FeW2LTraits> FeLCfg;
+
+#ifdef FE_S3_SMEM_TABLES
+#define FE_S3_WIN(C, sm) ((sm) + C::OFF_TAB + C::TAB_WIN)
+#define FE_S3_TWA(C, sm) ((sm) + C::OFF_TAB + C::TAB_TWA)
+#define FE_S3_TWB(C, sm) ((sm) + C::OFF_TAB + C::TAB_TWB)
+#else
+#define FE_S3_WIN(C, sm) C::win()
+#define FE_S3_TWA(C, sm) C::tw_a()
+#define FE_S3_TWB(C, sm) C::tw_b()
+#endif
+template <class C>
+FE_HD FE_INLINE void fe_c_copy_tables(float* sm, int tid) {
+#ifdef FE_S3_SMEM_TABLES
+    float* t = sm + C::OFF_TAB;
+    for (int i = tid; i < C::N; i += C::NT) t[C::TAB_WIN + i] = C::win()[i];
+    for (int i = tid; i < C::M * 18; i += C::NT) t[C::TAB_TWA + i] = C::tw_a()[i];
+    for (int i = tid; i < C::R3 * 2 * C::R2; i += C::NT) t[C::TAB_TWB + i] = C::tw_b()[i];
+#else
+    (void)sm; (void)tid;
+#endif
+}
 
 struct FeCTile {
     int b, t0, T;
@@ -152,12 +182,12 @@ FE_HD FE_INLINE void fe_c_stage_a(float* sm, int f, int m) {
 #pragma unroll
     for (int n1 = 0; n1 < C::R1; ++n1) {
         // sample n = M*n1 + m; (M*n1 + m) / HOP == n1 / 4 for every m < M (HOP == 4 M)
-        x[n1] = s[C::M * n1 + n1 / (C::HOP / C::M)] * C::win()[C::M * n1 + m];
+        x[n1] = s[C::M * n1 + n1 / (C::HOP / C::M)] * FE_S3_WIN(C, sm)[C::M * n1 + m];
     }
     float yr[9], yi[9];
     fe_rdft16_h9(x, yr, yi);
     float2* __restrict__ a = reinterpret_cast<float2*>(sm + C::OFF_A) + C::FS * f + m;
-    const float* __restrict__ tw = C::tw_a() + m * 18;
+    const float* __restrict__ tw = FE_S3_TWA(C, sm) + m * 18;
     a[0] = make_float2(yr[0], 0.0f);
 #pragma unroll
     for (int k1 = 1; k1 < 8; ++k1) {
@@ -188,7 +218,7 @@ FE_HD FE_INLINE void fe_c_stage_b(float* sm, int f, int k1, int n3) {
         xr[n2] = v.x; xi[n2] = v.y;
     }
     C::dft_b(xr, xi, yr, yi);
-    const float* __restrict__ tw = C::tw_b() + n3 * (2 * C::R2);
+    const float* __restrict__ tw = FE_S3_TWB(C, sm) + n3 * (2 * C::R2);
     a[0] = make_float2(yr[0], yi[0]);
 #pragma unroll
     for (int k2 = 1; k2 < C::R2; ++k2) {
