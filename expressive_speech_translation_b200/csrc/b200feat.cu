@@ -2009,19 +2009,24 @@ struct RsDevicePlan {
     int32_t* kstart = nullptr;
     // tensor-core path (fe_resample_tc.cuh): the dense tap matrix, split hi / lo, in the B-operand layout
     float* hpack = nullptr;
-    int nch = 0;
+    int nch = 0, tc_m = 0;      // tc_m blocks of the plan form one row of the GEMM
 };
 
-// long filters with a phase count the MMA takes as N: the polyphase sum runs as a 3 x TF32 GEMM
-static bool rs_tc_applicable(const FeRsPlan& pl, int lpfw, double rolloff) {
+// Long filters run as a 3 x TF32 GEMM (fe_resample_tc.cuh).  m consecutive blocks are taken as one (orig * m input samples ->
+// new * m outputs, the "phases" of the GEMM), m the largest value with N = new * m a multiple of 16 and <= 160: 44.1 -> 16 kHz
+// is 441 -> 160 with m = 1, 48 -> 16 kHz is 3 -> 1 with m = 160 (480 -> 160).  Returns m, or 0 when the path does not apply.
+static int rs_tc_blocks(const FeRsPlan& pl, int lpfw, double rolloff) {
     const char* e = getenv("B200FEAT_RESAMPLE_TC");
-    if (e && atoi(e) == 0) return false;
-    // The GEMM is dense over K = 2 * width + orig taps per phase; the window's support is 2 * lpfw * orig / base of them.
+    if (e && atoi(e) == 0) return 0;
+    int m = FeRsTcCfg::MAX_N / pl.newf;
+    while (m > 0 && (pl.newf * m) % 16 != 0) --m;
+    if (m <= 0) return 0;
+    // The GEMM is dense over K = 2 * width + orig * m taps per output; the window's support is 2 * lpfw * orig / base of them.
     // Short filters (torchaudio's default: 33 live taps of 475 at 44.1 -> 16 kHz) stay on the CUDA-core kernel, which only
     // touches the live taps and runs near the HBM roofline there.
-    const int K = 2 * pl.width + pl.orig;
+    const int K = 2 * pl.width + pl.orig * m;
     const double live = 2.0 * lpfw * pl.orig / (std::min(pl.orig, pl.newf) * rolloff);
-    return pl.newf % 16 == 0 && pl.newf >= 16 && pl.newf <= FeRsTcCfg::MAX_N && live >= 256.0 && live >= 0.4 * K;
+    return (live >= 256.0 && live >= 0.4 * K) ? m : 0;
 }
 static float tf32_rna_host(float v) {            // cvt.rna.tf32.f32: nearest, ties away from zero
     uint32_t u;
@@ -2030,18 +2035,21 @@ static float tf32_rna_host(float v) {            // cvt.rna.tf32.f32: nearest, t
     memcpy(&v, &u, 4);
     return v;
 }
-static std::vector<float> rs_tc_pack(const FeRsPlan& pl, int lpfw, double rolloff, int method, double beta, int* nch_out) {
+static std::vector<float> rs_tc_pack(const FeRsPlan& pl, int m, int lpfw, double rolloff, int method, double beta, int* nch_out) {
     typedef FeRsTcCfg C;
-    const int N = pl.newf, K = 2 * pl.width + pl.orig, nch = (K + C::KC - 1) / C::KC;
+    const int N = pl.newf * m, K = 2 * pl.width + pl.orig, Ke = K + pl.orig * (m - 1), nch = (Ke + C::KC - 1) / C::KC;
     std::vector<float> h((size_t)nch * 2 * N * C::KC, 0.0f);
-    for (int p = 0; p < N; ++p)
+    for (int p = 0; p < pl.newf; ++p)
         for (int k = 0; k < K; ++k) {
             const float v = (float)fe_rs_tap(pl.orig, pl.newf, pl.width, lpfw, rolloff, method, beta, p, k);
             const float hi = tf32_rna_host(v), lo = tf32_rna_host(v - hi);
-            const int c = k / C::KC, kk = k % C::KC;
-            const size_t off = (size_t)(p / 8) * (C::SBO / 4) + (size_t)(kk / 4) * (C::LBO / 4) + (p % 8) * 4 + (kk % 4);
-            h[((size_t)c * 2 + 0) * N * C::KC + off] = hi;
-            h[((size_t)c * 2 + 1) * N * C::KC + off] = lo;
+            for (int c = 0; c < m; ++c) {           // output pe = c * new + p of the block group reads the window shifted by c * orig
+                const int pe = c * pl.newf + p, ke = k + c * pl.orig;
+                const int ch = ke / C::KC, kk = ke % C::KC;
+                const size_t off = (size_t)(pe / 8) * (C::SBO / 4) + (size_t)(kk / 4) * (C::LBO / 4) + (pe % 8) * 4 + (kk % 4);
+                h[((size_t)ch * 2 + 0) * N * C::KC + off] = hi;
+                h[((size_t)ch * 2 + 1) * N * C::KC + off] = lo;
+            }
         }
     *nch_out = nch;
     return h;
@@ -2091,8 +2099,8 @@ int rs_get_plan(int orig_freq, int new_freq, int lpfw, double rolloff, int metho
     if (e == cudaSuccess) e = cudaMalloc(&dp->kstart, dp->plan.kstart.size() * sizeof(int32_t));
     if (e == cudaSuccess) e = cudaMemcpy(dp->taps, dp->plan.taps.data(), dp->plan.taps.size() * sizeof(float), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(dp->kstart, dp->plan.kstart.data(), dp->plan.kstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && rs_tc_applicable(dp->plan, lpfw, rolloff)) {
-        const std::vector<float> hp = rs_tc_pack(dp->plan, lpfw, rolloff, method, beta, &dp->nch);
+    if (e == cudaSuccess && (dp->tc_m = rs_tc_blocks(dp->plan, lpfw, rolloff)) > 0) {
+        const std::vector<float> hp = rs_tc_pack(dp->plan, dp->tc_m, lpfw, rolloff, method, beta, &dp->nch);
         e = cudaMalloc(&dp->hpack, hp.size() * sizeof(float));
         if (e == cudaSuccess) e = cudaMemcpy(dp->hpack, hp.data(), hp.size() * sizeof(float), cudaMemcpyHostToDevice);
         if (e == cudaSuccess)
@@ -2183,7 +2191,7 @@ int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, cons
         q.x_stride = direct ? pcm_stride : (s16x2 ? pcm_stride / 2 : Ls);
         q.w0 = w0; q.w1 = w1;
         q.lengths = lengths; q.L_in = L_in; q.out = out; q.out_stride = out_stride; q.L_out = L_out;
-        q.hpack = dp->hpack; q.B = B; q.orig = dp->plan.orig; q.newf = dp->plan.newf; q.width = dp->plan.width;
+        q.hpack = dp->hpack; q.B = B; q.orig = dp->plan.orig * dp->tc_m; q.newf = dp->plan.newf * dp->tc_m; q.width = dp->plan.width;
         q.nch = dp->nch;
         const int64_t nblocks = (L_out + q.newf - 1) / q.newf;
         q.tiles_per_clip = (int32_t)((nblocks + C::M - 1) / C::M);

@@ -358,3 +358,23 @@ def test_gpu_reference_kaiser_filter_on_tensor_cores_full_size():
     assert (got4[:1].double() - ref).abs().max() <= 4e-6
     ref = orc.condition(pcm4[63:, :7001], 44100, 16000, **kw)
     assert (got4[63:, :ref.shape[1]].double() - ref).abs().max() <= 4e-6 and not got4[63, ref.shape[1]:].any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("of,nf", [(48000, 16000), (24000, 16000), (16000, 24000), (32000, 16000), (44100, 16000)])
+def test_gpu_reference_kaiser_filter_other_ratios(of, nf):
+    """The tensor-core path regroups m blocks so that new * m outputs form the GEMM's N (48 -> 16 kHz: 480 -> 160): every
+    ratio whose regrouped phase count is a multiple of 16 takes it.  Ragged clips, float64 restatement, 4e-6."""
+    import expressive_speech_translation_b200 as fe
+    kw = dict(fe.REFERENCE_RESAMPLER)
+    g = torch.Generator().manual_seed(of + nf)
+    y = (0.3 * torch.randn(3, 30011, generator=g)).clamp(-1, 1)
+    lens = [30011, 9999, 1]
+    got = fe.condition_pcm(y.cuda(), of, nf, lengths=lens, **kw).cpu()
+    for b, n in enumerate(lens):
+        ref = orc.resample_restated(y[b, :n], of, nf, dtype=torch.float64, **kw)
+        assert (got[b, :ref.shape[0]].double() - ref).abs().max() <= 4e-6, (b, n)
+        assert not got[b, ref.shape[0]:].any()
+    st = torch.randint(-20000, 20000, (2, 8000, 2), generator=g, dtype=torch.int16)
+    got = fe.condition_pcm(st.cuda(), of, nf, **kw).cpu()
+    assert (got.double() - orc.condition(st, of, nf, **kw)).abs().max() <= 4e-6

@@ -26,7 +26,28 @@ st = torch.randint(-20000, 20000, (2, 50000, 2), generator=g, dtype=torch.int16)
 gs = fe.condition_pcm(st.cuda(), 44100, 16000, mix=(0.65, 0.35), **kw).cpu()
 rs = orc.condition(st, 44100, 16000, weights=(0.65, 0.35), **kw)
 err2 = float((gs.double() - rs).abs().max())
+for of, nf in ((48000, 16000), (24000, 16000), (16000, 24000), (32000, 16000)):
+    y = (0.3 * torch.randn(2, 30011, generator=g)).clamp(-1, 1)
+    got_r = fe.condition_pcm(y.cuda(), of, nf, lengths=[30011, 9999], **kw).cpu()
+    e = 0.0
+    for b, n in enumerate([30011, 9999]):
+        ref = orc.resample_restated(y[b, :n], of, nf, dtype=torch.float64, **kw)
+        e = max(e, float((got_r[b, :ref.shape[0]].double() - ref).abs().max()))
+        assert not got_r[b, ref.shape[0]:].any()
+    print(f"[{of}->{nf}: {e:.2e}]", end=" ")
 gen = torch.Generator(device="cuda").manual_seed(1)
+b48 = (0.1 * torch.randn(B, 1440000, generator=gen, device="cuda")).clamp_(-1, 1)
+o48 = torch.empty(B, 480000, device="cuda")
+for _ in range(2):
+    fe.condition_pcm(b48, 48000, 16000, out=o48, **kw)
+torch.cuda.synchronize()
+a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+a.record()
+for _ in range(5):
+    fe.condition_pcm(b48, 48000, 16000, out=o48, **kw)
+b_.record(); torch.cuda.synchronize()
+print(f"[48k->16k {B} x 30 s: {a.elapsed_time(b_) / 5:.3f} ms]", end=" ")
+del b48, o48
 big = (0.1 * torch.randn(B, 1323000, generator=gen, device="cuda")).clamp_(-1, 1)
 out = torch.empty(B, 480000, device="cuda")
 for _ in range(2):
