@@ -25,6 +25,7 @@ from .api import (  # noqa: F401
     kaldi_fbank_host,
     condition_pcm,
     condition_stereo_auto,
+    condition_pcm_host,
     pcm_whisper_log_mel_batch,
     pcm_whisper_log_mel_host,
     REFERENCE_RESAMPLER,

@@ -631,6 +631,31 @@ def pcm_whisper_log_mel_batch(pcm, orig_freq, new_freq=WHISPER_SR, lengths=None,
     return out
 
 
+def condition_pcm_host(pcm, orig_freq, new_freq, lengths=None, mix=None, out=None, device=None, pin_output=True,
+                       lowpass_filter_width=6, rolloff=0.99, resampling_method="sinc_interp_hann", beta=None):
+    """condition_pcm for host buffers: host (ideally pinned) int16 / float32 PCM -> host float32 waveform
+    (B, ceil(new * L / orig)) through the library's chunked H2D / resampler / D2H pipeline.  Blocks."""
+    x = _pcm_tensor(pcm)
+    if x.is_cuda:
+        raise ValueError("pcm: the *_host entry points take host memory")
+    x = x.contiguous()
+    of, nf, width, ro, meth, bt = _rs_args(orig_freq, new_freq, lowpass_filter_width, rolloff, resampling_method, beta)
+    B, L, C = x.shape
+    L_out = resample_out_len(L, of, nf)
+    dev = _cuda_device(device)
+    out = _host_out((B, L_out), out, pin_output)
+    mix_arr = None
+    if mix is not None:
+        if len(mix) != C:
+            raise ValueError(f"mix has {len(mix)} weights for {C} channel(s)")
+        mix_arr = (ctypes.c_float * C)(*[float(v) for v in mix])
+    ln = _host_lengths(lengths, B)
+    if B and L_out:
+        check(lib.b200feat_resample_host(_ptr(x), _DTYPES[x.dtype], C, mix_arr, _ptr(ln), B, L, of, nf, width, ro, meth, bt,
+                                         _ptr(out), dev.index), "b200feat_resample_host")
+    return out
+
+
 def pcm_whisper_log_mel_host(pcm, orig_freq, new_freq=WHISPER_SR, lengths=None, mix=None, n_mels=80, padding=0, norm="per_clip",
                              out=None, out_dtype=torch.float32, device=None, pin_output=True, lowpass_filter_width=6,
                              rolloff=0.99, resampling_method="sinc_interp_hann", beta=None):

@@ -205,6 +205,23 @@ int b200feat_pcm_whisper_logmel_host(const void* pcm_host, int32_t pcm_dtype, in
                          Ls * 4 + 8, 1024);
 }
 
+// PCM in -> resampled float32 waveform out through the chunked pipeline (the host-buffer twin of b200feat_resample)
+int b200feat_resample_host(const void* pcm_host, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                           const int64_t* lengths_host, int32_t B, int64_t L_in, int32_t orig_freq, int32_t new_freq,
+                           int32_t lowpass_filter_width, double rolloff, int32_t method, double beta, float* out_host, int32_t device) {
+    if (pcm_dtype != B200FEAT_F32 && pcm_dtype != B200FEAT_S16)
+        return fail(B200FEAT_EINVAL, "resample_host: pcm_dtype must be B200FEAT_F32 or B200FEAT_S16, got %d", pcm_dtype);
+    if (channels != 1 && channels != 2) return fail(B200FEAT_EINVAL, "resample_host: channels must be 1 or 2, got %d", channels);
+    if (orig_freq <= 0 || new_freq <= 0) return fail(B200FEAT_EINVAL, "resample_host: Original frequency and desired frequecy should be positive");
+    const int64_t L = fe_rs_out_len(L_in, orig_freq, new_freq);
+    const int64_t frame_bytes = (int64_t)channels * (pcm_dtype == B200FEAT_S16 ? 2 : 4);
+    return host_pipeline(B200FEAT_KIND_COSY /* 16-byte workspace */, pcm_host, frame_bytes, lengths_host, B, L_in, L_in, L, out_host, 4, device, false,
+                         [=](const void* dw, const int64_t* dl, int32_t nc, void* dout, void*, int64_t, cudaStream_t st) {
+                             return b200feat_resample(dw, pcm_dtype, channels, mix_host, dl, nc, L_in, L_in * channels, orig_freq, new_freq,
+                                                      lowpass_filter_width, rolloff, method, beta, static_cast<float*>(dout), L, L, st);
+                         });
+}
+
 int b200feat_cosy_mel_host(const float* wave_host, const int64_t* lengths_host, int32_t B, int64_t L,
                            float* out_host, int32_t device) {
     const int64_t T = b200feat_num_frames(B200FEAT_KIND_COSY, L, 0);

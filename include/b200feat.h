@@ -218,6 +218,12 @@ int b200feat_condition_stereo_auto(const void* pcm, int32_t pcm_dtype, const int
                                    float* scratch, int64_t scratch_floats, int32_t* decisions, float* correlations,
                                    void* cuda_stream);
 
+/* Host-buffer twin of b200feat_resample: pcm_host (B, L_in, channels) densely packed, out_host (B, L_out) float32 with
+ * L_out = b200feat_resample_out_len(L_in, orig_freq, new_freq); chunked H2D / kernel / D2H pipeline, blocking. */
+int b200feat_resample_host(const void* pcm_host, int32_t pcm_dtype, int32_t channels, const float* mix_host,
+                           const int64_t* lengths_host, int32_t B, int64_t L_in, int32_t orig_freq, int32_t new_freq,
+                           int32_t lowpass_filter_width, double rolloff, int32_t method, double beta, float* out_host, int32_t device);
+
 /* PCM in, Whisper log-mel out, ONE call ("int16 PCM goes in and features come out"):
  * b200feat_resample (mono mix + sinc resampler, arguments as there) followed by b200feat_whisper_logmel_ex on the same
  * stream; the float32 waveform between them lives in `workspace` (b200feat_pcm_whisper_workspace_bytes), never in a

@@ -114,3 +114,18 @@ def test_gpu_pcm_to_log_mel_in_one_call_device_and_host():
     h = fe.pcm_whisper_log_mel_host(big.pin_memory(), 44100, n_mels=80)
     d = fe.pcm_whisper_log_mel_batch(big.cuda(), 44100, n_mels=80)
     assert torch.equal(h, d.cpu())
+
+
+@pytest.mark.gpu
+def test_gpu_resample_host_twin_equals_device_path():
+    """b200feat_resample_host: pinned and pageable PCM, both filters (CUDA-core and tensor-core kernels), ragged, chunked"""
+    import expressive_speech_translation_b200 as fe
+    g = torch.Generator().manual_seed(4)
+    pcm = torch.randint(-20000, 20000, (40, 44100 * 6, 2), generator=g, dtype=torch.int16)      # 42 MB of PCM + 15 MB out: two chunks
+    lens = [pcm.shape[1]] * 38 + [50000, 3]
+    for kw in (dict(), dict(fe.REFERENCE_RESAMPLER)):
+        dev = fe.condition_pcm(pcm.cuda(), 44100, 16000, lengths=lens, mix=(0.65, 0.35), **kw).cpu()
+        assert torch.equal(fe.condition_pcm_host(pcm.pin_memory(), 44100, 16000, lengths=lens, mix=(0.65, 0.35), **kw), dev)
+        assert torch.equal(fe.condition_pcm_host(pcm.numpy(), 44100, 16000, lengths=lens, mix=(0.65, 0.35), pin_output=False, **kw), dev)
+    mono = (0.2 * torch.randn(3, 24000, generator=g)).clamp(-1, 1)
+    assert torch.equal(fe.condition_pcm_host(mono, 16000, 24000), fe.condition_pcm(mono.cuda(), 16000, 24000).cpu())
