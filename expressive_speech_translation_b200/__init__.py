@@ -16,6 +16,7 @@ from .api import (  # noqa: F401
     wav2lip_mel_batch,
     wav2lip_num_frames,
     melspectrogram,
+    spectral_gate_batch,
     whisper_num_windows,
     cosy_mel_batch,
     cosy_prompt_feat,

@@ -79,6 +79,10 @@ SYMBOLS = {
     "b200feat_resample_host": (_c.c_int, [_c.c_void_p, _c.c_int32, _c.c_int32, _c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64,
                                           _c.c_int32, _c.c_int32, _c.c_int32, _c.c_double, _c.c_int32, _c.c_double, _c.c_void_p,
                                           _c.c_int32]),
+    "b200feat_spectral_gate_out_len": (_c.c_int64, [_c.c_int64]),
+    "b200feat_spectral_gate_workspace_bytes": (_c.c_int64, [_c.c_int32, _c.c_int64]),
+    "b200feat_spectral_gate": (_c.c_int, [_c.c_void_p, _c.c_void_p, _c.c_int32, _c.c_int64, _c.c_int64, _c.c_void_p, _c.c_int64,
+                                          _c.c_void_p, _c.c_int64, _c.c_void_p]),
     "b200feat_profile_begin": (_c.c_int, []),
     "b200feat_profile_end": (_c.c_int, [_c.POINTER(_c.c_double), _c.POINTER(_c.c_int64), _c.POINTER(_c.c_double),
                                         _c.POINTER(_c.c_int64)]),

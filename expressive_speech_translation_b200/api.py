@@ -274,6 +274,29 @@ def melspectrogram(wav):
     return out if w.is_cuda else out.cpu()
 
 
+def spectral_gate_batch(wave, lengths=None, out=None):
+    """(B, L) mono float32 batch on a CUDA device -> (B, 256 * (L // 256)) denoised and peak-normalised waveform: the
+    STFT spectral gate + iSTFT + `/ max * 0.95` of /root/reference/Backend/services/audio_processor.py:322-358, per clip."""
+    wave = _as_float_tensor(wave, "audio")
+    device = _cuda_device(wave.device if wave.is_cuda else None)
+    w, stride = _prep_wave(wave, device)
+    B, L = w.shape
+    L_out = int(lib.b200feat_spectral_gate_out_len(L))
+    if out is None:
+        out = torch.empty((B, L_out), dtype=torch.float32, device=device)
+    elif out.shape != (B, L_out) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != device:
+        raise ValueError(f"out must be a contiguous float32 ({B}, {L_out}) tensor on the wave's device")
+    if B == 0 or L_out == 0:
+        return out
+    ln = _lengths_dev(lengths, B, device)
+    nws = int(lib.b200feat_spectral_gate_workspace_bytes(B, L))
+    ws = torch.empty(nws, dtype=torch.uint8, device=device)
+    with torch.cuda.device(device):
+        check(lib.b200feat_spectral_gate(_ptr(w), _ptr(ln), B, L, stride, _ptr(out), L_out, _ptr(ws), nws, _stream(device)),
+              "b200feat_spectral_gate")
+    return out
+
+
 def kaldi_fbank_batch(wave, lengths=None, subtract_mean=True, out=None):
     """(B, L) 16 kHz batch on a CUDA device -> (B, T, 80) kaldi fbank, optionally mean-normalised per clip."""
     wave = _as_float_tensor(wave, "waveform")

@@ -23,6 +23,7 @@
 #include "fe_kaldi3.cuh"
 #include "fe_resample_tc.cuh"
 #include "fe_cosy.cuh"
+#include "fe_gate.cuh"
 #include "fe_resample.cuh"
 #define FE_RS_HAVE_PARAMS
 #include "fe_resample_plan.h"
@@ -1326,6 +1327,121 @@ __global__ void fe_rs_lengths_kernel(const int64_t* __restrict__ in_len, int64_t
     out_len[i] = o > L_out ? L_out : o;
 }
 
+// =====================================================================================================
+// spectral gate (fe_gate.cuh)
+// =====================================================================================================
+__global__ void __launch_bounds__(FeGCfg::NT, 2) fe_gate_stft_kernel(const FeCosyParams p, const FeGateParams g) {
+    typedef FeGCfg C;
+    extern __shared__ __align__(16) float sm[];
+    const int tid = threadIdx.x, cta = blockIdx.x;
+    fe_c_phase_load<C>(p, sm, tid, cta);
+    __syncthreads();
+    fe_c_phase_a<C>(p, sm, tid, cta);
+    __syncthreads();
+    fe_c_phase_b<C>(p, sm, tid, cta);
+    __syncthreads();
+    fe_g_phase_c_spec(g, p, sm, tid, cta);
+}
+
+// One warp per (clip, bin): the order statistics lo = floor(0.1 (n - 1)) and lo + 1 of the bin's n magnitudes by a 4-pass
+// radix select on the float bits (magnitudes are >= 0, so the bit patterns order like the values), then torch.quantile's
+// linear interpolation (torch.lerp's two-sided form).
+__global__ void __launch_bounds__(256) fe_gate_quantile_kernel(const FeGateParams g) {
+    __shared__ int hist[8][256];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t row = (int64_t)blockIdx.x * 8 + w;
+    if (row >= (int64_t)g.B * 513) return;
+    const int b = (int)(row / 513);
+    const int n = (int)FeGateTraits::frames(fe_clip_len(g.lengths, b, g.L), 0);
+    if (n <= 0) { if (lane == 0) g.nf[row] = 0.0f; return; }
+    const float2* __restrict__ s = g.spec + row * g.Ts;
+    const float pos = 0.1f * (float)(n - 1);
+    const int lo = (int)floorf(pos);
+    const float frac = pos - (float)lo;
+    unsigned prefix = 0, mask = 0;
+    int k = lo;                                           // rank still to find among the elements that match `prefix` under `mask`
+    int* const h = hist[w];
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        for (int i = lane; i < 256; i += 32) h[i] = 0;
+        __syncwarp();
+        for (int t = lane; t < n; t += 32) {
+            const float2 x = s[t];
+            const unsigned u = __float_as_uint(sqrtf(x.x * x.x + x.y * x.y));
+            if ((u & mask) == prefix) atomicAdd(&h[(u >> shift) & 255u], 1);
+        }
+        __syncwarp();
+        // bucket holding rank k: prefix sums over the 256 counters, 8 per lane
+        int c[8], tot = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { c[j] = h[8 * lane + j]; tot += c[j]; }
+        int incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        int before = incl - tot, found = -1, kk = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (found < 0 && k < before + c[j]) { found = 8 * lane + j; kk = k - before; }
+            before += c[j];
+        }
+        const unsigned vote = __ballot_sync(0xffffffffu, found >= 0);
+        const int src = __ffs(vote) - 1;
+        found = __shfl_sync(0xffffffffu, found, src);
+        kk = __shfl_sync(0xffffffffu, kk, src);
+        prefix |= (unsigned)found << shift;
+        mask |= 255u << shift;
+        k = kk;
+        __syncwarp();
+    }
+    const float v_lo = __uint_as_float(prefix);
+    // v_hi = element of rank lo + 1: v_lo again if enough copies of it remain above rank lo, else the smallest larger element
+    int le = 0;
+    float nxt = 3.0e38f;
+    for (int t = lane; t < n; t += 32) {
+        const float2 x = s[t];
+        const float m = sqrtf(x.x * x.x + x.y * x.y);
+        if (m <= v_lo) ++le; else nxt = fminf(nxt, m);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { le += __shfl_xor_sync(0xffffffffu, le, o); nxt = fminf(nxt, __shfl_xor_sync(0xffffffffu, nxt, o)); }
+    if (lane == 0) {
+        const float v_hi = (lo + 1 >= n || le > lo + 1) ? v_lo : nxt;
+        const float d = v_hi - v_lo;
+        g.nf[row] = frac < 0.5f ? v_lo + frac * d : v_hi - d * (1.0f - frac);
+    }
+}
+
+__global__ void __launch_bounds__(FeGICfg::NT, 1) fe_gate_inverse_kernel(const FeGateParams g) {
+    extern __shared__ __align__(16) float sm[];
+    __shared__ float red[FeGICfg::NW];
+    const int tid = threadIdx.x, cta = blockIdx.x;
+    fe_gi_phase_load(g, sm, tid, cta);
+    __syncthreads();
+    fe_gi_phase_1(sm, tid);
+    __syncthreads();
+    fe_gi_phase_2(sm, tid);
+    __syncthreads();
+    fe_gi_phase_3(sm, tid);
+    __syncthreads();
+    float mx = fe_gi_phase_ola(g, sm, tid, cta);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((tid & 31) == 0) red[tid >> 5] = mx;
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 1; i < FeGICfg::NW; ++i) mx = fmaxf(mx, red[i]);
+        atomicMax(g.peak + cta / g.tiles_per_clip, __float_as_int(mx));      // mx >= 0: the int order is the float order
+    }
+}
+
+__global__ void __launch_bounds__(256) fe_gate_scale_kernel(const FeGateParams g) {
+    const int b = blockIdx.y;
+    const float peak = __int_as_float(g.peak[b]);
+    if (!(peak > 0.0f)) return;                                              // audio_processor.py:356 `if max_amp > 0`
+    float* __restrict__ o = g.out + (int64_t)b * g.out_stride;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < g.L_out; i += (int64_t)gridDim.x * blockDim.x)
+        o[i] = o[i] / peak * 0.95f;                                          // `audio / max_amp * 0.95`, in that order
+}
+
 // the eight instantiations (mel bins x output dtype x input dtype) behind one switch
 template <class F>
 static int whisper2_for_each(F f) {
@@ -1539,6 +1655,8 @@ int check_device_arch() {
                                          FE_K3_CMN_SMEM_ROWS * (FeK3Cfg::NMEL / 2) * 4));
             FE_CUDA(cudaFuncSetAttribute(fe_cosy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeCCfg::SMEM_BYTES));
             FE_CUDA(cudaFuncSetAttribute(fe_wav2lip_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeLCfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_gate_stft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeGCfg::SMEM_BYTES));
+            FE_CUDA(cudaFuncSetAttribute(fe_gate_inverse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FeGICfg::SMEM_BYTES));
             state[dev] = 1;
         }
     }
@@ -1909,6 +2027,77 @@ int b200feat_wav2lip_mel(const float* wave, const int64_t* lengths, int32_t B, i
         p.clip0 = (int32_t)c0; p.nclips = (int32_t)nc;
         ProfScope ps(st, 0);
         fe_wav2lip_kernel<<<(unsigned)(nc * tiles), FeLCfg::NT, FeLCfg::SMEM_BYTES, st>>>(p);
+        g_launches++;
+    }
+    FE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------ spectral gate
+int64_t b200feat_spectral_gate_out_len(int64_t n_samples) { return n_samples < 0 ? -1 : FeGICfg::HOP * (n_samples / FeGICfg::HOP); }
+
+int64_t b200feat_spectral_gate_workspace_bytes(int32_t B, int64_t L) {
+    if (B < 0 || L < 0) return -1;
+    const int64_t Ts = 1 + L / FeGICfg::HOP;
+    auto r = [](int64_t v) { return (v + 255) & ~(int64_t)255; };
+    return 256 + r((int64_t)B * 513 * Ts * 8) + r((int64_t)B * 513 * 4) + r((int64_t)B * 4);
+}
+
+int b200feat_spectral_gate(const float* wave, const int64_t* lengths, int32_t B, int64_t L, int64_t wave_stride,
+                           float* out, int64_t out_stride, void* workspace, int64_t workspace_bytes, void* cuda_stream) {
+    if (int rc = common_checks("spectral_gate", wave, out, B, L, wave_stride)) return rc;
+    const int64_t L_out = b200feat_spectral_gate_out_len(L);
+    if (out_stride < L_out) return fail(B200FEAT_EINVAL, "spectral_gate: out_stride %lld < %lld samples", (long long)out_stride, (long long)L_out);
+    if (B > 0 && L <= FeGCfg::PADL)
+        return fail(B200FEAT_EINVAL, "spectral_gate: reflect padding (512) needs more than 512 samples, got %lld", (long long)L);
+    const int64_t need = b200feat_spectral_gate_workspace_bytes(B, L);
+    if (B > 0 && (workspace == nullptr || workspace_bytes < need))
+        return fail(B200FEAT_EWORKSPACE, "spectral_gate: workspace too small (%lld bytes, need %lld)", (long long)workspace_bytes, (long long)need);
+    if (B == 0 || L_out == 0) return 0;
+    if (int rc = check_device_arch()) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const int64_t Ts = 1 + L / FeGICfg::HOP;
+    auto r256 = [](int64_t v) { return (v + 255) & ~(int64_t)255; };
+    char* w = static_cast<char*>(workspace);
+    w += (256 - (reinterpret_cast<uintptr_t>(w) & 255)) & 255;
+    FeGateParams g;
+    memset(&g, 0, sizeof(g));
+    g.wave = wave; g.lengths = lengths; g.wave_stride = wave_stride; g.L = L; g.B = B;
+    g.spec = reinterpret_cast<float2*>(w); w += r256((int64_t)B * 513 * Ts * 8);
+    g.nf = reinterpret_cast<float*>(w); w += r256((int64_t)B * 513 * 4);
+    g.peak = reinterpret_cast<int32_t*>(w);
+    g.Ts = Ts; g.out = out; g.out_stride = out_stride; g.L_out = L_out;
+    g.tiles_per_clip = (int32_t)((L_out / FeGICfg::HOP + 2 + FeGICfg::OUT_HOPS - 1) / FeGICfg::OUT_HOPS);
+    FeCosyParams p;
+    memset(&p, 0, sizeof(p));
+    p.wave = wave; p.lengths = lengths; p.wave_stride = wave_stride; p.L = L; p.B = B; p.T_out = Ts;
+    const int64_t tiles = (Ts + FeGCfg::FT - 1) / FeGCfg::FT;
+    p.tiles_per_clip = (int32_t)tiles;
+    p.vec_ok = (aligned16(wave) && wave_stride % 4 == 0) ? 1 : 0;
+    p.clip0 = 0; p.nclips = B;
+    if ((int64_t)B * tiles > 0x7fffffff || (int64_t)B * g.tiles_per_clip > 0x7fffffff || B > 65535)
+        return fail(B200FEAT_EINVAL, "spectral_gate: batch too large");
+    FE_CUDA(cudaMemsetAsync(g.peak, 0, (size_t)B * 4, st));
+    {
+        ProfScope ps(st, 0);
+        fe_gate_stft_kernel<<<(unsigned)(B * tiles), FeGCfg::NT, FeGCfg::SMEM_BYTES, st>>>(p, g);
+        g_launches++;
+    }
+    {
+        ProfScope ps(st, 1);
+        fe_gate_quantile_kernel<<<(unsigned)(((int64_t)B * 513 + 7) / 8), 256, 0, st>>>(g);
+        g_launches++;
+    }
+    {
+        ProfScope ps(st, 0);
+        fe_gate_inverse_kernel<<<(unsigned)((int64_t)B * g.tiles_per_clip), FeGICfg::NT, FeGICfg::SMEM_BYTES, st>>>(g);
+        g_launches++;
+    }
+    {
+        int64_t gx = (L_out + 1023) / 1024;
+        if (gx > 1024) gx = 1024;
+        ProfScope ps(st, 1);
+        fe_gate_scale_kernel<<<dim3((unsigned)gx, (unsigned)B), 256, 0, st>>>(g);
         g_launches++;
     }
     FE_CUDA(cudaGetLastError());

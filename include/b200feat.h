@@ -218,6 +218,20 @@ int b200feat_condition_stereo_auto(const void* pcm, int32_t pcm_dtype, const int
                                    float* scratch, int64_t scratch_floats, int32_t* decisions, float* correlations,
                                    void* cuda_stream);
 
+/* Spectral-gate denoiser.  Replaces, for a batch of mono clips,
+ * /root/reference/Backend/services/audio_processor.py:322-358: torch.stft(1024, 256, Hann) | noise floor = 10 % quantile of
+ * each bin's magnitudes over time | gain = clamp((mag - 1.5 floor) / (mag + 1e-8), 0, 1) | x 1.2 on the range
+ * [int(T * 0.0625), int(T * 0.25)) of `mag.shape[1]` -- which is the FRAME axis in the reference's (513, T) tensor, and is
+ * reproduced as such | torch.istft | audio / max|audio| * 0.95.
+ *   wave (B, wave_stride) float32, L > 512 samples per row; lengths device int64[B] or NULL (a clip of <= 512 samples yields
+ *   zeros); out (B, out_stride) float32, b200feat_spectral_gate_out_len(L) = 256 * (L / 256) samples per row, a ragged clip's
+ *   row is zero behind its own 256 * (len / 256); workspace: b200feat_spectral_gate_workspace_bytes(B, L) (the complex
+ *   spectrum, 513 * (1 + L / 256) * 8 bytes per clip, the noise floors and the peaks).  Float32 throughout, like the reference. */
+int64_t b200feat_spectral_gate_out_len(int64_t n_samples);
+int64_t b200feat_spectral_gate_workspace_bytes(int32_t B, int64_t L);
+int b200feat_spectral_gate(const float* wave, const int64_t* lengths, int32_t B, int64_t L, int64_t wave_stride,
+                           float* out, int64_t out_stride, void* workspace, int64_t workspace_bytes, void* cuda_stream);
+
 /* Host-buffer twin of b200feat_resample: pcm_host (B, L_in, channels) densely packed, out_host (B, L_out) float32 with
  * L_out = b200feat_resample_out_len(L_in, orig_freq, new_freq); chunked H2D / kernel / D2H pipeline, blocking. */
 int b200feat_resample_host(const void* pcm_host, int32_t pcm_dtype, int32_t channels, const float* mix_host,

@@ -29,6 +29,7 @@ def load():
     lib.emu_whisper_f16.argtypes = [vp, vp, i32, i64, i64, i32, i32, i32, vp, i64]
     lib.emu_whisper3.argtypes = [vp, vp, i32, i64, i64, i32, i32, i32, vp, i32, i64]
     lib.emu_wav2lip.argtypes = [vp, vp, i32, i64, i64, vp, i64, i32, i32]
+    lib.emu_gate.argtypes = [vp, vp, i32, i64, i64, vp]
     lib.emu_whisper3_windows.argtypes = [vp, vp, i32, i64, i64, i32, i32, i32, i32, i32, vp, i32]
     lib.emu_whisper_s16.argtypes = [vp, vp, i32, i64, i64, i32, i32, i32, vp, i64]
     lib.emu_f2h.argtypes = [vp, vp, i64]

@@ -396,6 +396,70 @@ extern "C" int emu_wav2lip(const float* wave, const int64_t* lengths, int B, int
     return emu_stft3<FeLCfg>(wave, lengths, B, L, stride, out, T_out, frame_major, pad_mode);
 }
 
+// ------------------------------------------------------------------------------------------ spectral gate
+#include "fe_gate.cuh"
+#include <algorithm>
+extern "C" int emu_gate(const float* wave, const int64_t* lengths, int B, int64_t L, int64_t stride, float* out) {
+    typedef FeGCfg C;
+    const int64_t Ts = 1 + L / 256, L_out = 256 * (L / 256);
+    std::vector<float2> spec((size_t)B * 513 * Ts);
+    std::vector<float> nf((size_t)B * 513, 0.0f);
+    std::vector<int32_t> peak(B > 0 ? B : 1, 0);
+    FeGateParams g;
+    memset(&g, 0, sizeof(g));
+    g.wave = wave; g.lengths = lengths; g.wave_stride = stride; g.L = L; g.B = B;
+    g.spec = spec.data(); g.Ts = Ts; g.nf = nf.data(); g.peak = peak.data(); g.out = out; g.out_stride = L_out; g.L_out = L_out;
+    g.tiles_per_clip = (int)((L_out / FeGICfg::HOP + 2 + FeGICfg::OUT_HOPS - 1) / FeGICfg::OUT_HOPS);
+    FeCosyParams p;
+    memset(&p, 0, sizeof(p));
+    p.wave = wave; p.lengths = lengths; p.wave_stride = stride; p.L = L; p.B = B; p.T_out = Ts;
+    p.tiles_per_clip = (int)((Ts + C::FT - 1) / C::FT);
+    p.vec_ok = (((uintptr_t)wave & 15) == 0) && (stride % 4 == 0);
+    p.clip0 = 0; p.nclips = B;
+    {   // kernel 1: STFT
+        std::vector<float> sm(C::SMEM_FLOATS);
+        for (int cta = 0; cta < B * p.tiles_per_clip; ++cta) {
+            for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_load<C>(p, sm.data(), tid, cta);
+            for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_a<C>(p, sm.data(), tid, cta);
+            for (int tid = 0; tid < C::NT; ++tid) fe_c_phase_b<C>(p, sm.data(), tid, cta);
+            for (int tid = 0; tid < C::NT; ++tid) fe_g_phase_c_spec(g, p, sm.data(), tid, cta);
+        }
+    }
+    // kernel 2 restated (the GPU kernel selects by radix; here: sort): torch.quantile's linear interpolation
+    for (int b = 0; b < B; ++b) {
+        const int n = (int)FeGateTraits::frames(fe_clip_len(lengths, b, L), 0);
+        for (int bin = 0; bin < 513 && n > 0; ++bin) {
+            std::vector<float> m(n);
+            for (int t = 0; t < n; ++t) { const float2 x = spec[((size_t)b * 513 + bin) * Ts + t]; m[t] = sqrtf(x.x * x.x + x.y * x.y); }
+            std::sort(m.begin(), m.end());
+            const float pos = 0.1f * (float)(n - 1);
+            const int lo = (int)floorf(pos);
+            const float frac = pos - (float)lo, v_lo = m[lo], v_hi = m[std::min(lo + 1, n - 1)], d = v_hi - v_lo;
+            nf[(size_t)b * 513 + bin] = frac < 0.5f ? v_lo + frac * d : v_hi - d * (1.0f - frac);
+        }
+    }
+    {   // kernel 3: inverse
+        std::vector<float> sm(FeGICfg::SMEM_FLOATS);
+        for (int cta = 0; cta < B * g.tiles_per_clip; ++cta) {
+            for (int tid = 0; tid < FeGICfg::NT; ++tid) fe_gi_phase_load(g, sm.data(), tid, cta);
+            for (int tid = 0; tid < FeGICfg::NT; ++tid) fe_gi_phase_1(sm.data(), tid);
+            for (int tid = 0; tid < FeGICfg::NT; ++tid) fe_gi_phase_2(sm.data(), tid);
+            for (int tid = 0; tid < FeGICfg::NT; ++tid) fe_gi_phase_3(sm.data(), tid);
+            float mx = 0.0f;
+            for (int tid = 0; tid < FeGICfg::NT; ++tid) mx = std::max(mx, fe_gi_phase_ola(g, sm.data(), tid, cta));
+            union { float f; int32_t i; } u; u.f = mx;
+            int32_t& pk = peak[cta / g.tiles_per_clip];
+            pk = std::max(pk, u.i);
+        }
+    }
+    for (int b = 0; b < B; ++b) {   // kernel 4
+        union { float f; int32_t i; } u; u.i = peak[b];
+        if (!(u.f > 0.0f)) continue;
+        for (int64_t i = 0; i < L_out; ++i) out[(size_t)b * L_out + i] = out[(size_t)b * L_out + i] / u.f * 0.95f;
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------ resample
 #include "fe_resample.cuh"
 #define FE_RS_HAVE_PARAMS

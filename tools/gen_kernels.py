@@ -406,6 +406,8 @@ def main():
     cl.append(gen_codelet("fe_cdft10", 10))
     # Wav2Lip / Diff2Lip: N = 800 = 16 x 5 x 10 (shares fe_rdft16_h9 and fe_cdft10 with CosyVoice)
     cl.append(gen_codelet("fe_cdft5", 5))
+    # spectral gate (fe_gate.cuh): N = 1024 = 16 x 8 x 8 (forward: fe_rdft16_h9 first; inverse: complex fe_cdft16 first)
+    cl.append(gen_codelet("fe_cdft8", 8))
     with open(os.path.join(OUT, "fe_codelets.h"), "w") as f:
         f.write("\n".join(cl))
 
@@ -500,6 +502,12 @@ def main():
     tb.append(table(emit_array("fe_tw_w2l_a", twiddle_table(800, 50, 9))))
     tb.append("// Wav2Lip stage-B twiddles W_50^(n3*k2), [n3 = 0..9][k2 = 0..4]")
     tb.append(table(emit_array("fe_tw_w2l_b", twiddle_table(50, 10, 5))))
+    n = np.arange(1024, dtype=np.float64)
+    tb.append("// spectral gate: periodic Hann N = 1024; W_1024^(m*k1) [m = 0..63][k1 = 0..8] (forward) and [k1 = 0..15] (inverse); W_64^(n3*k2)")
+    tb.append(table(emit_array("fe_win_gate", 0.5 - 0.5 * np.cos(2 * np.pi * n / 1024.0))))
+    tb.append(table(emit_array("fe_tw_gate_a", twiddle_table(1024, 64, 9))))
+    tb.append(table(emit_array("fe_tw_gate_a16", twiddle_table(1024, 64, 16))))
+    tb.append(table(emit_array("fe_tw_gate_b", twiddle_table(64, 8, 8))))
     wl = slaney(16000, 800, 80, 55.0, 7600.0)
     tb.append(table(gen_melrolled("fe_melroll_w2l", wl, 401)))
     with open(os.path.join(OUT, "fe_tables.h"), "w") as f:
