@@ -99,6 +99,18 @@ class Workload:
             self.featurizer = "wav2lip_mel"
             self.traffic_key = None
             self.cpu_desc = "oracle.wav2lip (the reference's numpy/scipy arithmetic, float64)"
+        elif key == "gate":
+            # SURVEY 8(f)3, second half (not a BASELINE config): other_workloads only
+            self.B, self.L, self.sr, self.n_mels = 256, 480000, 16000, 0
+            self.T = 1 + self.L // 256
+            self.out_shape = (self.B, 256 * (self.L // 256))
+            self.kernel = "fe_gate_stft_kernel + fe_gate_quantile_kernel + fe_gate_inverse_kernel + fe_gate_scale_kernel"
+            self.cpu_clips = 16
+            self.desc = ("SURVEY 8(f)3: AudioProcessor's spectral gate (Backend/services/audio_processor.py:321-358; STFT 1024/256, 10 % "
+                         "quantile noise floor per bin, gain mask, iSTFT, peak normalisation), 256 x 30 s @ 16 kHz per GPU")
+            self.featurizer = "spectral_gate"
+            self.traffic_key = None
+            self.cpu_desc = "oracle.gate (the reference's own torch lines)"
         elif key == "cfg5":
             # the manifest sweep: a FIXED total of 10 000 clips, contiguous shards per rank (strong scaling), each shard
             # featurized in sub-batches of <= 512 clips like the manifest runner does
@@ -141,7 +153,7 @@ class Workload:
         else:
             raise ValueError(key)
         # algorithmic flops per audio-second (sparse mel, 2.5 N log2 N real-FFT model)
-        self.flops_per_audio_s = {"cfg2": 1.05e6, "cfg2pcm": None, "cfg2pcmk": None, "cfg3": 2.7e6, "cfg4": 1.4e6, "cfg5": 1.04e6, "w2l": 1.6e6}[key]
+        self.flops_per_audio_s = {"cfg2": 1.05e6, "cfg2pcm": None, "cfg2pcmk": None, "cfg3": 2.7e6, "cfg4": 1.4e6, "cfg5": 1.04e6, "w2l": 1.6e6, "gate": None}[key]
         self.audio_s_per_step = self.B * self.L / self.sr              # this rank's share
         self.scaling = "strong" if key == "cfg5" else "weak"
         # whole-job audio per step: fixed total for the sweep, per-GPU work x N otherwise
@@ -149,7 +161,7 @@ class Workload:
         self.e2e_clips = min(self.B, 1024)                              # clips of the shard the host-buffer leg streams per step
         if key in ("cfg2pcm", "cfg2pcmk") and world > 1:
             self.e2e_clips = 256                                        # 5.3 KB of pinned PCM per audio-ms: keep N ranks' pinned buffers small
-        self.out_per_clip = self.out_shape[1] * self.out_shape[2]
+        self.out_per_clip = self.out_shape[1] * (self.out_shape[2] if len(self.out_shape) > 2 else 1)
         self.bytes_per_clip = 4 * self.L + 4 * self.out_per_clip     # algorithmic: 4*(in) + 4*(out)
         if key in ("cfg2pcm", "cfg2pcmk"):                            # the roofline kernel here is the resampler: PCM in + waveform out
             self.bytes_per_clip = self.pcm_L * self.pcm_ch * 2 + 4 * self.L
@@ -180,6 +192,8 @@ class Workload:
             return lambda: fe.cosy_mel_batch(x, out=out)
         if self.key == "w2l":
             return lambda: fe.wav2lip_mel_batch(x, out=out)
+        if self.key == "gate":
+            return lambda: fe.spectral_gate_batch(x, out=out)
         return lambda: fe.kaldi_fbank_batch(x, subtract_mean=True, out=out)
 
     def host_step(self, fe, xh, oh, dev):
@@ -375,7 +389,11 @@ def measure_light(fe, wl, dev, rank, world, steps, barrier, max_over_ranks):
     res = {"workload": wl.desc, "scaling": wl.scaling, "ms_per_step": ms_step, "value": wl.global_audio_s / (ms_step * 1e-3), "unit": UNIT,
            "steps": steps, "kernel": wl.kernel, "kernel_ms_per_step": k_ms_step, "epilogue_ms_per_step": prof["epilogue_ms"] / steps,
            "launches_per_step": (prof["feature_launches"] + prof["epilogue_launches"]) // steps}
-    if wl.key in ("cfg2pcm", "cfg2pcmk"):
+    if wl.key == "gate":
+        res["roofline"] = {"bound": "hbm", "note": "four kernels; algorithmic bytes = waveform in + waveform out; the complex spectrum (513 x T x 8 "
+                                                   "bytes per clip, written once and read three times) is intermediate traffic",
+                           "frac_whole_step": bytes_step / 1e9 / (ms_step * 1e-3) / peak}
+    elif wl.key in ("cfg2pcm", "cfg2pcmk"):
         chain_bytes = wl.B * (wl.pcm_L * wl.pcm_ch * 2 + 4 * wl.out_per_clip)
         res["roofline"] = {"bound": "hbm", "note": "whole chain (mono mix + resampler, then log-mel) against the bytes a fully fused chain would "
                                                    "move: int16 PCM in + float32 features out; the float32 waveform in between is extra traffic",
@@ -684,7 +702,7 @@ def run_ours(args, rank, world, local_rank):
         del xh, oh
         torch.cuda.empty_cache()
         others = {}
-        for key in ("cfg3", "cfg4", "cfg2pcm", "cfg2pcmk", "w2l", "cfg5"):
+        for key in ("cfg3", "cfg4", "cfg2pcm", "cfg2pcmk", "w2l", "gate", "cfg5"):
             wl = Workload(key, rank, world)
             others[key] = measure_light(fe, wl, dev, rank, world, 3 if key == "cfg5" else min(args.steps, 5), barrier, max_over_ranks)
 
