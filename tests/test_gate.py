@@ -110,6 +110,16 @@ def test_gpu_against_the_reference_lines(fe):
 
 
 @pytest.mark.gpu
+def test_gpu_long_clip_more_frames_than_the_quantile_cache(fe):
+    """40 s = 2501 frames: the quantile kernel keeps rows of up to 2048 magnitudes in shared memory and re-reads longer ones"""
+    x = _clips(2, 16000 * 40, 11)
+    out = fe.spectral_gate_batch(x.cuda(), lengths=[16000 * 40, 16000 * 25]).cpu()
+    for b, n in enumerate([16000 * 40, 16000 * 25]):
+        ref = gate.reference_spectral_gate(x[b, :n])[0]
+        assert (out[b, :ref.shape[0]] - ref).abs().max() <= TOL, b
+
+
+@pytest.mark.gpu
 def test_gpu_full_size_properties(fe):
     """256 x 30 s: finite, peak 0.95 per clip, deterministic, one clip against the reference lines"""
     g = torch.Generator(device="cuda").manual_seed(2)
