@@ -7,21 +7,12 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "b200feat.cu")
 LIB = os.path.join(HERE, "lib", "libb200feat.so")
-DEPS = [
-    SRC,
-    os.path.join(HERE, "csrc", "b200feat_host.inl"),
-    os.path.join(HERE, "csrc", "fe_common.h"),
-    os.path.join(HERE, "csrc", "fe_whisper2.cuh"),
-    os.path.join(HERE, "csrc", "fe_whisper3.cuh"),
-    os.path.join(HERE, "csrc", "fe_kaldi.cuh"),
-    os.path.join(HERE, "csrc", "fe_kaldi3.cuh"),
-    os.path.join(HERE, "csrc", "fe_cosy.cuh"),
-    os.path.join(HERE, "csrc", "fe_resample.cuh"),
-    os.path.join(HERE, "csrc", "fe_resample_plan.h"),
-    os.path.join(HERE, "csrc", "generated", "fe_codelets.h"),
-    os.path.join(HERE, "csrc", "generated", "fe_tables.h"),
-    os.path.join(os.path.dirname(HERE), "include", "b200feat.h"),
-]
+import glob
+
+# every source under csrc/ (headers, the .inl, the generated tables): a header-only edit must rebuild the library
+DEPS = sorted(set([SRC] + glob.glob(os.path.join(HERE, "csrc", "*.cu")) + glob.glob(os.path.join(HERE, "csrc", "*.cuh")) +
+                  glob.glob(os.path.join(HERE, "csrc", "*.h")) + glob.glob(os.path.join(HERE, "csrc", "*.inl")) +
+                  glob.glob(os.path.join(HERE, "csrc", "generated", "*.h"))))
 
 
 def nvcc_path():

@@ -1084,7 +1084,7 @@ __global__ void __launch_bounds__(FeRsTcCfg::NTHREADS, 1) fe_resample_tc_kernel(
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int N = p.newf;
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(tc_smem);
-    const uint32_t stage_bytes = (uint32_t)(2 * N * C::KC * 4);            // H(hi, lo) of one chunk
+    const uint32_t stage_bytes = (uint32_t)p.stage_floats * 4u;            // room for the H(hi, lo) of the largest chunk
     const uint32_t bar0 = sbase + (uint32_t)C::NST * stage_bytes;          // full[NST], empty[NST], accf[2], acce[2], tmem slot
     const uint32_t full0 = bar0, empty0 = bar0 + 8u * C::NST, accf0 = bar0 + 16u * C::NST, acce0 = accf0 + 16u;
     uint32_t* const tm_slot = reinterpret_cast<uint32_t*>(tc_smem + (size_t)C::NST * stage_bytes + 16 * C::NST + 32);
@@ -1126,7 +1126,7 @@ __global__ void __launch_bounds__(FeRsTcCfg::NTHREADS, 1) fe_resample_tc_kernel(
 #pragma unroll 1
             for (int c = 0; c < p.nch; ++c, ++it, s = (s + 1 == C::NST ? 0 : s + 1), ph ^= (s == 0 ? 1u : 0u)) {
                 if (it % (uint32_t)C::PGROUPS != (uint32_t)group) continue;
-                const int64_t g = g0 + (int64_t)c * C::KC;
+                const int64_t g = g0 + (p.k0_dense >= 0 ? p.k0_dense + c * C::KC : p.vtab[c].x);
                 float e[C::KC];      // 4-byte elements: float32 samples, or (S16X2) int16 stereo frames as raw bits
                 if (g >= 0 && g + C::KC + 4 <= len) {
                     // 36 elements from the 16-byte boundary below g, shifted by g & 3 in registers
@@ -1219,26 +1219,29 @@ __global__ void __launch_bounds__(FeRsTcCfg::NTHREADS, 1) fe_resample_tc_kernel(
     } else if (warp == C::MMA_WARP) {
         // ------------------------------------------------------------------ MMA issuer: A from Tensor Memory, H from shared memory
         if (lane == 0) {
-            const uint32_t idesc = fe_umma_idesc_tf32(C::M, N);
-            const uint32_t lo_off = (uint32_t)(N * C::KC * 4);
             uint32_t s = 0, ph = 0, i = 0;
             for (int tile = first; tile < p.total_tiles; tile += step, ++i) {
                 const uint32_t a = i & 1u, aph = (i >> 1) & 1u;
                 fe_mbar_wait_spin(acce0 + 8u * a, aph ^ 1u);                   // the epilogue has drained this accumulator
                 fe_tc_fence_after();
                 const uint32_t d = tmem + a * (uint32_t)C::ACC_STRIDE;
+                int4 vnext = p.vtab[0];
 #pragma unroll 1
                 for (int c = 0; c < p.nch; ++c) {
+                    const int4 vc = vnext;
+                    if (c + 1 < p.nch) vnext = p.vtab[c + 1];              // the next entry's load overlaps this chunk's wait and issue
+                    const uint32_t n = (uint32_t)vc.z, dcol = d + ((uint32_t)vc.y & 0xffffu), first = ((uint32_t)vc.y >> 16) & 1u;
+                    const uint32_t idesc = fe_umma_idesc_tf32(C::M, (int)n);
                     fe_mbar_wait_spin(full0 + 8u * s, ph);
                     fe_tc_fence_after();
                     const uint32_t t_hi = tmem + C::a_hi_col(s), t_lo = tmem + C::a_lo_col(s);
-                    const uint64_t dbh = fe_umma_desc(sbase + s * stage_bytes), dbl = fe_umma_desc(sbase + s * stage_bytes + lo_off);
+                    const uint64_t dbh = fe_umma_desc(sbase + s * stage_bytes), dbl = fe_umma_desc(sbase + s * stage_bytes + n * C::KC * 4u);
 #pragma unroll
                     for (int ks = 0; ks < C::KC / 8; ++ks) {
                         const uint64_t ko = (uint64_t)(ks * 2 * C::LBO >> 4);  // the descriptor's address field counts 16-byte units
-                        fe_umma_tf32_ts(d, t_hi + 8 * ks, dbh + ko, idesc, (c | ks) != 0 ? 1u : 0u);
-                        fe_umma_tf32_ts(d, t_hi + 8 * ks, dbl + ko, idesc, 1u);
-                        fe_umma_tf32_ts(d, t_lo + 8 * ks, dbh + ko, idesc, 1u);
+                        fe_umma_tf32_ts(dcol, t_hi + 8 * ks, dbh + ko, idesc, (first && ks == 0) ? 0u : 1u);
+                        fe_umma_tf32_ts(dcol, t_hi + 8 * ks, dbl + ko, idesc, 1u);
+                        fe_umma_tf32_ts(dcol, t_lo + 8 * ks, dbh + ko, idesc, 1u);
                     }
                     fe_umma_commit(empty0 + 8u * s);       // arrives when the MMAs issued so far have read this stage
                     if (++s == C::NST) { s = 0; ph ^= 1u; }
@@ -1254,11 +1257,13 @@ __global__ void __launch_bounds__(FeRsTcCfg::NTHREADS, 1) fe_resample_tc_kernel(
             for (int tile = first; tile < p.total_tiles; tile += step) {
 #pragma unroll 1
                 for (int c = 0; c < p.nch; ++c) {
+                    const int4 vc = p.vtab[c];
+                    const uint32_t bytes = (uint32_t)vc.z * (uint32_t)(2 * C::KC * 4);
                     fe_mbar_wait_spin(empty0 + 8u * s, ph ^ 1u);
-                    fe_mbar_expect_tx(full0 + 8u * s, stage_bytes);
-                    const float* src = p.hpack + (size_t)c * (size_t)(2 * N * C::KC);
+                    fe_mbar_expect_tx(full0 + 8u * s, bytes);
+                    const float* src = p.hpack + (size_t)vc.w;
                     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                                 ::"r"(sbase + s * stage_bytes), "l"(src), "r"(stage_bytes), "r"(full0 + 8u * s) : "memory");
+                                 ::"r"(sbase + s * stage_bytes), "l"(src), "r"(bytes), "r"(full0 + 8u * s) : "memory");
                     if (++s == C::NST) { s = 0; ph ^= 1u; }
                 }
             }
@@ -2212,25 +2217,22 @@ struct RsDevicePlan {
     int32_t* kstart = nullptr;
     // tensor-core path (fe_resample_tc.cuh): the dense tap matrix, split hi / lo, in the B-operand layout
     float* hpack = nullptr;
-    int nch = 0, tc_m = 0;      // tc_m blocks of the plan form one row of the GEMM
+    int4* vtab = nullptr;
+    int nch = 0, tc_m = 0, tc_stage_floats = 0, tc_k0_dense = -1;      // tc_m blocks of the plan form one row of the GEMM
 };
 
-// Long filters run as a 3 x TF32 GEMM (fe_resample_tc.cuh).  m consecutive blocks are taken as one (orig * m input samples ->
+
+// The resampler's GEMM on the tensor cores (fe_resample_tc.cuh).  m consecutive blocks are taken as one (orig * m input samples ->
 // new * m outputs, the "phases" of the GEMM), m the largest value with N = new * m a multiple of 16 and <= 160: 44.1 -> 16 kHz
-// is 441 -> 160 with m = 1, 48 -> 16 kHz is 3 -> 1 with m = 160 (480 -> 160).  Returns m, or 0 when the path does not apply.
-static int rs_tc_blocks(const FeRsPlan& pl, int lpfw, double rolloff) {
-    const char* e = getenv("B200FEAT_RESAMPLE_TC");
-    if (e && atoi(e) == 0) return 0;
-    int m = FeRsTcCfg::MAX_N / pl.newf;
-    while (m > 0 && (pl.newf * m) % 16 != 0) --m;
-    if (m <= 0) return 0;
-    // The GEMM is dense over K = 2 * width + orig * m taps per output; the window's support is 2 * lpfw * orig / base of them.
-    // Short filters (torchaudio's default: 33 live taps of 475 at 44.1 -> 16 kHz) stay on the CUDA-core kernel, which only
-    // touches the live taps and runs near the HBM roofline there.
-    const int K = 2 * pl.width + pl.orig * m;
-    const double live = 2.0 * lpfw * pl.orig / (std::min(pl.orig, pl.newf) * rolloff);
-    return (live >= 256.0 && live >= 0.4 * K) ? m : 0;
-}
+// is 441 -> 160 with m = 1, 48 -> 16 kHz is 3 -> 1 with m = 160 (480 -> 160).  The plan is a table of chunks of 32 taps:
+//   dense   one block of all N phases over the whole K = 2 * width + orig * m       (long filters: the reference's kaiser / width 128)
+//   banded  blocks of 32 phases, each over the K range its phases' windows cover      (short filters: torchaudio's default)
+// whichever multiplies fewer zeros.  Ratios whose phase count does not fit stay on the CUDA-core kernel.
+struct RsTcPlan {
+    int m = 0, N = 0, orig_e = 0, stage_floats = 0, k0_dense = -1;
+    std::vector<int4> vtab;
+    std::vector<float> hpack;
+};
 static float tf32_rna_host(float v) {            // cvt.rna.tf32.f32: nearest, ties away from zero
     uint32_t u;
     memcpy(&u, &v, 4);
@@ -2238,24 +2240,75 @@ static float tf32_rna_host(float v) {            // cvt.rna.tf32.f32: nearest, t
     memcpy(&v, &u, 4);
     return v;
 }
-static std::vector<float> rs_tc_pack(const FeRsPlan& pl, int m, int lpfw, double rolloff, int method, double beta, int* nch_out) {
+static bool rs_tc_make(const FeRsPlan& pl, int lpfw, double rolloff, int method, double beta, RsTcPlan* out) {
     typedef FeRsTcCfg C;
-    const int N = pl.newf * m, K = 2 * pl.width + pl.orig, Ke = K + pl.orig * (m - 1), nch = (Ke + C::KC - 1) / C::KC;
-    std::vector<float> h((size_t)nch * 2 * N * C::KC, 0.0f);
+    const char* e = getenv("B200FEAT_RESAMPLE_TC");
+    const int mode = e ? atoi(e) : 3;                // 0 = off, 1 = dense only, 2 = banded only, 3 = both (default)
+    if (mode == 0) return false;
+    int m = C::MAX_N / pl.newf;
+    while (m > 0 && (pl.newf * m) % 16 != 0) --m;
+    if (m <= 0) return false;
+    const int N = pl.newf * m, K = 2 * pl.width + pl.orig, Ke = K + pl.orig * (m - 1);
+    // the regrouped tap matrix He[pe][ke] and every row's support
+    std::vector<float> He((size_t)N * Ke, 0.0f);
+    std::vector<int> lo(N, Ke), hi(N, -1);
     for (int p = 0; p < pl.newf; ++p)
         for (int k = 0; k < K; ++k) {
             const float v = (float)fe_rs_tap(pl.orig, pl.newf, pl.width, lpfw, rolloff, method, beta, p, k);
-            const float hi = tf32_rna_host(v), lo = tf32_rna_host(v - hi);
-            for (int c = 0; c < m; ++c) {           // output pe = c * new + p of the block group reads the window shifted by c * orig
+            if (v == 0.0f) continue;
+            for (int c = 0; c < m; ++c) {             // output pe = c * new + p of the block group reads the window shifted by c * orig
                 const int pe = c * pl.newf + p, ke = k + c * pl.orig;
-                const int ch = ke / C::KC, kk = ke % C::KC;
-                const size_t off = (size_t)(pe / 8) * (C::SBO / 4) + (size_t)(kk / 4) * (C::LBO / 4) + (pe % 8) * 4 + (kk % 4);
-                h[((size_t)ch * 2 + 0) * N * C::KC + off] = hi;
-                h[((size_t)ch * 2 + 1) * N * C::KC + off] = lo;
+                He[(size_t)pe * Ke + ke] = v;
+                lo[pe] = std::min(lo[pe], ke); hi[pe] = std::max(hi[pe], ke);
             }
         }
-    *nch_out = nch;
-    return h;
+    struct Blk { int p0, n, k0, nch; };
+    auto blocks = [&](int band) {
+        std::vector<Blk> b;
+        for (int p0 = 0; p0 < N; p0 += band) {
+            const int n = std::min(band, N - p0);
+            int l = Ke, u = -1;
+            for (int p = p0; p < p0 + n; ++p) { l = std::min(l, lo[p]); u = std::max(u, hi[p]); }
+            if (u < l) { l = 0; u = 0; }
+            b.push_back({p0, n, l, (u - l + C::KC) / C::KC});
+        }
+        return b;
+    };
+    // cost of a tile of 128 rows in cycles: the producers take about 900 per chunk whatever its N, the MMA thread 12 MMAs per chunk
+    // at about 30 + 0.35 N cycles each (46 at N = 32, 86 at N = 160: profiles/r02_ubench_tmem_mma.txt, r02_resample_tc.txt)
+    auto cost = [](const std::vector<Blk>& b) {
+        double chunks = 0.0, mma = 0.0;
+        for (const Blk& x : b) { chunks += x.nch; mma += x.nch * 12.0 * (30.0 + 0.35 * x.n); }
+        return std::max(900.0 * chunks, mma);
+    };
+    const std::vector<Blk> dense = blocks(N), banded = blocks(C::BAND);
+    const bool use_banded = mode == 2 || (mode == 3 && cost(banded) < cost(dense));
+    const std::vector<Blk>& bl = use_banded ? banded : dense;
+    out->m = m; out->N = N; out->orig_e = pl.orig * m;
+    out->vtab.clear(); out->hpack.clear();
+    int max_n = 0;
+    for (const Blk& b : bl) {
+        max_n = std::max(max_n, b.n);
+        for (int c = 0; c < b.nch; ++c) {
+            int4 v;
+            v.x = b.k0 + c * C::KC; v.y = b.p0 | (c == 0 ? 0x10000 : 0); v.z = b.n; v.w = (int)out->hpack.size();
+            out->vtab.push_back(v);
+            const size_t base = out->hpack.size();
+            out->hpack.resize(base + (size_t)2 * b.n * C::KC, 0.0f);
+            for (int pl_ = 0; pl_ < b.n; ++pl_)
+                for (int kk = 0; kk < C::KC; ++kk) {
+                    const int ke = v.x + kk;
+                    const float t = ke < Ke ? He[(size_t)(b.p0 + pl_) * Ke + ke] : 0.0f;
+                    const float h = tf32_rna_host(t), l = tf32_rna_host(t - h);
+                    const size_t off = (size_t)(pl_ / 8) * (C::SBO / 4) + (size_t)(kk / 4) * (C::LBO / 4) + (pl_ % 8) * 4 + (kk % 4);
+                    out->hpack[base + off] = h;
+                    out->hpack[base + (size_t)b.n * C::KC + off] = l;
+                }
+        }
+    }
+    out->stage_floats = 2 * max_n * C::KC;
+    out->k0_dense = use_banded ? -1 : bl[0].k0;
+    return true;
 }
 typedef std::tuple<int, int, int, int, double, int, double> RsKey;
 std::mutex g_rs_mu;
@@ -2302,19 +2355,23 @@ int rs_get_plan(int orig_freq, int new_freq, int lpfw, double rolloff, int metho
     if (e == cudaSuccess) e = cudaMalloc(&dp->kstart, dp->plan.kstart.size() * sizeof(int32_t));
     if (e == cudaSuccess) e = cudaMemcpy(dp->taps, dp->plan.taps.data(), dp->plan.taps.size() * sizeof(float), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(dp->kstart, dp->plan.kstart.data(), dp->plan.kstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess && (dp->tc_m = rs_tc_blocks(dp->plan, lpfw, rolloff)) > 0) {
-        const std::vector<float> hp = rs_tc_pack(dp->plan, dp->tc_m, lpfw, rolloff, method, beta, &dp->nch);
-        e = cudaMalloc(&dp->hpack, hp.size() * sizeof(float));
-        if (e == cudaSuccess) e = cudaMemcpy(dp->hpack, hp.data(), hp.size() * sizeof(float), cudaMemcpyHostToDevice);
+    RsTcPlan tc;
+    if (e == cudaSuccess && rs_tc_make(dp->plan, lpfw, rolloff, method, beta, &tc)) {
+        dp->tc_m = tc.m; dp->nch = (int)tc.vtab.size(); dp->tc_stage_floats = tc.stage_floats; dp->tc_k0_dense = tc.k0_dense;
+        e = cudaMalloc(&dp->hpack, tc.hpack.size() * sizeof(float));
+        if (e == cudaSuccess) e = cudaMalloc(&dp->vtab, tc.vtab.size() * sizeof(int4));
+        if (e == cudaSuccess) e = cudaMemcpy(dp->hpack, tc.hpack.data(), tc.hpack.size() * sizeof(float), cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(dp->vtab, tc.vtab.data(), tc.vtab.size() * sizeof(int4), cudaMemcpyHostToDevice);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(fe_resample_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeRsTcCfg::smem_bytes(FeRsTcCfg::MAX_N));
+            e = cudaFuncSetAttribute(fe_resample_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeRsTcCfg::smem_bytes(2 * FeRsTcCfg::MAX_N * FeRsTcCfg::KC));
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(fe_resample_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeRsTcCfg::smem_bytes(FeRsTcCfg::MAX_N));
+            e = cudaFuncSetAttribute(fe_resample_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FeRsTcCfg::smem_bytes(2 * FeRsTcCfg::MAX_N * FeRsTcCfg::KC));
     }
     if (e != cudaSuccess) {
         if (dp->taps) cudaFree(dp->taps);
         if (dp->kstart) cudaFree(dp->kstart);
         if (dp->hpack) cudaFree(dp->hpack);
+        if (dp->vtab) cudaFree(dp->vtab);
         delete dp;
         return fail(B200FEAT_ECUDA, "resample: uploading the tap table failed: %s", cudaGetErrorString(e));
     }
@@ -2395,7 +2452,7 @@ int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, cons
         q.w0 = w0; q.w1 = w1;
         q.lengths = lengths; q.L_in = L_in; q.out = out; q.out_stride = out_stride; q.L_out = L_out;
         q.hpack = dp->hpack; q.B = B; q.orig = dp->plan.orig * dp->tc_m; q.newf = dp->plan.newf * dp->tc_m; q.width = dp->plan.width;
-        q.nch = dp->nch;
+        q.nch = dp->nch; q.vtab = dp->vtab; q.stage_floats = dp->tc_stage_floats; q.k0_dense = dp->tc_k0_dense;
         const int64_t nblocks = (L_out + q.newf - 1) / q.newf;
         q.tiles_per_clip = (int32_t)((nblocks + C::M - 1) / C::M);
         const int64_t total = (int64_t)B * q.tiles_per_clip;
@@ -2407,8 +2464,8 @@ int b200feat_resample(const void* pcm, int32_t pcm_dtype, int32_t channels, cons
         const int sms = g_num_sms[dev < 64 ? dev : 0] > 0 ? g_num_sms[dev < 64 ? dev : 0] : 148;
         {
             ProfScope ps(st, 0);
-            if (s16x2) fe_resample_tc_kernel<true><<<(unsigned)(total < sms ? total : sms), C::NTHREADS, C::smem_bytes(q.newf), st>>>(q);
-            else fe_resample_tc_kernel<false><<<(unsigned)(total < sms ? total : sms), C::NTHREADS, C::smem_bytes(q.newf), st>>>(q);
+            if (s16x2) fe_resample_tc_kernel<true><<<(unsigned)(total < sms ? total : sms), C::NTHREADS, C::smem_bytes(q.stage_floats), st>>>(q);
+            else fe_resample_tc_kernel<false><<<(unsigned)(total < sms ? total : sms), C::NTHREADS, C::smem_bytes(q.stage_floats), st>>>(q);
             g_launches++;
         }
         if (mono) FE_CUDA(cudaFreeAsync(mono, st));

@@ -16,6 +16,11 @@
 // host, and each K step issues three MMAs, hi*hi + hi*lo + lo*hi, into one float32 accumulator in Tensor Memory: float32
 // accuracy (the dropped lo*lo term is 2^-22 relative) at a third of the TF32 rate.
 //
+// BANDED form (short filters: torchaudio's default hann / width-6 filter has 33 live taps of 475 at 44.1 -> 16 kHz): the phases are
+// cut into blocks of 32; a block only multiplies the K range its phases' windows cover (4 chunks of 32 taps instead of 15), into
+// its own 32 accumulator columns.  The kernel runs a table of chunks {first tap, accumulator column, N, H offset}; the dense form
+// is the table with one block.
+//
 // Roles of the 18 warps of a persistent CTA (one per SM):
 //   0-11  producers   three groups of four warps, chunks in turn: A(hi, lo) chunk of 128 rows x 32 k -> Tensor Memory
 //   12-15 epilogue    Tensor Memory -> registers -> out (one row of `new` samples per lane), masks ragged ends
@@ -29,7 +34,9 @@
 
 struct FeRsTcCfg {
     static constexpr int M = 128, KC = 32, NST = 3;
-    static constexpr int PGROUPS = 3;                          // producer groups of four warps (they take the chunks in turn)
+    static constexpr int PGROUPS = 3;                          // producer groups of four warps (they take the chunks in turn).  Must not
+                                                               // exceed NST: a group more than NST chunks ahead would wait on a stage's
+                                                               // barrier two phases early, which a parity wait cannot tell apart
     static constexpr int MMA_WARP = 4 * PGROUPS + 4, NTHREADS = 32 * (MMA_WARP + 2);
     static constexpr int LBO = 128, SBO = (KC / 4) * 128;      // H in shared memory: K-major core matrices, no swizzle
     // Tensor Memory columns (512): two accumulators of N <= 160 columns at 0 and 256; the A operand's NST stages of KC
@@ -38,8 +45,8 @@ struct FeRsTcCfg {
     static FE_HD constexpr uint32_t a_hi_col(uint32_t s) { return 160u + (uint32_t)KC * s; }
     static FE_HD constexpr uint32_t a_lo_col(uint32_t s) { return 416u + (uint32_t)KC * s; }
     static_assert(160 + KC * NST <= 256, "A stages must fit between the accumulators");
-    static int stage_bytes(int N) { return 2 * N * KC * 4; }
-    static int smem_bytes(int N) { return NST * stage_bytes(N) + 1024; }
+    static constexpr int BAND = 32;                            // phases per block of the banded form
+    static int smem_bytes(int stage_floats) { return NST * stage_floats * 4 + 1024; }
 };
 
 struct FeRsTcParams {
@@ -50,8 +57,11 @@ struct FeRsTcParams {
     int64_t L_in;
     float* out;                // (B, out_stride)
     int64_t out_stride, L_out;
-    const float* hpack;        // [nch][hi | lo][N / 8][KC / 4][8][4]
-    int32_t B, orig, newf, width, nch;
+    const float* hpack;        // per chunk: [hi | lo][n / 8][KC / 4][8][4]
+    const int4* vtab;          // per chunk: x = first tap (column of X), y = first accumulator column | 0x10000 on the first chunk of a
+                               // phase block, z = phases n of the block (the MMA's N), w = offset of the chunk's H in hpack (floats)
+    int32_t B, orig, newf, width, nch, stage_floats;
+    int32_t k0_dense;          // >= 0: one block, chunk c starts at tap k0_dense + 32 c (the producers need not read vtab); -1: banded
     int32_t tiles_per_clip, total_tiles;
     int32_t out_vec;           // out rows 16-byte aligned
 };
