@@ -26,6 +26,16 @@ the authoring container (see ``oracle/make_golden.py``):
                        analytically in the test (<= 5e-6 relative on energies >= 1e-2).
                        openai-whisper and matcha themselves are not importable here, so
                        a1 / a2 are pinned to independent twins, not to the upstream files.
+  * resampler        : oracle/resample.py runs the real torchaudio.functional.resample /
+                       transforms.Resample and pins a float64 restatement to them; the stereo
+                       rule is the reference's own torch lines (audio_processor.py:306-319)
+  * Wav2Lip mel      : oracle/wav2lip.py restates the reference-held
+                       Backend/diff2lip/audio/audio.py:45-51 line by line (librosa 0.9.2 is absent:
+                       its stft / filters.mel restated), pinned by torch.stft + torchaudio
+                       melscale_fbanks and by transformers.audio_utils.spectrogram
+                       (oracle/make_golden_w2l.py, tests/golden/w2l_rand.npz)
+  * spectral gate    : oracle/gate.py IS the reference's torch code
+                       (Backend/services/audio_processor.py:321-358), runnable here
 """
 from .filters import slaney_mel_filters, kaldi_mel_banks  # noqa: F401
 from .featurizers import (  # noqa: F401
